@@ -1,0 +1,146 @@
+/* ntcomp_b200.h -- C ABI of the B200-native ntcomp encode/decode hot path (libntcomp_b200.so).
+ *
+ * Drop-in boundary for tmaklin/ntcomp's sequence codec (reference file:line in each comment).
+ * Plain pointers and sizes only; every call returns an int32 status (NTC_OK == 0) and never
+ * throws/panics across the boundary; ntc_last_error() returns the calling thread's last message.
+ * One ntc_ctx per GPU, used from one host thread at a time; different contexts are independent.
+ * There is NO CPU fallback: every compute entry point fails with NTC_ERR_CUDA without a GPU.
+ *
+ * Record word (src/encode.rs:145-158, little-endian u64):
+ *   reference record (len > 11): bytes 0-3 colex rank (u32), bytes 4-6 len (u24), byte 7 = first (0/1)
+ *   literal record   (len <= 11): bytes 0-6 2-bit bases (base j at bits 2j..2j+1, A0 C1 G2 T3),
+ *                                 byte 7 = (first + 2) | len << 2
+ * Records of a read run from the read's END to its START; `first` marks the END segment.
+ */
+#ifndef NTCOMP_B200_H
+#define NTCOMP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ntc_index ntc_index; /* host-side flat SBWT + LCS (replaces SbwtIndexVariant + LcsArray, src/lib.rs:20-22) */
+typedef struct ntc_ctx ntc_ctx;     /* one GPU: re-laid-out index in HBM + workspaces */
+
+enum {
+    NTC_OK = 0,
+    NTC_ERR_INVALID_ARG = 1,
+    NTC_ERR_CUDA = 2,        /* no device / CUDA failure: there is no CPU fallback */
+    NTC_ERR_CAPACITY = 3,    /* caller's output buffer too small */
+    NTC_ERR_EMPTY_READ = 4,  /* EncodeError, src/lib.rs:224 / src/encode.rs:133 */
+    NTC_ERR_BAD_BASE = 5,    /* non-ACGT byte, or a base absent from the index (d == 0): the reference
+                                underflows at src/lib.rs:207 */
+    NTC_ERR_LEN24 = 6,       /* a record length >= 2^24, src/lib.rs:226 */
+    NTC_ERR_IO = 7,
+    NTC_ERR_BAD_RECORD = 8,  /* colex rank >= n_sets in a record handed to decode */
+    NTC_ERR_UNSUPPORTED = 9  /* k outside [12,255] or n_sets >= 2^32 (src/encode.rs:147 truncates to u32, Q2) */
+};
+
+const char* ntc_last_error(void);
+const char* ntc_version(void);
+
+/* ---------------- index (host) ------------------------------------------------------------- */
+
+/* Host SBWT+LCS construction; replaces kbo::build(&seqs, opts) as called at src/main.rs:111-134 and
+ * tests/fasta_data.rs:49-56 (add_revcomp = true, build_select = true there).  Offline preprocessing. */
+int32_t ntc_index_build(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n_seqs, uint32_t k,
+                        int32_t add_revcomp, int32_t n_threads, ntc_index** out);
+
+/* Flattened view of an existing SbwtIndex<SubsetMatrix> + LcsArray (what a Rust host passes after
+ * kbo::index::load_sbwt, src/main.rs:149,190): 4 subset rows of n_sets bits (LSB-first u64 words,
+ * A,C,G,T) and LCS as one byte per node.  C is recomputed from the rows. */
+int32_t ntc_index_from_arrays(uint32_t k, uint64_t n_sets, const uint64_t* row_a, const uint64_t* row_c,
+                              const uint64_t* row_g, const uint64_t* row_t, const uint8_t* lcs, ntc_index** out);
+
+/* Own flat file format (stands in for kbo::index::serialize_sbwt / load_sbwt, src/main.rs:138,149). */
+int32_t ntc_index_save(const ntc_index* idx, const char* path);
+int32_t ntc_index_load(const char* path, ntc_index** out);
+
+uint32_t ntc_index_k(const ntc_index* idx);          /* sbwt.k(), src/lib.rs:171 */
+uint64_t ntc_index_n_sets(const ntc_index* idx);
+void ntc_index_get_C(const ntc_index* idx, uint64_t out[5]);
+void ntc_index_get_row(const ntc_index* idx, int32_t c, uint64_t* out /* ceil(n_sets/64) words */);
+void ntc_index_get_lcs(const ntc_index* idx, uint8_t* out /* n_sets bytes */);
+void ntc_index_free(ntc_index* idx);
+
+/* ---------------- context (one per GPU) ---------------------------------------------------- */
+
+int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out);
+void ntc_ctx_destroy(ntc_ctx* ctx);
+/* bytes of HBM held by the re-laid-out index: [0]=rank blocks, [1]=LCS, [2]=decode jump table */
+void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]);
+
+/* ---------------- encode ------------------------------------------------------------------- */
+
+/* flat_map(encode_dictionary . encode_sequence) over a batch of reads: src/main.rs:166,169 with
+ * src/lib.rs:163-230 and src/encode.rs:129-166.  `bases` = reads concatenated (ASCII ACGT),
+ * `offsets` = n_reads+1 byte offsets.  Writes the u64 records of all reads in input order and, if
+ * rec_offsets != NULL, n_reads+1 record offsets.  HOST buffers. */
+int32_t ntc_encode_batch(ntc_ctx* ctx, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads,
+                         uint64_t* records, uint64_t cap, uint64_t* n_records, uint64_t* rec_offsets);
+
+/* encode_sequence alone (src/lib.rs:163): per record the tuple (len, interval.start, interval.end)
+ * as three u64; `triples` holds 3*cap words. */
+int32_t ntc_encode_sequence_batch(ntc_ctx* ctx, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads,
+                                  uint64_t* triples, uint64_t cap, uint64_t* n_records, uint64_t* rec_offsets);
+
+/* encode_dictionary alone (src/encode.rs:129): one read's dictionary of n (len,start,end) triples
+ * -> n record words (literal bases are rebuilt from the index, as access_kmer does at :151). */
+int32_t ntc_encode_dictionary(ntc_ctx* ctx, const uint64_t* triples, uint64_t n, uint64_t* records);
+
+/* worst-case number of records for a batch with this many bases (one record per base) */
+uint64_t ntc_encode_bound(uint64_t n_bases);
+
+/* ---------------- decode ------------------------------------------------------------------- */
+
+/* decode_sequence (src/lib.rs:254-318) over a record stream: sequences concatenated into `bases`,
+ * n_seqs+1 offsets into seq_offsets (capacity cap_seqs+1 entries).  HOST buffers. */
+int32_t ntc_decode_batch(ntc_ctx* ctx, const uint64_t* records, uint64_t n_records, uint8_t* bases, uint64_t cap,
+                         uint64_t* seq_offsets, uint64_t cap_seqs, uint64_t* n_seqs);
+
+/* decode_sequence + the FASTA writer loop of src/main.rs:201-209: ">seq.{N}\n{bases}\n" with
+ * N = first_seq_number, first_seq_number+1, ...  (1-based, running across blocks). */
+int32_t ntc_decode_fasta(ntc_ctx* ctx, const uint64_t* records, uint64_t n_records, uint64_t first_seq_number,
+                         uint8_t* text, uint64_t cap, uint64_t* n_bytes, uint64_t* n_seqs);
+
+/* exact output sizes for a record stream (host scan of the flag/len fields) */
+void ntc_decode_bound(const uint64_t* records, uint64_t n_records, uint64_t first_seq_number, uint64_t* n_bases,
+                      uint64_t* n_seqs, uint64_t* fasta_bytes);
+
+/* ---------------- device-resident variants (buffers already in HBM, stream-ordered) ----------
+ * Same semantics; all pointers are device pointers on ctx's GPU, `stream` is a cudaStream_t (0 =
+ * default stream).  Results that are counts stay on the device: d_counts[0] = n_records / n_seqs,
+ * d_counts[1] = bytes written.  ntc_ctx_status() synchronises the stream and returns the status of
+ * everything enqueued since the last call (and the counts, if out != NULL). */
+int32_t ntc_encode_device(ntc_ctx* ctx, const uint8_t* d_bases, const uint64_t* d_offsets, uint64_t n_reads,
+                          uint64_t n_bases, uint64_t* d_records, uint64_t cap, uint64_t* d_rec_offsets,
+                          uint64_t* d_counts, void* stream);
+int32_t ntc_decode_device(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_records, uint64_t first_seq_number,
+                          int32_t fasta, uint8_t* d_out, uint64_t cap, uint64_t* d_seq_offsets, uint64_t cap_seqs,
+                          uint64_t* d_counts, void* stream);
+int32_t ntc_ctx_status(ntc_ctx* ctx, void* stream);
+
+/* number of kernels this library launched on ctx since creation (bench.py's gpu_launches) */
+uint64_t ntc_ctx_launch_count(const ntc_ctx* ctx);
+
+/* matching statistics only (diagnostic / parity entry point for StreamingIndex::matching_statistics,
+ * src/lib.rs:172-173): per base d (u8) and interval start (u32).  HOST buffers. */
+int32_t ntc_matching_statistics(ntc_ctx* ctx, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads,
+                                uint8_t* d_out, uint32_t* start_out);
+
+/* ---------------- synthetic inputs (splitmix64 counter-based) -------------------- */
+void ntc_synth_genome(uint64_t seed, uint64_t n, uint8_t* out);
+/* reads r0..r0+n_reads of length read_len drawn from genome (both strands, substitution errors at
+ * rate err_ppm / 1e6) */
+void ntc_synth_reads(const uint8_t* genome, uint64_t genome_len, uint64_t seed, uint64_t r0, uint64_t n_reads,
+                     uint32_t read_len, uint32_t err_ppm, uint8_t* out, int32_t n_threads);
+/* same generator on the GPU, writing into device memory */
+int32_t ntc_synth_reads_device(ntc_ctx* ctx, const uint8_t* d_genome, uint64_t genome_len, uint64_t seed, uint64_t r0,
+                               uint64_t n_reads, uint32_t read_len, uint32_t err_ppm, uint8_t* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NTCOMP_B200_H */

@@ -1,0 +1,250 @@
+"""Host-side mirror of ntcomp's lib.rs encode/decode API over the C ABI (include/ntcomp_b200.h).
+
+Names, argument meaning and error behaviour follow the reference:
+
+    encode_sequence(nucleotides, sbwt, lcs)   src/lib.rs:163     -> [(len, range(start, end)), ...]
+    encode_dictionary(dictionary, sbwt)       src/encode.rs:129  -> uint64 record words
+    decode_sequence(encoding, sbwt)           src/lib.rs:254     -> [bytes, ...]
+
+In the reference `sbwt` / `lcs` are `SbwtIndexVariant` / `LcsArray`; here both live in one
+`Context` (the index re-laid-out in one GPU's HBM), which is passed for either argument.
+The batched calls (`Context.encode_batch`, `.decode_batch`, `.decode_fasta`) are what a host should
+use; the per-read functions above are thin shims over a batch of one, as in INTEGRATION.md.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import NtcError, check
+
+
+class EncodeError(ValueError):
+    """src/encode.rs:38-47: 'invalid input to encode'."""
+
+    def __str__(self):
+        return "invalid input to encode"
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _u8(x):
+    if isinstance(x, (bytes, bytearray, memoryview)):
+        return np.frombuffer(bytes(x), dtype=np.uint8)
+    return np.ascontiguousarray(x, dtype=np.uint8)
+
+
+def concat_reads(reads):
+    """list of bytes / uint8 arrays -> (bases uint8[total], offsets uint64[n+1])"""
+    arrs = [_u8(r) for r in reads]
+    offsets = np.zeros(len(arrs) + 1, dtype=np.uint64)
+    if arrs:
+        offsets[1:] = np.cumsum([len(a) for a in arrs], dtype=np.uint64)
+    bases = np.concatenate(arrs) if arrs else np.zeros(0, dtype=np.uint8)
+    return np.ascontiguousarray(bases, dtype=np.uint8), offsets
+
+
+class Index:
+    """Host flat SBWT + LCS (stands in for kbo::build / kbo::index::load_sbwt, src/main.rs:134,149)."""
+
+    def __init__(self, handle):
+        self._h = handle
+        L = _lib.lib()
+        self.k = int(L.ntc_index_k(handle))
+        self.n_sets = int(L.ntc_index_n_sets(handle))
+
+    @classmethod
+    def build(cls, seqs, k, add_revcomp=True, n_threads=0):
+        L = _lib.lib()
+        arrs = [_u8(s) for s in seqs]
+        n = len(arrs)
+        ptrs = (C.c_void_p * max(n, 1))(*[a.ctypes.data for a in arrs])
+        lens = np.array([len(a) for a in arrs], dtype=np.uint64)
+        h = C.c_void_p()
+        check(L.ntc_index_build(C.cast(ptrs, C.c_void_p), _ptr(lens), n, k, int(add_revcomp), n_threads, C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def from_arrays(cls, k, n_sets, rows, lcs):
+        L = _lib.lib()
+        rows = [np.ascontiguousarray(r, dtype=np.uint64) for r in rows]
+        lcs = np.ascontiguousarray(lcs, dtype=np.uint8)
+        h = C.c_void_p()
+        check(L.ntc_index_from_arrays(k, n_sets, _ptr(rows[0]), _ptr(rows[1]), _ptr(rows[2]), _ptr(rows[3]), _ptr(lcs), C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def load(cls, path):
+        h = C.c_void_p()
+        check(_lib.lib().ntc_index_load(str(path).encode(), C.byref(h)))
+        return cls(h)
+
+    def save(self, path):
+        check(_lib.lib().ntc_index_save(self._h, str(path).encode()))
+
+    def C(self):
+        out = np.zeros(5, dtype=np.uint64)
+        _lib.lib().ntc_index_get_C(self._h, _ptr(out))
+        return out
+
+    def rows(self):
+        out = []
+        for c in range(4):
+            a = np.zeros((self.n_sets + 63) // 64, dtype=np.uint64)
+            _lib.lib().ntc_index_get_row(self._h, c, _ptr(a))
+            out.append(a)
+        return out
+
+    def lcs(self):
+        a = np.zeros(self.n_sets, dtype=np.uint8)
+        _lib.lib().ntc_index_get_lcs(self._h, _ptr(a))
+        return a
+
+    def close(self):
+        if self._h:
+            _lib.lib().ntc_index_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Context:
+    """One GPU: index in HBM + workspaces.  Raises NtcError(NTC_ERR_CUDA) when no GPU is present."""
+
+    def __init__(self, index, device=0):
+        h = C.c_void_p()
+        check(_lib.lib().ntc_ctx_create(device, index._h, C.byref(h)))
+        self._h = h
+        self.device = device
+        self.k = index.k
+        self.n_sets = index.n_sets
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _lib.lib().ntc_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def index_bytes(self):
+        out = np.zeros(3, dtype=np.uint64)
+        _lib.lib().ntc_ctx_index_bytes(self._h, _ptr(out))
+        return {"rank": int(out[0]), "lcs": int(out[1]), "jump": int(out[2])}
+
+    def launch_count(self):
+        return int(_lib.lib().ntc_ctx_launch_count(self._h))
+
+    # ---- host-buffer API ----
+    def encode_batch(self, bases, offsets, cap=None, want_offsets=True):
+        """flat_map(encode_dictionary . encode_sequence): returns (records uint64[], rec_offsets uint64[n+1])."""
+        bases = _u8(bases)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n = len(offsets) - 1
+        if cap is None:
+            cap = max(int(offsets[-1] - offsets[0]), 1)
+        rec = np.empty(cap, dtype=np.uint64)
+        roff = np.zeros(n + 1, dtype=np.uint64) if want_offsets else None
+        n_rec = C.c_uint64(0)
+        check(_lib.lib().ntc_encode_batch(self._h, _ptr(bases), _ptr(offsets), n, _ptr(rec), cap, C.byref(n_rec), _ptr(roff)))
+        return rec[: n_rec.value], roff
+
+    def encode_sequence_batch(self, bases, offsets):
+        """encode_sequence over a batch: returns (triples uint64[n_rec,3], rec_offsets)."""
+        bases = _u8(bases)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n = len(offsets) - 1
+        cap = max(int(offsets[-1] - offsets[0]), 1)
+        tri = np.empty(3 * cap, dtype=np.uint64)
+        roff = np.zeros(n + 1, dtype=np.uint64)
+        n_rec = C.c_uint64(0)
+        check(_lib.lib().ntc_encode_sequence_batch(self._h, _ptr(bases), _ptr(offsets), n, _ptr(tri), cap, C.byref(n_rec), _ptr(roff)))
+        return tri[: 3 * n_rec.value].reshape(-1, 3), roff
+
+    def encode_dictionary(self, triples):
+        tri = np.ascontiguousarray(triples, dtype=np.uint64).reshape(-1, 3)
+        out = np.empty(max(len(tri), 1), dtype=np.uint64)
+        check(_lib.lib().ntc_encode_dictionary(self._h, _ptr(tri), len(tri), _ptr(out)))
+        return out[: len(tri)]
+
+    def decode_bound(self, records, first_seq_number=1):
+        rec = np.ascontiguousarray(records, dtype=np.uint64)
+        nb, ns, fb = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        _lib.lib().ntc_decode_bound(_ptr(rec), len(rec), first_seq_number, C.byref(nb), C.byref(ns), C.byref(fb))
+        return nb.value, ns.value, fb.value
+
+    def decode_batch(self, records):
+        """decode_sequence: returns (bases uint8[], seq_offsets uint64[n_seqs+1])."""
+        rec = np.ascontiguousarray(records, dtype=np.uint64)
+        nb, ns, _ = self.decode_bound(rec)
+        bases = np.empty(max(nb, 1), dtype=np.uint8)
+        soff = np.zeros(ns + 1, dtype=np.uint64)
+        n_seqs = C.c_uint64(0)
+        check(_lib.lib().ntc_decode_batch(self._h, _ptr(rec), len(rec), _ptr(bases), nb, _ptr(soff), ns, C.byref(n_seqs)))
+        return bases[:nb], soff[: n_seqs.value + 1]
+
+    def decode_fasta(self, records, first_seq_number=1):
+        """decode_sequence + the writer loop of src/main.rs:201-209: returns (text bytes, n_seqs)."""
+        rec = np.ascontiguousarray(records, dtype=np.uint64)
+        _, _, fb = self.decode_bound(rec, first_seq_number)
+        text = np.empty(max(fb, 1), dtype=np.uint8)
+        n_bytes, n_seqs = C.c_uint64(0), C.c_uint64(0)
+        check(_lib.lib().ntc_decode_fasta(self._h, _ptr(rec), len(rec), first_seq_number, _ptr(text), fb, C.byref(n_bytes), C.byref(n_seqs)))
+        return text[: n_bytes.value].tobytes(), n_seqs.value
+
+    def matching_statistics(self, bases, offsets):
+        bases = _u8(bases)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        nb = int(offsets[-1] - offsets[0])
+        d = np.zeros(max(nb, 1), dtype=np.uint8)
+        s = np.zeros(max(nb, 1), dtype=np.uint32)
+        check(_lib.lib().ntc_matching_statistics(self._h, _ptr(bases), _ptr(offsets), len(offsets) - 1, _ptr(d), _ptr(s)))
+        return d[:nb], s[:nb]
+
+    # ---- device-resident API (raw device pointers as ints, e.g. torch.Tensor.data_ptr()) ----
+    def encode_device(self, d_bases, d_offsets, n_reads, n_bases, d_records, cap, d_rec_offsets, d_counts, stream=0):
+        check(_lib.lib().ntc_encode_device(self._h, d_bases, d_offsets, n_reads, n_bases, d_records, cap, d_rec_offsets, d_counts, stream))
+
+    def decode_device(self, d_records, n_records, first_seq_number, fasta, d_out, cap, d_seq_offsets, cap_seqs, d_counts, stream=0):
+        check(_lib.lib().ntc_decode_device(self._h, d_records, n_records, first_seq_number, int(fasta), d_out, cap, d_seq_offsets, cap_seqs,
+                                           d_counts, stream))
+
+    def status(self, stream=0):
+        check(_lib.lib().ntc_ctx_status(self._h, stream))
+
+
+# ---- reference-named shims (batch of one) ----
+
+def encode_sequence(nucleotides, sbwt, lcs=None):
+    """src/lib.rs:163.  `sbwt` is a Context (it also holds the LCS array)."""
+    seq = _u8(nucleotides)
+    try:
+        tri, _ = sbwt.encode_sequence_batch(seq, np.array([0, len(seq)], dtype=np.uint64))
+    except NtcError as e:
+        if e.code == 4:  # NTC_ERR_EMPTY_READ
+            raise EncodeError() from e
+        raise
+    return [(int(t[0]), range(int(t[1]), int(t[2]))) for t in tri]
+
+
+def encode_dictionary(dictionary, sbwt):
+    """src/encode.rs:129."""
+    if len(dictionary) == 0:
+        raise EncodeError()
+    tri = np.array([[ln, rg.start, rg.stop] for ln, rg in dictionary], dtype=np.uint64)
+    return sbwt.encode_dictionary(tri)
+
+
+def decode_sequence(encoding, sbwt):
+    """src/lib.rs:254."""
+    bases, off = sbwt.decode_batch(encoding)
+    return [bases[int(off[i]): int(off[i + 1])].tobytes() for i in range(len(off) - 1)]

@@ -1,0 +1,252 @@
+// api.cu -- C ABI of the hot path: context creation (index re-layout + upload), the stream-ordered
+// device pipelines, and the host-buffer entry points a Rust/cgo/ctypes caller binds.
+// There is no CPU fallback here: without a GPU every compute entry point returns NTC_ERR_CUDA.
+#include <algorithm>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "../../include/ntcomp_b200.h"
+#include "ctx.h"
+#include "decode_kernels.cuh"
+#include "encode_kernels.cuh"
+#include "host_index.h"
+#include "synth_common.h"
+
+using namespace ntc;
+
+namespace {
+
+struct CountLoad {
+    const uint32_t* c;
+    __device__ __forceinline__ Pair64 operator()(uint64_t i) const { return Pair64{c[i], 0}; }
+};
+
+inline unsigned blocks_for(uint64_t n, unsigned per) { return (unsigned)((n + per - 1) / per); }
+
+__global__ void copy_totals_kernel(const uint64_t* totals, uint64_t* counts) {
+    counts[0] = totals[0];
+    counts[1] = totals[0] * 8;
+}
+
+__global__ void __launch_bounds__(256) synth_reads_kernel(const uint8_t* __restrict__ genome, uint64_t genome_len, uint64_t seed,
+                                                          uint64_t r0, uint64_t n_reads, uint32_t read_len, uint32_t err_ppm,
+                                                          uint8_t* __restrict__ out) {
+    uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    uint64_t total = n_reads * read_len;
+    if (i >= total) return;
+    uint64_t r = i / read_len;
+    uint32_t t = (uint32_t)(i - r * read_len);
+    out[i] = read_base(genome, genome_len, seed, r0 + r, read_len, err_ppm, t);
+}
+
+int32_t status_to_code(uint32_t st) {
+    if (st & ST_BAD_BASE) { set_error("read holds a non-ACGT byte or a base absent from the index (reference underflows at src/lib.rs:207)"); return NTC_ERR_BAD_BASE; }
+    if (st & ST_EMPTY_READ) { set_error("empty read (EncodeError, src/lib.rs:224)"); return NTC_ERR_EMPTY_READ; }
+    if (st & ST_LEN24) { set_error("record length >= 2^24 (src/lib.rs:226)"); return NTC_ERR_LEN24; }
+    if (st & ST_BAD_RECORD) { set_error("record holds a colex rank >= n_sets"); return NTC_ERR_BAD_RECORD; }
+    if (st & ST_CAPACITY) { set_error("output buffer too small"); return NTC_ERR_CAPACITY; }
+    return NTC_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// encode pipeline on device buffers.  MODE 0 records, 1 triples.  carry (device, 2 x u64, may be
+// null) is added to every record offset; the grand total lands in totals_out (device, 2 x u64).
+// ------------------------------------------------------------------------------------------
+int32_t encode_pipeline(ntc_ctx* ctx, int mode, const uint8_t* d_bases, const uint64_t* d_offsets, uint64_t n_reads,
+                        uint64_t n_bases, uint64_t* d_out, uint64_t cap, uint64_t* d_rec_offsets, const uint64_t* carry,
+                        uint64_t* totals_out, cudaStream_t st) {
+    if (n_reads == 0) {
+        NTC_CUDA_TRY(cudaMemsetAsync(totals_out, 0, 16, st));
+        if (carry) NTC_CUDA_TRY(cudaMemcpyAsync(totals_out, carry, 16, cudaMemcpyDeviceToDevice, st));
+        if (d_rec_offsets) NTC_CUDA_TRY(cudaMemcpyAsync(d_rec_offsets, totals_out, 8, cudaMemcpyDeviceToDevice, st));
+        return NTC_OK;
+    }
+    const uint64_t n_words = n_bases / 32 + 2;
+    NTC_CUDA_TRY(ensure(&ctx->packed, n_words * 8));
+    NTC_CUDA_TRY(ensure(&ctx->scratch, std::max<uint64_t>(n_bases, 1) * 8));
+    NTC_CUDA_TRY(ensure(&ctx->counts, n_reads * 4));
+    NTC_CUDA_TRY(ensure(&ctx->tiles, scan_num_tiles(n_reads) * sizeof(Pair64)));
+    uint64_t* rec_off = d_rec_offsets;
+    if (!rec_off) {
+        NTC_CUDA_TRY(ensure(&ctx->rec_off, (n_reads + 1) * 8));
+        rec_off = (uint64_t*)ctx->rec_off.p;
+    }
+    uint64_t* packed = (uint64_t*)ctx->packed.p;
+    uint64_t* scratch = (uint64_t*)ctx->scratch.p;
+    uint32_t* counts = (uint32_t*)ctx->counts.p;
+
+    if (n_bases) {
+        pack2bit_kernel<<<blocks_for((n_bases + 31) / 32, kPackThreads), kPackThreads, 0, st>>>(d_bases, d_offsets, n_bases, packed,
+                                                                                                ctx->d_status);
+        ctx->launches++;
+    }
+    ms_kernel<<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
+                                                                      ctx->d_status);
+    ctx->launches++;
+    ctx->launches += exclusive_scan_pairs(CountLoad{counts}, n_reads, (Pair64*)ctx->tiles.p, carry, totals_out, rec_off, nullptr, st);
+    if (mode == 0)
+        emit_kernel<0><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
+                                                                               rec_off, d_out, cap, ctx->d_status);
+    else
+        emit_kernel<1><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
+                                                                               rec_off, d_out, cap, ctx->d_status);
+    ctx->launches++;
+    NTC_CUDA_TRY(cudaGetLastError());
+    return NTC_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// decode pipeline on device buffers
+// ------------------------------------------------------------------------------------------
+int32_t decode_pipeline(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* d_out,
+                        uint64_t cap, uint64_t* d_seq_offsets, uint64_t cap_seqs, uint64_t* d_counts, cudaStream_t st) {
+    if (n_rec == 0) {
+        NTC_CUDA_TRY(cudaMemsetAsync(d_counts, 0, 16, st));
+        if (d_seq_offsets) NTC_CUDA_TRY(cudaMemsetAsync(d_seq_offsets, 0, 8, st));
+        return NTC_OK;
+    }
+    NTC_CUDA_TRY(ensure(&ctx->base_off, (n_rec + 1) * 8));
+    NTC_CUDA_TRY(ensure(&ctx->seq_idx, (n_rec + 1) * 8));
+    NTC_CUDA_TRY(ensure(&ctx->seq_first, (n_rec + 1) * 8));
+    NTC_CUDA_TRY(ensure(&ctx->tiles, scan_num_tiles(n_rec) * sizeof(Pair64)));
+    uint64_t* base_off = (uint64_t*)ctx->base_off.p;
+    uint64_t* seq_idx = (uint64_t*)ctx->seq_idx.p;
+    uint64_t* seq_first = (uint64_t*)ctx->seq_first.p;
+    uint64_t* totals = ctx->d_totals + 4;
+    ctx->launches += exclusive_scan_pairs(RecordLoad{d_records}, n_rec, (Pair64*)ctx->tiles.p, nullptr, totals, base_off, seq_idx, st);
+    seq_starts_kernel<<<blocks_for(n_rec, 256), 256, 0, st>>>(d_records, n_rec, seq_idx, seq_first);
+    seq_offsets_kernel<<<blocks_for(n_rec + 1, 256), 256, 0, st>>>(base_off, seq_first, totals, n_rec, d_seq_offsets, cap_seqs, first_no,
+                                                                   fasta, cap, d_counts, ctx->d_status);
+    walk_kernel<<<blocks_for(n_rec, 128), 128, 0, st>>>(ctx->dix, d_records, n_rec, base_off, seq_idx, seq_first, totals, first_no, fasta,
+                                                        d_out, cap, d_counts, ctx->d_status);
+    ctx->launches += 3;
+    NTC_CUDA_TRY(cudaGetLastError());
+    return NTC_OK;
+}
+
+int32_t read_status(ntc_ctx* ctx, cudaStream_t st) {
+    uint32_t h = 0;
+    NTC_CUDA_TRY(cudaMemcpyAsync(&h, ctx->d_status, 4, cudaMemcpyDeviceToHost, st));
+    NTC_CUDA_TRY(cudaStreamSynchronize(st));
+    if (h) NTC_CUDA_TRY(cudaMemsetAsync(ctx->d_status, 0, 4, st));
+    return status_to_code(h);
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
+    if (!idx || !out) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    *out = nullptr;
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) {
+        set_error(std::string("no CUDA device available (this library has no CPU fallback): ") + cudaGetErrorString(e));
+        return NTC_ERR_CUDA;
+    }
+    if (device < 0 || device >= n_dev) { set_error("device ordinal out of range"); return NTC_ERR_INVALID_ARG; }
+    NTC_CUDA_TRY(cudaSetDevice(device));
+    ntc_ctx* ctx = new ntc_ctx();
+    ctx->device = device;
+    ctx->k = idx->k;
+    ctx->n = idx->n;
+    if (const char* env = getenv("NTC_MAX_CHUNK_BASES")) {
+        unsigned long long v = strtoull(env, nullptr, 10);
+        if (v >= 1024) ctx->max_chunk_bases = v;
+    }
+    int threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    std::vector<uint32_t> rank;
+    std::vector<uint64_t> jump;
+    build_rank_blocks(*idx, &rank, threads);
+    build_jump_table(*idx, &jump, threads);
+    std::vector<uint8_t> lcs(idx->lcs);
+    lcs.push_back(0);
+    auto fail = [&](const char* what, cudaError_t err) {
+        set_error(std::string(what) + ": " + cudaGetErrorString(err));
+        ntc_ctx_destroy(ctx);
+        return NTC_ERR_CUDA;
+    };
+    ctx->index_bytes[0] = rank.size() * 4;
+    ctx->index_bytes[1] = lcs.size();
+    ctx->index_bytes[2] = jump.size() * 8;
+    if ((e = cudaMalloc(&ctx->d_rank, ctx->index_bytes[0])) != cudaSuccess) return fail("cudaMalloc rank", e);
+    if ((e = cudaMalloc(&ctx->d_lcs, ctx->index_bytes[1])) != cudaSuccess) return fail("cudaMalloc lcs", e);
+    if ((e = cudaMalloc(&ctx->d_jump, ctx->index_bytes[2])) != cudaSuccess) return fail("cudaMalloc jump", e);
+    if ((e = cudaMemcpy(ctx->d_rank, rank.data(), ctx->index_bytes[0], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload rank", e);
+    if ((e = cudaMemcpy(ctx->d_lcs, lcs.data(), ctx->index_bytes[1], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload lcs", e);
+    if ((e = cudaMemcpy(ctx->d_jump, jump.data(), ctx->index_bytes[2], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload jump", e);
+    if ((e = cudaMalloc((void**)&ctx->d_status, 16)) != cudaSuccess) return fail("cudaMalloc status", e);
+    if ((e = cudaMalloc((void**)&ctx->d_totals, 64)) != cudaSuccess) return fail("cudaMalloc totals", e);
+    if ((e = cudaMalloc((void**)&ctx->d_counts, 32)) != cudaSuccess) return fail("cudaMalloc counts", e);
+    cudaMemset(ctx->d_status, 0, 16);
+    cudaMemset(ctx->d_totals, 0, 64);
+    cudaMemset(ctx->d_counts, 0, 32);
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    ctx->dix.rank = (const uint4*)ctx->d_rank;
+    ctx->dix.lcs = (const uint8_t*)ctx->d_lcs;
+    ctx->dix.jump = (const uint64_t*)ctx->d_jump;
+    ctx->dix.n = (uint32_t)idx->n;
+    ctx->dix.k = idx->k;
+    *out = ctx;
+    return NTC_OK;
+}
+
+void ntc_ctx_destroy(ntc_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+    cudaFree(ctx->d_rank); cudaFree(ctx->d_lcs); cudaFree(ctx->d_jump);
+    cudaFree(ctx->d_status); cudaFree(ctx->d_totals); cudaFree(ctx->d_counts);
+    DevBuf* bufs[] = {&ctx->packed, &ctx->scratch, &ctx->counts, &ctx->tiles, &ctx->rec_off, &ctx->base_off, &ctx->seq_idx,
+                      &ctx->seq_first, &ctx->st_in, &ctx->st_off, &ctx->st_out, &ctx->st_out2};
+    for (DevBuf* b : bufs) release(b);
+    delete ctx;
+}
+
+void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]) { memcpy(out, ctx->index_bytes, 24); }
+uint64_t ntc_ctx_launch_count(const ntc_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int32_t ntc_ctx_status(ntc_ctx* ctx, void* stream) {
+    if (!ctx) { set_error("null ctx"); return NTC_ERR_INVALID_ARG; }
+    NTC_CUDA_TRY(cudaSetDevice(ctx->device));
+    return read_status(ctx, (cudaStream_t)stream);
+}
+
+// ---------------- device-resident entry points ----------------
+
+int32_t ntc_encode_device(ntc_ctx* ctx, const uint8_t* d_bases, const uint64_t* d_offsets, uint64_t n_reads, uint64_t n_bases,
+                          uint64_t* d_records, uint64_t cap, uint64_t* d_rec_offsets, uint64_t* d_counts, void* stream) {
+    if (!ctx || !d_offsets || (!d_records && cap)) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    NTC_CUDA_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t rc = encode_pipeline(ctx, 0, d_bases, d_offsets, n_reads, n_bases, d_records, cap, d_rec_offsets, nullptr, ctx->d_totals, st);
+    if (rc) return rc;
+    if (d_counts) { copy_totals_kernel<<<1, 1, 0, st>>>(ctx->d_totals, d_counts); ctx->launches++; }
+    return NTC_OK;
+}
+
+int32_t ntc_decode_device(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_records, uint64_t first_seq_number, int32_t fasta,
+                          uint8_t* d_out, uint64_t cap, uint64_t* d_seq_offsets, uint64_t cap_seqs, uint64_t* d_counts, void* stream) {
+    if (!ctx || (!d_records && n_records) || !d_counts) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    if (fasta && first_seq_number == 0) { set_error("first_seq_number is 1-based"); return NTC_ERR_INVALID_ARG; }
+    NTC_CUDA_TRY(cudaSetDevice(ctx->device));
+    return decode_pipeline(ctx, d_records, n_records, first_seq_number, fasta, d_out, cap, d_seq_offsets, cap_seqs, d_counts,
+                           (cudaStream_t)stream);
+}
+
+int32_t ntc_synth_reads_device(ntc_ctx* ctx, const uint8_t* d_genome, uint64_t genome_len, uint64_t seed, uint64_t r0, uint64_t n_reads,
+                               uint32_t read_len, uint32_t err_ppm, uint8_t* d_out, void* stream) {
+    if (!ctx || !d_genome || !d_out || read_len == 0 || genome_len < read_len) { set_error("bad argument"); return NTC_ERR_INVALID_ARG; }
+    NTC_CUDA_TRY(cudaSetDevice(ctx->device));
+    uint64_t total = n_reads * read_len;
+    if (total) synth_reads_kernel<<<blocks_for(total, 256), 256, 0, (cudaStream_t)stream>>>(d_genome, genome_len, seed, r0, n_reads, read_len,
+                                                                                             err_ppm, d_out);
+    NTC_CUDA_TRY(cudaGetLastError());
+    return NTC_OK;
+}
+
+}  // extern "C"
+
+#include "api_host.inc"

@@ -1,0 +1,77 @@
+// ctx.h -- per-GPU context: re-laid-out index in HBM, grow-only workspaces, status words.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+
+#include "device_common.cuh"
+#include "scan.cuh"
+
+namespace ntc {
+void set_error(const std::string& msg);
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+}  // namespace ntc
+
+struct ntc_ctx {
+    int device = 0;
+    ntc::DevIndex dix{};
+    void* d_rank = nullptr;
+    void* d_lcs = nullptr;
+    void* d_jump = nullptr;
+    uint64_t index_bytes[3] = {0, 0, 0};
+    uint32_t k = 0;
+    uint64_t n = 0;
+
+    uint32_t* d_status = nullptr;   // [4]
+    uint64_t* d_totals = nullptr;   // [8]: ping-pong scan totals (2 x Pair64) + spare
+    uint64_t* d_counts = nullptr;   // [4]: internal counts for the host-buffer API
+    uint64_t launches = 0;
+    uint64_t max_chunk_bases = 1ull << 30;
+
+    // encode workspaces
+    ntc::DevBuf packed, scratch, counts, tiles, rec_off;
+    // decode workspaces
+    ntc::DevBuf base_off, seq_idx, seq_first;
+    // staging for the host-buffer API
+    ntc::DevBuf st_in, st_off, st_out, st_out2;
+    cudaStream_t stream = nullptr;  // internal stream of the host-buffer API
+};
+
+namespace ntc {
+
+#define NTC_CUDA_TRY(expr)                                                                   \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            ntc::set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));              \
+            return NTC_ERR_CUDA;                                                             \
+        }                                                                                    \
+    } while (0)
+
+// grow-only device buffer
+inline cudaError_t ensure(DevBuf* b, size_t bytes) {
+    if (bytes <= b->cap) return cudaSuccess;
+    if (b->p) { cudaFree(b->p); b->p = nullptr; b->cap = 0; }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&b->p, want);
+    if (e != cudaSuccess) { want = bytes; e = cudaMalloc(&b->p, want); }
+    if (e == cudaSuccess) b->cap = want;
+    return e;
+}
+inline void release(DevBuf* b) {
+    if (b->p) cudaFree(b->p);
+    b->p = nullptr;
+    b->cap = 0;
+}
+
+}  // namespace ntc

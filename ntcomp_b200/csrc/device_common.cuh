@@ -1,0 +1,70 @@
+// device_common.cuh -- HBM layout of the re-laid-out index and small device helpers (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ntc {
+
+// status bits accumulated by kernels in ctx->d_status[0]
+enum : uint32_t {
+    ST_EMPTY_READ = 1u << 0,
+    ST_BAD_BASE = 1u << 1,
+    ST_LEN24 = 1u << 2,
+    ST_CAPACITY = 1u << 3,
+    ST_BAD_RECORD = 1u << 4,
+};
+
+// Index as the kernels see it.  All arrays are L2-resident at the BASELINE configs
+// (5 Mbp / k=91: rank 13.4 MB, LCS 10 MB, jump 80 MB).
+struct DevIndex {
+    const uint4* rank;     // [(n/48+1) * 4] entries {C[c] + ones before block, row bits 0-31,
+                           //   row bits 32-47 | Q bits 0-15 << 16, Q bits 16-47}; c = entry index & 3
+    const uint8_t* lcs;    // [n + 1], lcs[n] = 0
+    const uint64_t* jump;  // [n] pred^16 | chars16 << 32
+    uint32_t n;
+    uint32_t k;
+};
+
+// scratch entry written by the matching-statistics pass, one per base:
+//   bits 0-31 interval start, 32-39 d, 40-63 length of the run of "unique predecessor" positions
+//   ending here (replaces left_extend_kmer's 4 x search per base, src/lib.rs:94-128)
+__device__ __forceinline__ uint64_t make_entry(uint32_t s, uint32_t d, uint32_t urun) {
+    return (uint64_t)s | ((uint64_t)d << 32) | ((uint64_t)urun << 40);
+}
+__device__ __forceinline__ uint32_t entry_s(uint64_t e) { return (uint32_t)e; }
+__device__ __forceinline__ uint32_t entry_d(uint64_t e) { return (uint32_t)(e >> 32) & 0xFFu; }
+__device__ __forceinline__ uint32_t entry_urun(uint64_t e) { return (uint32_t)(e >> 40); }
+
+// ones of the entry's row in block-relative positions [0, off), off in [0, 48)
+__device__ __forceinline__ uint32_t entry_rank(const uint4& e, uint32_t off) {
+    uint64_t bits = (uint64_t)e.y | ((uint64_t)(e.z & 0xFFFFu) << 32);
+    return e.x + (uint32_t)__popcll(bits & ((1ull << off) - 1ull));
+}
+__device__ __forceinline__ uint32_t entry_qbit(const uint4& e, uint32_t off) {
+    uint64_t q = (uint64_t)(e.z >> 16) | ((uint64_t)e.w << 16);
+    return (uint32_t)(q >> off) & 1u;
+}
+
+__device__ __forceinline__ uint4 ldg_entry(const uint4* p) { return __ldg(p); }
+
+// 2-bit base at chunk-relative position p of a packed stream (32 bases per u64, LSB first)
+__device__ __forceinline__ uint32_t packed_base(const uint64_t* __restrict__ packed, uint64_t p) {
+    return (uint32_t)(__ldg(packed + (p >> 5)) >> ((p & 31) * 2)) & 3u;
+}
+// up to 32 bases starting at position p, base j of the result at bits 2j..2j+1 (bitnuc as_2bit order)
+__device__ __forceinline__ uint64_t packed_slice(const uint64_t* __restrict__ packed, uint64_t p, uint32_t len) {
+    uint64_t w0 = __ldg(packed + (p >> 5));
+    uint32_t sh = (uint32_t)(p & 31) * 2;
+    uint64_t v = w0 >> sh;
+    if (sh && (p & 31) + len > 32) v |= __ldg(packed + (p >> 5) + 1) << (64 - sh);
+    return len >= 32 ? v : (v & ((1ull << (2 * len)) - 1ull));
+}
+
+// "ACGT"[code] for four 2-bit codes held in the low byte of x -> 4 ASCII bytes
+__device__ __forceinline__ uint32_t codes4_to_ascii(uint32_t x) {
+    // spread 2-bit codes into nibble selectors for PRMT over the table 'A','C','G','T'
+    uint32_t sel = (x & 3u) | ((x & 0xCu) << 2) | ((x & 0x30u) << 4) | ((x & 0xC0u) << 6);
+    return __byte_perm(0x54474341u, 0u, sel);
+}
+
+}  // namespace ntc

@@ -1,0 +1,246 @@
+// host_index.cpp -- flat index bookkeeping, own file format, and the HBM layouts derived from the
+// canonical arrays (rank blocks with inline counts + Q bits; 16-step decode jump table).
+#include "host_index.h"
+
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <thread>
+
+#include "../../include/ntcomp_b200.h"
+
+namespace ntc {
+
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+const char* last_error() { return g_error.c_str(); }
+
+namespace {
+template <typename F>
+void parallel_chunks(uint64_t n, uint64_t chunk, int n_threads, F f) {  // f(lo, hi)
+    uint64_t n_chunks = (n + chunk - 1) / chunk;
+    std::atomic<uint64_t> next(0);
+    auto work = [&]() {
+        for (;;) {
+            uint64_t c = next.fetch_add(1);
+            if (c >= n_chunks) break;
+            f(c * chunk, std::min(n, (c + 1) * chunk));
+        }
+    };
+    if (n_threads < 1) n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    std::vector<std::thread> pool;
+    for (int t = 1; t < n_threads; t++) pool.emplace_back(work);
+    work();
+    for (auto& t : pool) t.join();
+}
+inline bool row_bit(const ntc_index& idx, int c, uint64_t i) { return (idx.rows[c][i >> 6] >> (i & 63)) & 1; }
+}  // namespace
+
+int32_t finalize_index(ntc_index* idx) {
+    if (idx->k < kMinK || idx->k > kMaxK) { set_error("k must be in [12,255]"); return NTC_ERR_UNSUPPORTED; }
+    if (idx->n == 0 || idx->n >= (1ull << 32)) { set_error("n_sets must be in [1, 2^32)"); return NTC_ERR_UNSUPPORTED; }
+    const uint64_t words = (idx->n + 63) / 64;
+    idx->C[0] = 1;
+    for (int c = 0; c < 4; c++) {
+        if (idx->rows[c].size() < words) { set_error("row too short"); return NTC_ERR_INVALID_ARG; }
+        idx->rows[c].resize(words);
+        if (idx->n & 63) idx->rows[c][words - 1] &= (1ull << (idx->n & 63)) - 1;
+        uint64_t ones = 0;
+        for (uint64_t w = 0; w < words; w++) ones += (uint64_t)__builtin_popcountll(idx->rows[c][w]);
+        idx->C[c + 1] = idx->C[c] + ones;
+    }
+    if (idx->C[4] != idx->n) { set_error("subset rows must hold exactly n_sets-1 edges"); return NTC_ERR_INVALID_ARG; }
+    if (idx->lcs.size() != idx->n) { set_error("lcs must have n_sets entries"); return NTC_ERR_INVALID_ARG; }
+    return NTC_OK;
+}
+
+void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out, int n_threads) {
+    const uint64_t n = idx.n;
+    const uint32_t k = idx.k;
+    const uint64_t n_blocks = n / kBlockNodes + 1;  // position n (interval end) must be addressable
+    out->assign(n_blocks * 16, 0);
+    // running counts at block starts: one sequential popcount pass per row
+    std::vector<uint32_t> cum[4];
+    for (int c = 0; c < 4; c++) {
+        cum[c].resize(idx.rows[c].size() + 1);
+        uint32_t acc = 0;
+        for (size_t w = 0; w < idx.rows[c].size(); w++) { cum[c][w] = acc; acc += (uint32_t)__builtin_popcountll(idx.rows[c][w]); }
+        cum[c][idx.rows[c].size()] = acc;
+    }
+    auto rank = [&](int c, uint64_t i) -> uint32_t {
+        if (i >= n) return cum[c][idx.rows[c].size()];
+        uint64_t w = i >> 6, b = i & 63;
+        uint32_t r = cum[c][w];
+        if (b) r += (uint32_t)__builtin_popcountll(idx.rows[c][w] & ((1ull << b) - 1));
+        return r;
+    };
+    auto qbit = [&](uint64_t v) -> uint64_t {
+        if (v >= n) return 0;
+        bool lead = idx.lcs[v] < k - 1;
+        bool next_lead = (v + 1 == n) || idx.lcs[v + 1] < k - 1;
+        return (lead && next_lead) ? 1 : 0;
+    };
+    parallel_chunks(n_blocks, 4096, n_threads, [&](uint64_t lo, uint64_t hi) {
+        for (uint64_t b = lo; b < hi; b++) {
+            uint64_t base = b * kBlockNodes;
+            uint64_t q = 0;
+            for (uint32_t i = 0; i < kBlockNodes; i++) q |= qbit(base + i) << i;
+            for (int c = 0; c < 4; c++) {
+                uint64_t bits = 0;
+                for (uint32_t i = 0; i < kBlockNodes && base + i < n; i++) bits |= (uint64_t)row_bit(idx, c, base + i) << i;
+                uint32_t* e = out->data() + b * 16 + c * 4;
+                e[0] = rank(c, base);
+                e[1] = (uint32_t)bits;
+                e[2] = (uint32_t)((bits >> 32) & 0xFFFF) | (uint32_t)((q & 0xFFFF) << 16);
+                e[3] = (uint32_t)(q >> 16);
+            }
+        }
+    });
+}
+
+void build_jump_table(const ntc_index& idx, std::vector<uint64_t>* out, int n_threads) {
+    const uint64_t n = idx.n;
+    // one inverse-LF step: pred[C[c] + j] = position of the j-th one of row c; in-label = c
+    std::vector<uint32_t> pred(n), tmp_p(n);
+    std::vector<uint32_t> chars(n), tmp_c(n);
+    pred[0] = 0;
+    chars[0] = 0;
+    for (int c = 0; c < 4; c++) {
+        uint64_t j = idx.C[c];
+        for (size_t w = 0; w < idx.rows[c].size(); w++) {
+            uint64_t x = idx.rows[c][w];
+            while (x) {
+                int b = __builtin_ctzll(x);
+                pred[j] = (uint32_t)(w * 64 + b);
+                chars[j] = (uint32_t)c;
+                j++;
+                x &= x - 1;
+            }
+        }
+    }
+    // pointer doubling: after the round with step t, pred = pred^(2t) and chars holds the last 2t
+    // bases with the LAST base in the TOP 2 bits of a 2*(2t)-bit field.
+    for (int t = 1; t < 16; t *= 2) {
+        parallel_chunks(n, 1 << 16, n_threads, [&](uint64_t lo, uint64_t hi) {
+            for (uint64_t v = lo; v < hi; v++) {
+                uint32_t u = pred[v];
+                tmp_p[v] = pred[u];
+                tmp_c[v] = (chars[v] << (2 * t)) | chars[u];  // earlier bases (from u) go below
+            }
+        });
+        pred.swap(tmp_p);
+        chars.swap(tmp_c);
+    }
+    out->resize(n);
+    parallel_chunks(n, 1 << 16, n_threads, [&](uint64_t lo, uint64_t hi) {
+        for (uint64_t v = lo; v < hi; v++) (*out)[v] = (uint64_t)pred[v] | ((uint64_t)chars[v] << 32);
+    });
+}
+
+}  // namespace ntc
+
+// ---------------------------------------------------------------------------------------------
+// C ABI: index management
+// ---------------------------------------------------------------------------------------------
+using namespace ntc;
+
+extern "C" {
+
+const char* ntc_last_error(void) { return ntc::last_error(); }
+const char* ntc_version(void) { return "ntcomp_b200 0.1 (sm_100a)"; }
+
+int32_t ntc_index_build(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n_seqs, uint32_t k, int32_t add_revcomp,
+                        int32_t n_threads, ntc_index** out) {
+    if (!out || (n_seqs && (!seqs || !lens))) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    *out = nullptr;
+    try {
+        return build_index(seqs, lens, n_seqs, k, add_revcomp != 0, n_threads, out);
+    } catch (const std::exception& e) {
+        set_error(std::string("index build failed: ") + e.what());
+        return NTC_ERR_INVALID_ARG;
+    }
+}
+
+int32_t ntc_index_from_arrays(uint32_t k, uint64_t n_sets, const uint64_t* row_a, const uint64_t* row_c, const uint64_t* row_g,
+                              const uint64_t* row_t, const uint8_t* lcs, ntc_index** out) {
+    if (!out || !row_a || !row_c || !row_g || !row_t || !lcs) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    *out = nullptr;
+    try {
+        ntc_index* idx = new ntc_index();
+        idx->k = k;
+        idx->n = n_sets;
+        const uint64_t words = (n_sets + 63) / 64;
+        const uint64_t* rows[4] = {row_a, row_c, row_g, row_t};
+        for (int c = 0; c < 4; c++) idx->rows[c].assign(rows[c], rows[c] + words);
+        idx->lcs.assign(lcs, lcs + n_sets);
+        int32_t rc = finalize_index(idx);
+        if (rc) { delete idx; return rc; }
+        *out = idx;
+        return NTC_OK;
+    } catch (const std::exception& e) {
+        set_error(e.what());
+        return NTC_ERR_INVALID_ARG;
+    }
+}
+
+static const char kMagic[8] = {'N', 'T', 'C', 'B', '2', '0', '0', '1'};
+
+int32_t ntc_index_save(const ntc_index* idx, const char* path) {
+    if (!idx || !path) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    FILE* f = fopen(path, "wb");
+    if (!f) { set_error(std::string("cannot open for writing: ") + path); return NTC_ERR_IO; }
+    uint64_t hdr[2] = {idx->k, idx->n};
+    bool ok = fwrite(kMagic, 1, 8, f) == 8 && fwrite(hdr, 8, 2, f) == 2;
+    const uint64_t words = (idx->n + 63) / 64;
+    for (int c = 0; c < 4 && ok; c++) ok = fwrite(idx->rows[c].data(), 8, words, f) == words;
+    ok = ok && fwrite(idx->lcs.data(), 1, idx->n, f) == idx->n;
+    ok = (fclose(f) == 0) && ok;
+    if (!ok) { set_error("short write"); return NTC_ERR_IO; }
+    return NTC_OK;
+}
+
+int32_t ntc_index_load(const char* path, ntc_index** out) {
+    if (!out || !path) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) { set_error(std::string("cannot open: ") + path); return NTC_ERR_IO; }
+    char magic[8];
+    uint64_t hdr[2];
+    if (fread(magic, 1, 8, f) != 8 || memcmp(magic, kMagic, 8) != 0 || fread(hdr, 8, 2, f) != 2 || hdr[1] == 0 ||
+        hdr[1] >= (1ull << 32)) {
+        fclose(f);
+        set_error("not an ntcomp_b200 index file");
+        return NTC_ERR_IO;
+    }
+    ntc_index* idx = new ntc_index();
+    idx->k = (uint32_t)hdr[0];
+    idx->n = hdr[1];
+    const uint64_t words = (idx->n + 63) / 64;
+    bool ok = true;
+    for (int c = 0; c < 4 && ok; c++) {
+        idx->rows[c].resize(words);
+        ok = fread(idx->rows[c].data(), 8, words, f) == words;
+    }
+    idx->lcs.resize(idx->n);
+    ok = ok && fread(idx->lcs.data(), 1, idx->n, f) == idx->n;
+    fclose(f);
+    if (!ok) { delete idx; set_error("truncated index file"); return NTC_ERR_IO; }
+    int32_t rc = finalize_index(idx);
+    if (rc) { delete idx; return rc; }
+    *out = idx;
+    return NTC_OK;
+}
+
+uint32_t ntc_index_k(const ntc_index* idx) { return idx ? idx->k : 0; }
+uint64_t ntc_index_n_sets(const ntc_index* idx) { return idx ? idx->n : 0; }
+void ntc_index_get_C(const ntc_index* idx, uint64_t out[5]) { memcpy(out, idx->C, 5 * sizeof(uint64_t)); }
+void ntc_index_get_row(const ntc_index* idx, int32_t c, uint64_t* out) {
+    memcpy(out, idx->rows[c].data(), ((idx->n + 63) / 64) * 8);
+}
+void ntc_index_get_lcs(const ntc_index* idx, uint8_t* out) { memcpy(out, idx->lcs.data(), idx->n); }
+void ntc_index_free(ntc_index* idx) { delete idx; }
+
+uint64_t ntc_encode_bound(uint64_t n_bases) { return n_bases; }
+
+}  // extern "C"

@@ -1,0 +1,43 @@
+// host_index.h -- host-side flat SBWT + LCS (the canonical arrays) and the derived HBM layouts.
+// Replaces sbwt::SbwtIndexVariant::SubsetMatrix + sbwt::LcsArray as used at src/lib.rs:20-22,170,263.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+struct ntc_index {
+    uint32_t k = 0;
+    uint64_t n = 0;                 // n_sets
+    std::vector<uint64_t> rows[4];  // n bits each, LSB-first, A,C,G,T
+    uint64_t C[5] = {0, 0, 0, 0, 0};
+    std::vector<uint8_t> lcs;       // n bytes
+};
+
+namespace ntc {
+
+constexpr uint32_t kMinK = 12;   // len <= 11 literals index kmer[k-len..k) (src/encode.rs:152): needs k >= 11;
+                                 // the decode jump table packs 16 bases, the bucketed builder uses 8
+constexpr uint32_t kMaxK = 255;  // d and LCS are stored in one byte
+constexpr uint32_t kBlockNodes = 48;  // nodes per 64-byte rank block
+
+void set_error(const std::string& msg);
+
+// recomputes C from rows and validates (edge count == n-1, k range, n < 2^32)
+int32_t finalize_index(ntc_index* idx);
+
+int32_t build_index(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n_seqs, uint32_t k, bool add_revcomp,
+                    int n_threads, ntc_index** out);
+
+// ---- derived device layouts (built on the host, uploaded by ntc_ctx_create) ----
+
+// Rank blocks: 64 bytes per 48 nodes = 4 x 16-byte entries (A,C,G,T), entry =
+//   u32 ones of this row before the block | 48 row bits | 48 Q bits
+// Q[v] = node v is alone in its (k-1)-suffix group  <=>  LCS[v] < k-1 and (v+1 == n or LCS[v+1] < k-1).
+// One rank probe = one aligned 16-byte load = one 32-byte L2 sector.
+void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out /* 16 u32 per block */, int n_threads);
+
+// Decode jump table: one u64 per node = pred^16(v) (low 32 bits) | last 16 bases of node v's k-mer
+// (high 32 bits, base at string position k-16+i in bits 2i..2i+1).  Root and '$' positions code 0.
+void build_jump_table(const ntc_index& idx, std::vector<uint64_t>* out, int n_threads);
+
+}  // namespace ntc

@@ -1,0 +1,249 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.
+Bar: bit-exact (integer / byte work).  P1 record stream, P3 decoded bytes + FASTA, P4 cross decode.
+"""
+import numpy as np
+import pytest
+
+import helpers
+import ntcomp_b200 as nt
+from ntcomp_b200 import synth
+from oracle import binding as ob
+
+pytestmark = pytest.mark.gpu
+
+
+class Case:
+    def __init__(self, contigs, k, add_revcomp=True):
+        self.contigs = contigs
+        self.k = k
+        self.index = nt.Index.build(contigs, k, add_revcomp)
+        self.oracle = ob.OracleIndex.from_arrays(k, self.index.n_sets, self.index.rows(), self.index.lcs())
+        self.ctx = nt.Context(self.index, 0)
+
+
+@pytest.fixture(scope="module")
+def small_cases():
+    rng = np.random.default_rng(11)
+    cases = []
+    for k, sizes in [(12, [400, 90]), (16, [3000]), (31, [20000, 500, 31, 30]), (91, [30000, 2000]), (255, [1500, 900, 300])]:
+        cases.append(Case([helpers.random_seq(rng, n) for n in sizes], k))
+    return cases
+
+
+def _reads_for(rng, case, n):
+    k = case.k
+    reads = helpers.sample_reads(rng, [c for c in case.contigs if len(c) > 0], n,
+                                 lengths=[1, 2, 5, k - 1, k, k + 1, k + 2, 2 * k, 3 * k + 7, 150, 150, 150, 400, 1000],
+                                 error_rates=[0, 0, 0.01, 0.01, 0.05, 0.3], k=k)
+    reads += [np.ascontiguousarray(c) for c in case.contigs if len(c) > 0]            # the contigs themselves (C1 style)
+    reads += [helpers.random_seq(rng, 200), helpers.random_seq(rng, 7)]                # unrelated sequence
+    return reads
+
+
+def test_matching_statistics_parity(small_cases):
+    rng = np.random.default_rng(5)
+    for case in small_cases:
+        reads = _reads_for(rng, case, 200)
+        bases, off = nt.concat_reads(reads)
+        d, s = case.ctx.matching_statistics(bases, off)
+        for i, r in enumerate(reads):
+            od, os_, _ = case.oracle.matching_statistics(r)
+            lo, hi = int(off[i]), int(off[i + 1])
+            assert (d[lo:hi] == od).all(), (case.k, i)
+            assert (s[lo:hi] == os_).all(), (case.k, i)
+
+
+def test_encode_records_parity_literal_oracle(small_cases):
+    """P1 against the literal restatement (4 x search left extension, access_kmer literals)."""
+    rng = np.random.default_rng(6)
+    for case in small_cases:
+        reads = _reads_for(rng, case, 150)
+        bases, off = nt.concat_reads(reads)
+        rec, roff = case.ctx.encode_batch(bases, off)
+        orec, oroff = case.oracle.encode_reads(bases, off, fast=False, threads=8)
+        assert (roff == oroff).all(), case.k
+        assert (rec == orec).all(), case.k
+
+
+def test_encode_sequence_triples_and_dictionary(small_cases):
+    rng = np.random.default_rng(7)
+    for case in small_cases:
+        reads = _reads_for(rng, case, 40)
+        for r in reads:
+            got = nt.encode_sequence(r, case.ctx)
+            want = case.oracle.encode_sequence(r, fast=False)
+            assert [(ln, (rg.start, rg.stop)) for ln, rg in got] == want, case.k
+            words = nt.encode_dictionary(got, case.ctx)
+            assert (words == case.oracle.encode_dictionary(want)).all()
+
+
+def test_decode_parity_and_roundtrip(small_cases):
+    rng = np.random.default_rng(8)
+    for case in small_cases:
+        reads = _reads_for(rng, case, 150)
+        bases, off = nt.concat_reads(reads)
+        rec, _ = case.ctx.encode_batch(bases, off)
+        db, doff = case.ctx.decode_batch(rec)
+        ob_, ooff = case.oracle.decode(rec, fast=False)          # literal decode_sequence
+        assert (doff == ooff).all() and (db == ob_).all(), case.k
+        assert (doff == off).all() and (db == bases).all(), case.k
+        seqs = nt.decode_sequence(rec, case.ctx)
+        assert seqs == [bytes(r) for r in reads]
+        # P4: oracle-encoded stream through the GPU decoder
+        orec, _ = case.oracle.encode_reads(bases, off, fast=True, threads=8)
+        db2, doff2 = case.ctx.decode_batch(orec)
+        assert (db2 == bases).all() and (doff2 == off).all()
+
+
+def test_decode_fasta_text(small_cases):
+    rng = np.random.default_rng(9)
+    case = small_cases[2]
+    reads = _reads_for(rng, case, 120)
+    bases, off = nt.concat_reads(reads)
+    rec, _ = case.ctx.encode_batch(bases, off)
+    for first in (1, 9, 98, 65530, 99999999):
+        text, n_seqs = case.ctx.decode_fasta(rec, first)
+        assert n_seqs == len(reads)
+        assert text == helpers.fasta_text(reads, first)
+
+
+def test_decode_drops_records_before_first_flag(small_cases):
+    case = small_cases[2]
+    rng = np.random.default_rng(10)
+    reads = _reads_for(rng, case, 20)
+    bases, off = nt.concat_reads(reads)
+    rec, roff = case.ctx.encode_batch(bases, off)
+    cut = rec[int(roff[3]) + 1:]                     # starts in the middle of read 3's records
+    db, doff = case.ctx.decode_batch(cut)
+    ob_, ooff = case.oracle.decode(cut, fast=False)
+    assert (doff == ooff).all() and (db == ob_).all()
+    assert len(doff) - 1 == len(reads) - 4
+    empty_b, empty_off = case.ctx.decode_batch(np.zeros(0, dtype=np.uint64))
+    assert len(empty_b) == 0 and list(empty_off) == [0]
+
+
+def test_fixture_c1_shape_roundtrip():
+    """BASELINE config #1: tests/fasta_data.rs shape (7 contigs < 2000 bp, k = 255, block size 3)."""
+    contigs, k, block = helpers.fixture_c1()
+    case = Case(contigs, k)
+    decoded = []
+    for b in range(0, len(contigs), block):
+        bases, off = nt.concat_reads(contigs[b:b + block])
+        rec, _ = case.ctx.encode_batch(bases, off)
+        orec, _ = case.oracle.encode_reads(bases, off, fast=False)
+        assert (rec == orec).all()
+        blob = ob.write_block(rec, min(block, len(contigs) - b))   # host container stays the reference's (oracle restatement here)
+        if blob is None:
+            decoded += nt.decode_sequence(rec, case.ctx)            # Q4: block the reference would drop
+            continue
+        rec2, _, _ = ob.read_block(blob)
+        assert (rec2 == rec).all()
+        decoded += nt.decode_sequence(rec2, case.ctx)
+    assert decoded == [bytes(c) for c in contigs]                    # fasta_data.rs:93,99
+    assert sum(map(len, decoded)) == sum(map(len, contigs))          # fasta_data.rs:100
+
+
+def test_error_codes(small_cases):
+    case = small_cases[2]
+    good = bytes(case.contigs[0][:100])
+    with pytest.raises(nt.EncodeError):
+        nt.encode_sequence(b"", case.ctx)                            # lib.rs:224
+    with pytest.raises(nt.NtcError) as e:
+        case.ctx.encode_batch(*nt.concat_reads([good, b"ACGTNACGT"]))
+    assert e.value.code == 5                                         # NTC_ERR_BAD_BASE (Q3)
+    with pytest.raises(nt.NtcError) as e:
+        case.ctx.encode_batch(*nt.concat_reads([good, b"", good]))
+    assert e.value.code == 4
+    bases, off = nt.concat_reads([good] * 8)
+    with pytest.raises(nt.NtcError) as e:
+        case.ctx.encode_batch(bases, off, cap=3)
+    assert e.value.code == 3
+    # the context stays usable after an error
+    rec, _ = case.ctx.encode_batch(bases, off)
+    assert nt.decode_sequence(rec, case.ctx) == [good] * 8
+    bad = np.array([(case.index.n_sets + 5) | (20 << 32) | (1 << 56)], dtype=np.uint64)
+    with pytest.raises(nt.NtcError) as e:
+        case.ctx.decode_batch(bad)
+    assert e.value.code == 8
+
+
+def test_index_with_missing_base_flags_absent_base():
+    """d == 0: the reference underflows at lib.rs:207; the ABI reports NTC_ERR_BAD_BASE."""
+    contig = np.frombuffer(b"ACACACCACAACCCACACAAACCACACCA" * 4, dtype=np.uint8)
+    case = Case([contig], 12, add_revcomp=False)                    # index holds only A and C
+    with pytest.raises(nt.NtcError) as e:
+        case.ctx.encode_batch(*nt.concat_reads([b"ACACACCACAACCCAGACAAACC"]))
+    assert e.value.code == 5
+    with pytest.raises(ob.OracleError) as oe:
+        case.oracle.encode_sequence(b"ACACACCACAACCCAGACAAACC")
+    assert oe.value.code == -3
+
+
+def test_chunked_host_path_matches_unchunked(monkeypatch, small_cases):
+    case0 = small_cases[3]
+    rng = np.random.default_rng(12)
+    reads = _reads_for(rng, case0, 300)
+    bases, off = nt.concat_reads(reads)
+    rec, roff = case0.ctx.encode_batch(bases, off)
+    monkeypatch.setenv("NTC_MAX_CHUNK_BASES", "4096")
+    ctx2 = nt.Context(case0.index, 0)
+    rec2, roff2 = ctx2.encode_batch(bases, off)
+    assert (rec == rec2).all() and (roff == roff2).all()
+    tri, _ = case0.ctx.encode_sequence_batch(bases, off)
+    tri2, _ = ctx2.encode_sequence_batch(bases, off)
+    assert (tri == tri2).all()
+
+
+@pytest.mark.parametrize("cfg", ["C2-small", "C3-small", "C5-small"])
+def test_synthetic_config_shapes(cfg):
+    """BASELINE configs at reduced genome/read counts: oracle parity on a sample + full round trip."""
+    shape = {"C2-small": dict(genome=200_000, k=31, n_reads=20_000, read_len=150, err_ppm=10_000),
+             "C3-small": dict(genome=200_000, k=91, n_reads=20_000, read_len=150, err_ppm=10_000),
+             "C5-small": dict(genome=200_000, k=91, n_reads=60, read_len=10_000, err_ppm=50_000)}[cfg]
+    g = synth.genome(shape["genome"])
+    case = Case([g], shape["k"])
+    bases, off = synth.reads(g, 777, 0, shape["n_reads"], shape["read_len"], shape["err_ppm"])
+    rec, roff = case.ctx.encode_batch(bases, off)
+    n_check = min(shape["n_reads"], 3000)
+    orec, oroff = case.oracle.encode_reads(bases[: int(off[n_check])], off[: n_check + 1], fast=True, threads=8)
+    assert (roff[: n_check + 1] == oroff).all()
+    assert (rec[: int(roff[n_check])] == orec).all()
+    n_lit = min(shape["n_reads"], 40)
+    lrec, _ = case.oracle.encode_reads(bases[: int(off[n_lit])], off[: n_lit + 1], fast=False, threads=8)
+    assert (rec[: int(roff[n_lit])] == lrec).all()
+    db, doff = case.ctx.decode_batch(rec)
+    assert (doff == off).all() and (db == bases).all()
+    text, n_seqs = case.ctx.decode_fasta(rec, 1)
+    assert n_seqs == shape["n_reads"]
+    head = helpers.fasta_text([bases[int(off[i]): int(off[i + 1])] for i in range(50)], 1)
+    assert text[: len(head)] == head
+
+
+def test_device_resident_api_with_torch(small_cases):
+    import torch
+    case = small_cases[3]
+    rng = np.random.default_rng(13)
+    reads = _reads_for(rng, case, 200)
+    bases, off = nt.concat_reads(reads)
+    dev = torch.device("cuda:0")
+    d_bases = torch.from_numpy(bases).to(dev)
+    d_off = torch.from_numpy(off.astype(np.int64)).to(dev)
+    cap = len(bases)
+    d_rec = torch.zeros(cap, dtype=torch.int64, device=dev)
+    d_roff = torch.zeros(len(reads) + 1, dtype=torch.int64, device=dev)
+    d_cnt = torch.zeros(4, dtype=torch.int64, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    case.ctx.encode_device(d_bases.data_ptr(), d_off.data_ptr(), len(reads), len(bases), d_rec.data_ptr(), cap, d_roff.data_ptr(),
+                           d_cnt.data_ptr(), stream)
+    case.ctx.status(stream)
+    n_rec = int(d_cnt[0].item())
+    rec = d_rec[:n_rec].cpu().numpy().view(np.uint64)
+    orec, oroff = case.oracle.encode_reads(bases, off, fast=True, threads=8)
+    assert (rec == orec).all() and (d_roff.cpu().numpy().view(np.uint64) == oroff).all()
+    d_out = torch.zeros(len(bases) + 64, dtype=torch.uint8, device=dev)
+    d_soff = torch.zeros(len(reads) + 1, dtype=torch.int64, device=dev)
+    case.ctx.decode_device(d_rec.data_ptr(), n_rec, 1, False, d_out.data_ptr(), len(bases), d_soff.data_ptr(), len(reads), d_cnt.data_ptr(), stream)
+    case.ctx.status(stream)
+    assert int(d_cnt[0].item()) == len(reads) and int(d_cnt[1].item()) == len(bases)
+    assert (d_out[: len(bases)].cpu().numpy() == bases).all()
+    assert (d_soff.cpu().numpy().view(np.uint64) == off).all()
