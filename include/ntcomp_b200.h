@@ -125,6 +125,16 @@ int32_t ntc_ctx_status(ntc_ctx* ctx, void* stream);
 /* number of kernels this library launched on ctx since creation (bench.py's gpu_launches) */
 uint64_t ntc_ctx_launch_count(const ntc_ctx* ctx);
 
+/* measurement support (bench.py): per-kernel-class CUDA-event timing on the launching stream.
+ * classes: 0 pack2bit, 1 matching statistics, 2 record-offset scan, 3 emit, 4 decode scan,
+ * 5 sequence offsets, 6 walk, 7 misc.  ntc_ctx_kernel_times synchronises the device. */
+#define NTC_KERNEL_CLASSES 8
+int32_t ntc_ctx_set_profiling(ntc_ctx* ctx, int32_t on);
+int32_t ntc_ctx_kernel_times(ntc_ctx* ctx, double* ms /*[8]*/, uint64_t* launches /*[8]*/, int32_t reset);
+/* L2 random 32-byte-sector micro-benchmark: G sectors/s from a buffer of the given size */
+int32_t ntc_l2_random_bench(ntc_ctx* ctx, uint64_t buffer_bytes, uint32_t loads_per_thread, int32_t dependent,
+                            uint32_t n_blocks, double* gsectors_per_s);
+
 /* matching statistics only (diagnostic / parity entry point for StreamingIndex::matching_statistics,
  * src/lib.rs:172-173): per base d (u8) and interval start (u32).  HOST buffers. */
 int32_t ntc_matching_statistics(ntc_ctx* ctx, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads,

@@ -141,6 +141,23 @@ class Context:
         _lib.lib().ntc_ctx_index_bytes(self._h, _ptr(out))
         return {"rank": int(out[0]), "lcs": int(out[1]), "jump": int(out[2])}
 
+    KERNEL_CLASSES = ["pack2bit", "ms", "scan", "emit", "decode_scan", "seq_offsets", "walk", "misc"]
+
+    def set_profiling(self, on=True):
+        check(_lib.lib().ntc_ctx_set_profiling(self._h, int(on)))
+
+    def kernel_times(self, reset=True):
+        """{class: (ms, launches)} from CUDA events on the launching stream (synchronises)"""
+        ms = np.zeros(8, dtype=np.float64)
+        ln = np.zeros(8, dtype=np.uint64)
+        check(_lib.lib().ntc_ctx_kernel_times(self._h, _ptr(ms), _ptr(ln), int(reset)))
+        return {n: (float(ms[i]), int(ln[i])) for i, n in enumerate(self.KERNEL_CLASSES)}
+
+    def l2_random_bench(self, buffer_bytes, loads_per_thread=256, dependent=False, n_blocks=148 * 8 * 4):
+        out = C.c_double(0)
+        check(_lib.lib().ntc_l2_random_bench(self._h, buffer_bytes, loads_per_thread, int(dependent), n_blocks, C.byref(out)))
+        return out.value
+
     def launch_count(self):
         return int(_lib.lib().ntc_ctx_launch_count(self._h))
 

@@ -24,6 +24,25 @@ struct CountLoad {
 
 inline unsigned blocks_for(uint64_t n, unsigned per) { return (unsigned)((n + per - 1) / per); }
 
+// Brackets the launches of one kernel class with CUDA events on the launching stream when
+// profiling is on; always counts launches.
+struct Timed {
+    ntc_ctx* ctx; int cls; cudaStream_t st; cudaEvent_t e0 = nullptr, e1 = nullptr;
+    Timed(ntc_ctx* c, int k, cudaStream_t s, int n_launches = 1) : ctx(c), cls(k), st(s) {
+        ctx->launches += n_launches;
+        ctx->class_launches[cls] += n_launches;
+        if (!ctx->profiling) return;
+        auto get = [&]() { cudaEvent_t e; if (ctx->event_pool.empty()) cudaEventCreate(&e); else { e = ctx->event_pool.back(); ctx->event_pool.pop_back(); } return e; };
+        e0 = get(); e1 = get();
+        cudaEventRecord(e0, st);
+    }
+    ~Timed() {
+        if (!e0) return;
+        cudaEventRecord(e1, st);
+        ctx->spans.push_back(ntc_ctx::Span{cls, e0, e1});
+    }
+};
+
 __global__ void copy_totals_kernel(const uint64_t* totals, uint64_t* counts) {
     counts[0] = totals[0];
     counts[1] = totals[0] * 8;
@@ -77,21 +96,28 @@ int32_t encode_pipeline(ntc_ctx* ctx, int mode, const uint8_t* d_bases, const ui
     uint32_t* counts = (uint32_t*)ctx->counts.p;
 
     if (n_bases) {
+        Timed t(ctx, KC_PACK, st);
         pack2bit_kernel<<<blocks_for((n_bases + 31) / 32, kPackThreads), kPackThreads, 0, st>>>(d_bases, d_offsets, n_bases, packed,
                                                                                                 ctx->d_status);
-        ctx->launches++;
     }
-    ms_kernel<<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                      ctx->d_status);
-    ctx->launches++;
-    ctx->launches += exclusive_scan_pairs(CountLoad{counts}, n_reads, (Pair64*)ctx->tiles.p, carry, totals_out, rec_off, nullptr, st);
-    if (mode == 0)
-        emit_kernel<0><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                               rec_off, d_out, cap, ctx->d_status);
-    else
-        emit_kernel<1><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                               rec_off, d_out, cap, ctx->d_status);
-    ctx->launches++;
+    {
+        Timed t(ctx, KC_MS, st);
+        ms_kernel<<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
+                                                                          ctx->d_status);
+    }
+    {
+        Timed t(ctx, KC_SCAN, st, 3);
+        exclusive_scan_pairs(CountLoad{counts}, n_reads, (Pair64*)ctx->tiles.p, carry, totals_out, rec_off, nullptr, st);
+    }
+    {
+        Timed t(ctx, KC_EMIT, st);
+        if (mode == 0)
+            emit_kernel<0><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
+                                                                                   rec_off, d_out, cap, ctx->d_status);
+        else
+            emit_kernel<1><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
+                                                                                   rec_off, d_out, cap, ctx->d_status);
+    }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
 }
@@ -114,13 +140,21 @@ int32_t decode_pipeline(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec,
     uint64_t* seq_idx = (uint64_t*)ctx->seq_idx.p;
     uint64_t* seq_first = (uint64_t*)ctx->seq_first.p;
     uint64_t* totals = ctx->d_totals + 4;
-    ctx->launches += exclusive_scan_pairs(RecordLoad{d_records}, n_rec, (Pair64*)ctx->tiles.p, nullptr, totals, base_off, seq_idx, st);
-    seq_starts_kernel<<<blocks_for(n_rec, 256), 256, 0, st>>>(d_records, n_rec, seq_idx, seq_first);
-    seq_offsets_kernel<<<blocks_for(n_rec + 1, 256), 256, 0, st>>>(base_off, seq_first, totals, n_rec, d_seq_offsets, cap_seqs, first_no,
-                                                                   fasta, cap, d_counts, ctx->d_status);
-    walk_kernel<<<blocks_for(n_rec, 128), 128, 0, st>>>(ctx->dix, d_records, n_rec, base_off, seq_idx, seq_first, totals, first_no, fasta,
-                                                        d_out, cap, d_counts, ctx->d_status);
-    ctx->launches += 3;
+    {
+        Timed t(ctx, KC_DSCAN, st, 3);
+        exclusive_scan_pairs(RecordLoad{d_records}, n_rec, (Pair64*)ctx->tiles.p, nullptr, totals, base_off, seq_idx, st);
+    }
+    {
+        Timed t(ctx, KC_SEQ, st, 2);
+        seq_starts_kernel<<<blocks_for(n_rec, 256), 256, 0, st>>>(d_records, n_rec, seq_idx, seq_first);
+        seq_offsets_kernel<<<blocks_for(n_rec + 1, 256), 256, 0, st>>>(base_off, seq_first, totals, n_rec, d_seq_offsets, cap_seqs, first_no,
+                                                                       fasta, cap, d_counts, ctx->d_status);
+    }
+    {
+        Timed t(ctx, KC_WALK, st);
+        walk_kernel<<<blocks_for(n_rec, 128), 128, 0, st>>>(ctx->dix, d_records, n_rec, base_off, seq_idx, seq_first, totals, first_no, fasta,
+                                                            d_out, cap, d_counts, ctx->d_status);
+    }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
 }
@@ -223,7 +257,7 @@ int32_t ntc_encode_device(ntc_ctx* ctx, const uint8_t* d_bases, const uint64_t* 
     cudaStream_t st = (cudaStream_t)stream;
     int32_t rc = encode_pipeline(ctx, 0, d_bases, d_offsets, n_reads, n_bases, d_records, cap, d_rec_offsets, nullptr, ctx->d_totals, st);
     if (rc) return rc;
-    if (d_counts) { copy_totals_kernel<<<1, 1, 0, st>>>(ctx->d_totals, d_counts); ctx->launches++; }
+    if (d_counts) { Timed t(ctx, KC_MISC, st); copy_totals_kernel<<<1, 1, 0, st>>>(ctx->d_totals, d_counts); }
     return NTC_OK;
 }
 
@@ -247,6 +281,98 @@ int32_t ntc_synth_reads_device(ntc_ctx* ctx, const uint8_t* d_genome, uint64_t g
     return NTC_OK;
 }
 
+// ---------------- measurement support ----------------
+
+int32_t ntc_ctx_set_profiling(ntc_ctx* ctx, int32_t on) {
+    if (!ctx) { set_error("null ctx"); return NTC_ERR_INVALID_ARG; }
+    ctx->profiling = on != 0;
+    return NTC_OK;
+}
+
+// Synchronises the device, folds the recorded event spans into per-class totals and returns them:
+// ms[KC_COUNT] accumulated milliseconds, launches[KC_COUNT] kernel launches; reset != 0 clears.
+int32_t ntc_ctx_kernel_times(ntc_ctx* ctx, double* ms, uint64_t* launches, int32_t reset) {
+    if (!ctx) { set_error("null ctx"); return NTC_ERR_INVALID_ARG; }
+    NTC_CUDA_TRY(cudaSetDevice(ctx->device));
+    NTC_CUDA_TRY(cudaDeviceSynchronize());
+    for (auto& sp : ctx->spans) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, sp.e0, sp.e1) == cudaSuccess) ctx->class_ms[sp.cls] += t;
+        ctx->event_pool.push_back(sp.e0);
+        ctx->event_pool.push_back(sp.e1);
+    }
+    ctx->spans.clear();
+    for (int i = 0; i < KC_COUNT; i++) {
+        if (ms) ms[i] = ctx->class_ms[i];
+        if (launches) launches[i] = ctx->class_launches[i];
+        if (reset) { ctx->class_ms[i] = 0; ctx->class_launches[i] = 0; }
+    }
+    return NTC_OK;
+}
+
 }  // extern "C"
+
+// L2 random-sector micro-benchmark: every thread issues `loads` aligned 16-byte loads
+// (one 32-byte sector each) at pseudo-random offsets of an L2-resident buffer.  dependent == 0:
+// addresses come from a counter hash (independent, 8 in flight per thread); dependent != 0: each
+// address depends on the previous load (pointer chase, the access pattern of a rank chain).
+namespace {
+template <int DEP>
+__global__ void __launch_bounds__(256) l2_probe_kernel(const uint4* __restrict__ buf, uint32_t mask, uint32_t loads, uint32_t* sink) {
+    uint32_t tid = blockIdx.x * 256 + threadIdx.x;
+    uint32_t acc = 0;
+    if (DEP) {
+        uint32_t x = tid * 2654435761u;
+        for (uint32_t i = 0; i < loads; i++) {
+            uint4 v = __ldg(buf + (x & mask));
+            x = x * 1664525u + 1013904223u + v.x;
+            acc += v.y;
+        }
+        acc += x;
+    } else {
+        for (uint32_t i = 0; i < loads; i += 8) {
+            uint4 v[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                uint64_t h = ntc::splitmix64(((uint64_t)tid << 32) | (i + j));
+                v[j] = __ldg(buf + ((uint32_t)h & mask));
+            }
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc += v[j].x;
+        }
+    }
+    if (acc == 0x12345678u) *sink = acc;
+}
+}  // namespace
+
+extern "C" int32_t ntc_l2_random_bench(ntc_ctx* ctx, uint64_t buffer_bytes, uint32_t loads_per_thread, int32_t dependent,
+                                       uint32_t n_blocks, double* gsectors_per_s) {
+    if (!ctx || !gsectors_per_s || buffer_bytes < 4096) { set_error("bad argument"); return NTC_ERR_INVALID_ARG; }
+    NTC_CUDA_TRY(cudaSetDevice(ctx->device));
+    uint64_t entries = 1;
+    while (entries * 2 * 16 <= buffer_bytes) entries *= 2;
+    DevBuf buf;
+    NTC_CUDA_TRY(ensure(&buf, entries * 16));
+    NTC_CUDA_TRY(cudaMemset(buf.p, 1, entries * 16));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    loads_per_thread = (loads_per_thread + 7) / 8 * 8;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {
+        cudaEventRecord(e0, ctx->stream);
+        if (dependent) l2_probe_kernel<1><<<n_blocks, 256, 0, ctx->stream>>>((const uint4*)buf.p, (uint32_t)(entries - 1), loads_per_thread, ctx->d_status + 2);
+        else l2_probe_kernel<0><<<n_blocks, 256, 0, ctx->stream>>>((const uint4*)buf.p, (uint32_t)(entries - 1), loads_per_thread, ctx->d_status + 2);
+        cudaEventRecord(e1, ctx->stream);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (rep > 0) best = std::min(best, ms);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    release(&buf);
+    NTC_CUDA_TRY(cudaGetLastError());
+    *gsectors_per_s = (double)n_blocks * 256.0 * loads_per_thread / (best * 1e-3) / 1e9;
+    return NTC_OK;
+}
 
 #include "api_host.inc"

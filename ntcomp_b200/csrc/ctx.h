@@ -4,12 +4,16 @@
 
 #include <cstdint>
 #include <string>
+#include <vector>
 
 #include "device_common.cuh"
 #include "scan.cuh"
 
 namespace ntc {
 void set_error(const std::string& msg);
+
+// kernel classes for launch accounting / profiling
+enum KernelClass { KC_PACK = 0, KC_MS, KC_SCAN, KC_EMIT, KC_DSCAN, KC_SEQ, KC_WALK, KC_MISC, KC_COUNT };
 
 struct DevBuf {
     void* p = nullptr;
@@ -45,6 +49,14 @@ struct ntc_ctx {
     // staging for the host-buffer API
     ntc::DevBuf st_in, st_off, st_out, st_out2;
     cudaStream_t stream = nullptr;  // internal stream of the host-buffer API
+
+    // optional per-kernel-class timing with CUDA events on the launching stream (bench.py roofline)
+    bool profiling = false;
+    struct Span { int cls; cudaEvent_t e0, e1; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> event_pool;
+    double class_ms[ntc::KC_COUNT] = {0};
+    uint64_t class_launches[ntc::KC_COUNT] = {0};
 };
 
 namespace ntc {

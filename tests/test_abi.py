@@ -1,0 +1,65 @@
+"""The C-ABI library loads, exports every symbol include/ntcomp_b200.h declares, and refuses to
+compute without a GPU (no CPU fallback)."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import ntcomp_b200 as nt
+from ntcomp_b200 import _lib
+from conftest import ROOT, has_gpu
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "ntcomp_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ntc_[A-Za-z0-9_]+)\s*\(", text)))
+
+
+def test_every_declared_symbol_is_exported_and_bound():
+    L = _lib.lib()
+    names = _declared_symbols()
+    assert len(names) >= 25
+    for n in names:
+        assert hasattr(L, n), "libntcomp_b200.so does not export %s" % n
+        assert n in _lib.SIGNATURES, "%s has no ctypes prototype" % n
+    assert sorted(_lib.SIGNATURES) == names
+    assert b"sm_100a" in L.ntc_version()
+
+
+def test_library_holds_sm100a_code_only():
+    import subprocess
+    out = subprocess.run(["cuobjdump", "-lelf", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_\d+a?", out))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_product_does_not_link_or_import_the_oracle():
+    import subprocess
+    out = subprocess.run(["ldd", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in out
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "ntcomp_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".inc")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.replace("the oracle", "").replace("or the oracle", "") or f in ("synth.py", "synth_common.h"), f
+
+
+@pytest.mark.skipif(has_gpu(), reason="CPU-only behaviour")
+def test_fails_loudly_without_gpu():
+    g = np.frombuffer(b"ACGTTGCATGCATGCAGTCAGTCATGCATGCATGCAGTACGTAGCTAGCTAGCTAGCATG" * 4, dtype=np.uint8)
+    idx = nt.Index.build([g], 16)
+    with pytest.raises(nt.NtcError) as e:
+        nt.Context(idx, 0)
+    assert e.value.code == 2 and "no CPU fallback" in str(e.value)
+
+
+def test_bounds_helpers():
+    L = _lib.lib()
+    assert L.ntc_encode_bound(1234) == 1234
+    rec = np.array([(5 | (20 << 32) | (1 << 56)), (3 << 2 | 2) << 56, (7 | (12 << 32) | (1 << 56))], dtype=np.uint64)
+    ctxless = nt.Context.__new__(nt.Context)
+    nb, ns, fb = nt.Context.decode_bound(ctxless, rec, 9)
+    assert (nb, ns) == (35, 2)
+    assert fb == 35 + len(b">seq.9\n\n") + len(b">seq.10\n\n")
