@@ -19,7 +19,7 @@ namespace {
 
 struct CountLoad {
     const uint32_t* c;
-    __device__ __forceinline__ Pair64 operator()(uint64_t i) const { return Pair64{c[i], 0}; }
+    NTC_HD Pair64 operator()(uint64_t i) const { return Pair64{c[i], 0}; }
 };
 
 inline unsigned blocks_for(uint64_t n, unsigned per) { return (unsigned)((n + per - 1) / per); }

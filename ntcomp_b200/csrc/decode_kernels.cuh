@@ -4,23 +4,24 @@
 // Every reference record is a plain backward walk from its colex rank: access_kmer's
 // k selects and left_extend_kmer2's 4 x search per extended base collapse into inverse-LF steps,
 // and the jump table takes 16 of those steps per 8-byte load (pred^16 | last 16 bases).
+// Kernel bodies are per-thread NTC_HD functions (`*_thread`) so tests/emul can run them on the CPU.
 #pragma once
 #include "device_common.cuh"
 #include "scan.cuh"
 
 namespace ntc {
 
-__device__ __forceinline__ uint32_t record_len(uint64_t w) {
+NTC_HD uint32_t record_len(uint64_t w) {
     uint32_t flag = (uint32_t)(w >> 56);
     return (flag & 2u) ? (flag >> 2) : (uint32_t)(w >> 32) & 0xFFFFFFu;
 }
-__device__ __forceinline__ uint32_t record_first(uint64_t w) { return (uint32_t)(w >> 56) & 1u; }
+NTC_HD uint32_t record_first(uint64_t w) { return (uint32_t)(w >> 56) & 1u; }
 
 // scan input: a = bases of the record, b = 1 on the first record of a sequence
 struct RecordLoad {
     const uint64_t* rec;
-    __device__ __forceinline__ Pair64 operator()(uint64_t i) const {
-        uint64_t w = __ldg(rec + i);
+    NTC_HD Pair64 operator()(uint64_t i) const {
+        uint64_t w = NTC_LDG(rec + i);
         uint32_t L = record_len(w);
         if (((w >> 56) & 2u) && L > 32u) L = 0;  // bitnuc::from_2bit rejects > 32, result ignored (src/lib.rs:303)
         return Pair64{L, record_first(w)};
@@ -28,13 +29,13 @@ struct RecordLoad {
 };
 
 // number of decimal digits of x >= 1
-__device__ __forceinline__ uint32_t dec_digits(uint64_t x) {
+NTC_HD uint32_t dec_digits(uint64_t x) {
     uint32_t d = 1;
     while (x >= 10) { x /= 10; d++; }
     return d;
 }
 // sum of dec_digits(i) for i in [1, x]
-__device__ __forceinline__ uint64_t digits_prefix(uint64_t x) {
+NTC_HD uint64_t digits_prefix(uint64_t x) {
     uint64_t total = 0, lo = 1;
     uint32_t d = 1;
     while (lo <= x) {
@@ -49,51 +50,58 @@ __device__ __forceinline__ uint64_t digits_prefix(uint64_t x) {
 }
 // bytes of FASTA text before the bases of sequence `sid` (0-based in this batch), excluding bases:
 // headers ">seq.N\n" of sequences 0..sid and the '\n' closing sequences 0..sid-1
-__device__ __forceinline__ uint64_t fasta_overhead(uint64_t first_no, uint64_t sid) {
+NTC_HD uint64_t fasta_overhead(uint64_t first_no, uint64_t sid) {
     uint64_t digits = digits_prefix(first_no + sid) - digits_prefix(first_no - 1);
     return (sid + 1) * 6 + digits + sid;
 }
 
 // seq_first[j] = index of the record that opens sequence j; E_first gives its base offset
+NTC_HD void seq_starts_thread(const uint64_t* __restrict__ rec, uint64_t n_rec, const uint64_t* __restrict__ seq_idx,
+                              uint64_t* __restrict__ seq_first, uint64_t i) {
+    if (i >= n_rec) return;
+    if (record_first(NTC_LDG(rec + i))) seq_first[seq_idx[i]] = i;
+}
 __global__ void __launch_bounds__(256) seq_starts_kernel(const uint64_t* __restrict__ rec, uint64_t n_rec,
                                                          const uint64_t* __restrict__ seq_idx /* exclusive count of firsts */,
                                                          uint64_t* __restrict__ seq_first) {
-    uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
-    if (i >= n_rec) return;
-    if (record_first(__ldg(rec + i))) seq_first[seq_idx[i]] = i;
+    seq_starts_thread(rec, n_rec, seq_idx, seq_first, (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
 // seq_offsets[j] = bases before sequence j (relative to the first sequence), j in [0, n_seqs]
-__global__ void __launch_bounds__(256) seq_offsets_kernel(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
-                                                          const uint64_t* __restrict__ totals /* [bases, n_seqs] */, uint64_t n_rec,
-                                                          uint64_t* __restrict__ seq_offsets, uint64_t cap_seqs,
-                                                          uint64_t first_no, int fasta, uint64_t cap_bytes, uint64_t* __restrict__ counts,
-                                                          uint32_t* __restrict__ status) {
+NTC_HD void seq_offsets_thread(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
+                               const uint64_t* __restrict__ totals /* [bases, n_seqs] */, uint64_t n_rec,
+                               uint64_t* __restrict__ seq_offsets, uint64_t cap_seqs, uint64_t first_no, int fasta, uint64_t cap_bytes,
+                               uint64_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t j) {
     uint64_t n_seqs = totals[1];
-    uint64_t j = (uint64_t)blockIdx.x * 256 + threadIdx.x;
     uint64_t base0 = n_seqs ? base_off[seq_first[0]] : 0;
     if (j == 0) {
         uint64_t n_bases = n_seqs ? base_off[n_rec] - base0 : 0;
         uint64_t bytes = fasta ? (n_seqs ? n_bases + fasta_overhead(first_no, n_seqs - 1) + 1 : 0) : n_bases;
         counts[0] = n_seqs;
         counts[1] = bytes;
-        if (bytes > cap_bytes || (seq_offsets && n_seqs > cap_seqs)) atomicOr(status, ST_CAPACITY);
+        if (bytes > cap_bytes || (seq_offsets && n_seqs > cap_seqs)) NTC_ATOMIC_OR(status, (uint32_t)ST_CAPACITY);
     }
     if (!seq_offsets || j > n_seqs || j > cap_seqs) return;
     seq_offsets[j] = (j < n_seqs ? base_off[seq_first[j]] : base_off[n_rec]) - base0;
 }
+__global__ void __launch_bounds__(256) seq_offsets_kernel(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
+                                                          const uint64_t* __restrict__ totals, uint64_t n_rec,
+                                                          uint64_t* __restrict__ seq_offsets, uint64_t cap_seqs,
+                                                          uint64_t first_no, int fasta, uint64_t cap_bytes, uint64_t* __restrict__ counts,
+                                                          uint32_t* __restrict__ status) {
+    seq_offsets_thread(base_off, seq_first, totals, n_rec, seq_offsets, cap_seqs, first_no, fasta, cap_bytes, counts, status,
+                       (uint64_t)blockIdx.x * 256 + threadIdx.x);
+}
 
 // one thread per record: walk / unpack and store ASCII bases (and FASTA header + newline on the
 // record that opens a sequence)
-__global__ void __launch_bounds__(128) walk_kernel(DevIndex ix, const uint64_t* __restrict__ rec, uint64_t n_rec,
-                                                   const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_idx,
-                                                   const uint64_t* __restrict__ seq_first, const uint64_t* __restrict__ totals,
-                                                   uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes,
-                                                   const uint64_t* __restrict__ counts, uint32_t* __restrict__ status) {
-    uint64_t i = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, uint64_t n_rec, const uint64_t* __restrict__ base_off,
+                        const uint64_t* __restrict__ seq_idx, const uint64_t* __restrict__ seq_first, const uint64_t* __restrict__ totals,
+                        uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes, const uint64_t* __restrict__ counts,
+                        uint32_t* __restrict__ status, uint64_t i) {
     if (i >= n_rec) return;
     if (counts[1] > cap_bytes) return;  // capacity error already flagged
-    const uint64_t w = __ldg(rec + i);
+    const uint64_t w = NTC_LDG(rec + i);
     const uint32_t flag = (uint32_t)(w >> 56);
     const uint64_t n_seqs = totals[1];
     uint64_t incl = seq_idx[i] + (flag & 1u);  // sequences opened up to and including this record
@@ -126,17 +134,25 @@ __global__ void __launch_bounds__(128) walk_kernel(DevIndex ix, const uint64_t* 
         return;
     }
     uint32_t v = (uint32_t)w;
-    if (v >= ix.n) { atomicOr(status, ST_BAD_RECORD); return; }
+    if (v >= ix.n) { NTC_ATOMIC_OR(status, (uint32_t)ST_BAD_RECORD); return; }
     uint32_t remaining = L;
     while (remaining > 0) {
-        uint64_t ent = __ldg(ix.jump + v);
-        uint32_t t = min(remaining, 16u);
+        uint64_t ent = NTC_LDG(ix.jump + v);
+        uint32_t t = tmin(remaining, 16u);
         uint32_t chars = (uint32_t)(ent >> 32) >> (2 * (16 - t));  // last t bases, earliest in the low bits
         dst_end -= t;
         for (uint32_t q = 0; q < t; q++) dst_end[q] = (uint8_t)(0x54474341u >> (8 * ((chars >> (2 * q)) & 3u)));
         v = (uint32_t)ent;
         remaining -= t;
     }
+}
+__global__ void __launch_bounds__(128) walk_kernel(DevIndex ix, const uint64_t* __restrict__ rec, uint64_t n_rec,
+                                                   const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_idx,
+                                                   const uint64_t* __restrict__ seq_first, const uint64_t* __restrict__ totals,
+                                                   uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes,
+                                                   const uint64_t* __restrict__ counts, uint32_t* __restrict__ status) {
+    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_first, totals, first_no, fasta, out, cap_bytes, counts, status,
+                (uint64_t)blockIdx.x * 128 + threadIdx.x);
 }
 
 }  // namespace ntc

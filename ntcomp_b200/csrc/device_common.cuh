@@ -3,7 +3,24 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// Per-thread kernel bodies are __host__ __device__ so that tests/emul can run the very same code
+// on the CPU (one loop iteration per CUDA thread) before any GPU time is spent.  The product
+// library only ever launches them as kernels.
+#define NTC_HD __host__ __device__ __forceinline__
+#if defined(__CUDA_ARCH__)
+#define NTC_LDG(p) __ldg(p)
+#define NTC_POPCLL(x) __popcll(x)
+#define NTC_ATOMIC_OR(p, v) atomicOr((p), (v))
+#else
+#define NTC_LDG(p) (*(p))
+#define NTC_POPCLL(x) __builtin_popcountll(x)
+#define NTC_ATOMIC_OR(p, v) (*(p) |= (v))
+#endif
+
 namespace ntc {
+
+template <typename T> NTC_HD T tmin(T a, T b) { return a < b ? a : b; }
+template <typename T> NTC_HD T tmax(T a, T b) { return a > b ? a : b; }
 
 // status bits accumulated by kernels in ctx->d_status[0]
 enum : uint32_t {
@@ -28,43 +45,39 @@ struct DevIndex {
 // scratch entry written by the matching-statistics pass, one per base:
 //   bits 0-31 interval start, 32-39 d, 40-63 length of the run of "unique predecessor" positions
 //   ending here (replaces left_extend_kmer's 4 x search per base, src/lib.rs:94-128)
-__device__ __forceinline__ uint64_t make_entry(uint32_t s, uint32_t d, uint32_t urun) {
+NTC_HD uint64_t make_entry(uint32_t s, uint32_t d, uint32_t urun) {
     return (uint64_t)s | ((uint64_t)d << 32) | ((uint64_t)urun << 40);
 }
-__device__ __forceinline__ uint32_t entry_s(uint64_t e) { return (uint32_t)e; }
-__device__ __forceinline__ uint32_t entry_d(uint64_t e) { return (uint32_t)(e >> 32) & 0xFFu; }
-__device__ __forceinline__ uint32_t entry_urun(uint64_t e) { return (uint32_t)(e >> 40); }
+NTC_HD uint32_t entry_s(uint64_t e) { return (uint32_t)e; }
+NTC_HD uint32_t entry_d(uint64_t e) { return (uint32_t)(e >> 32) & 0xFFu; }
+NTC_HD uint32_t entry_urun(uint64_t e) { return (uint32_t)(e >> 40); }
 
 // ones of the entry's row in block-relative positions [0, off), off in [0, 48)
-__device__ __forceinline__ uint32_t entry_rank(const uint4& e, uint32_t off) {
+NTC_HD uint32_t entry_rank(const uint4& e, uint32_t off) {
     uint64_t bits = (uint64_t)e.y | ((uint64_t)(e.z & 0xFFFFu) << 32);
-    return e.x + (uint32_t)__popcll(bits & ((1ull << off) - 1ull));
+    return e.x + (uint32_t)NTC_POPCLL(bits & ((1ull << off) - 1ull));
 }
-__device__ __forceinline__ uint32_t entry_qbit(const uint4& e, uint32_t off) {
+NTC_HD uint32_t entry_qbit(const uint4& e, uint32_t off) {
     uint64_t q = (uint64_t)(e.z >> 16) | ((uint64_t)e.w << 16);
     return (uint32_t)(q >> off) & 1u;
 }
 
-__device__ __forceinline__ uint4 ldg_entry(const uint4* p) { return __ldg(p); }
+NTC_HD uint4 ldg_entry(const uint4* p) { return NTC_LDG(p); }
 
 // 2-bit base at chunk-relative position p of a packed stream (32 bases per u64, LSB first)
-__device__ __forceinline__ uint32_t packed_base(const uint64_t* __restrict__ packed, uint64_t p) {
-    return (uint32_t)(__ldg(packed + (p >> 5)) >> ((p & 31) * 2)) & 3u;
+NTC_HD uint32_t packed_base(const uint64_t* __restrict__ packed, uint64_t p) {
+    return (uint32_t)(NTC_LDG(packed + (p >> 5)) >> ((p & 31) * 2)) & 3u;
 }
 // up to 32 bases starting at position p, base j of the result at bits 2j..2j+1 (bitnuc as_2bit order)
-__device__ __forceinline__ uint64_t packed_slice(const uint64_t* __restrict__ packed, uint64_t p, uint32_t len) {
-    uint64_t w0 = __ldg(packed + (p >> 5));
+NTC_HD uint64_t packed_slice(const uint64_t* __restrict__ packed, uint64_t p, uint32_t len) {
+    uint64_t w0 = NTC_LDG(packed + (p >> 5));
     uint32_t sh = (uint32_t)(p & 31) * 2;
     uint64_t v = w0 >> sh;
-    if (sh && (p & 31) + len > 32) v |= __ldg(packed + (p >> 5) + 1) << (64 - sh);
+    if (sh && (p & 31) + len > 32) v |= NTC_LDG(packed + (p >> 5) + 1) << (64 - sh);
     return len >= 32 ? v : (v & ((1ull << (2 * len)) - 1ull));
 }
 
-// "ACGT"[code] for four 2-bit codes held in the low byte of x -> 4 ASCII bytes
-__device__ __forceinline__ uint32_t codes4_to_ascii(uint32_t x) {
-    // spread 2-bit codes into nibble selectors for PRMT over the table 'A','C','G','T'
-    uint32_t sel = (x & 3u) | ((x & 0xCu) << 2) | ((x & 0x30u) << 4) | ((x & 0xC0u) << 6);
-    return __byte_perm(0x54474341u, 0u, sel);
-}
+// ASCII of a 2-bit code
+NTC_HD uint8_t code_ascii(uint32_t c) { return (uint8_t)(0x54474341u >> (8 * (c & 3u))); }
 
 }  // namespace ntc

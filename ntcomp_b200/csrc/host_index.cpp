@@ -90,7 +90,7 @@ void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out, int n_t
                 uint64_t bits = 0;
                 for (uint32_t i = 0; i < kBlockNodes && base + i < n; i++) bits |= (uint64_t)row_bit(idx, c, base + i) << i;
                 uint32_t* e = out->data() + b * 16 + c * 4;
-                e[0] = rank(c, base);
+                e[0] = (uint32_t)idx.C[c] + rank(c, base);  // C[c] folded in: extend_right is entry count + popcount
                 e[1] = (uint32_t)bits;
                 e[2] = (uint32_t)((bits >> 32) & 0xFFFF) | (uint32_t)((q & 0xFFFF) << 16);
                 e[3] = (uint32_t)(q >> 16);

@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "device_common.cuh"
+
 namespace ntc {
 
 constexpr int kScanThreads = 256;
@@ -14,7 +16,7 @@ constexpr int kScanTile = kScanThreads * kScanItems;
 struct Pair64 {
     uint64_t a, b;
 };
-__device__ __forceinline__ Pair64 operator+(const Pair64& x, const Pair64& y) { return Pair64{x.a + y.a, x.b + y.b}; }
+NTC_HD Pair64 operator+(const Pair64& x, const Pair64& y) { return Pair64{x.a + y.a, x.b + y.b}; }
 
 __device__ __forceinline__ Pair64 warp_inclusive(Pair64 v, int lane) {
 #pragma unroll

@@ -1,5 +1,10 @@
-"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.
-Bar: bit-exact (integer / byte work).  P1 record stream, P3 decoded bytes + FASTA, P4 cross decode.
+"""Parity tests against the CPU oracle on the same inputs.  Bar: bit-exact (integer / byte work).
+P1 record stream, P3 decoded bytes + FASTA, P4 cross decode.
+
+Every case runs on two backends:
+  gpu   -- the CUDA path through the C ABI (ntcomp_b200.Context), marked `gpu`: the parity gate proper
+  emul  -- the same per-thread kernel bodies executed on the CPU (tests/emul), so kernel logic is
+           checked in the "not gpu" suite too.  The emulation is test infrastructure, not a fallback.
 """
 import numpy as np
 import pytest
@@ -9,24 +14,37 @@ import ntcomp_b200 as nt
 from ntcomp_b200 import synth
 from oracle import binding as ob
 
-pytestmark = pytest.mark.gpu
+BACKENDS = [pytest.param("emul"), pytest.param("gpu", marks=pytest.mark.gpu)]
+
+
+def make_ctx(backend, index):
+    if backend == "gpu":
+        return nt.Context(index, 0)
+    from emul_binding import EmulContext
+    return EmulContext(index)
 
 
 class Case:
-    def __init__(self, contigs, k, add_revcomp=True):
+    def __init__(self, backend, contigs, k, add_revcomp=True):
+        self.backend = backend
         self.contigs = contigs
         self.k = k
         self.index = nt.Index.build(contigs, k, add_revcomp)
         self.oracle = ob.OracleIndex.from_arrays(k, self.index.n_sets, self.index.rows(), self.index.lcs())
-        self.ctx = nt.Context(self.index, 0)
+        self.ctx = make_ctx(backend, self.index)
+
+
+@pytest.fixture(scope="module", params=BACKENDS)
+def backend(request):
+    return request.param
 
 
 @pytest.fixture(scope="module")
-def small_cases():
+def small_cases(backend):
     rng = np.random.default_rng(11)
     cases = []
     for k, sizes in [(12, [400, 90]), (16, [3000]), (31, [20000, 500, 31, 30]), (91, [30000, 2000]), (255, [1500, 900, 300])]:
-        cases.append(Case([helpers.random_seq(rng, n) for n in sizes], k))
+        cases.append(Case(backend, [helpers.random_seq(rng, n) for n in sizes], k))
     return cases
 
 
@@ -122,10 +140,10 @@ def test_decode_drops_records_before_first_flag(small_cases):
     assert len(empty_b) == 0 and list(empty_off) == [0]
 
 
-def test_fixture_c1_shape_roundtrip():
+def test_fixture_c1_shape_roundtrip(backend):
     """BASELINE config #1: tests/fasta_data.rs shape (7 contigs < 2000 bp, k = 255, block size 3)."""
     contigs, k, block = helpers.fixture_c1()
-    case = Case(contigs, k)
+    case = Case(backend, contigs, k)
     decoded = []
     for b in range(0, len(contigs), block):
         bases, off = nt.concat_reads(contigs[b:b + block])
@@ -167,10 +185,10 @@ def test_error_codes(small_cases):
     assert e.value.code == 8
 
 
-def test_index_with_missing_base_flags_absent_base():
+def test_index_with_missing_base_flags_absent_base(backend):
     """d == 0: the reference underflows at lib.rs:207; the ABI reports NTC_ERR_BAD_BASE."""
     contig = np.frombuffer(b"ACACACCACAACCCACACAAACCACACCA" * 4, dtype=np.uint8)
-    case = Case([contig], 12, add_revcomp=False)                    # index holds only A and C
+    case = Case(backend, [contig], 12, add_revcomp=False)                    # index holds only A and C
     with pytest.raises(nt.NtcError) as e:
         case.ctx.encode_batch(*nt.concat_reads([b"ACACACCACAACCCAGACAAACC"]))
     assert e.value.code == 5
@@ -179,7 +197,10 @@ def test_index_with_missing_base_flags_absent_base():
     assert oe.value.code == -3
 
 
+@pytest.mark.gpu
 def test_chunked_host_path_matches_unchunked(monkeypatch, small_cases):
+    if small_cases[0].backend != "gpu":
+        pytest.skip("host chunking lives in the C ABI")
     case0 = small_cases[3]
     rng = np.random.default_rng(12)
     reads = _reads_for(rng, case0, 300)
@@ -195,13 +216,15 @@ def test_chunked_host_path_matches_unchunked(monkeypatch, small_cases):
 
 
 @pytest.mark.parametrize("cfg", ["C2-small", "C3-small", "C5-small"])
-def test_synthetic_config_shapes(cfg):
+def test_synthetic_config_shapes(cfg, backend):
     """BASELINE configs at reduced genome/read counts: oracle parity on a sample + full round trip."""
     shape = {"C2-small": dict(genome=200_000, k=31, n_reads=20_000, read_len=150, err_ppm=10_000),
              "C3-small": dict(genome=200_000, k=91, n_reads=20_000, read_len=150, err_ppm=10_000),
              "C5-small": dict(genome=200_000, k=91, n_reads=60, read_len=10_000, err_ppm=50_000)}[cfg]
+    if backend == "emul":                      # the CPU emulation is ~1000x slower: shrink the batch
+        shape = dict(shape, n_reads=max(8, shape["n_reads"] // 40))
     g = synth.genome(shape["genome"])
-    case = Case([g], shape["k"])
+    case = Case(backend, [g], shape["k"])
     bases, off = synth.reads(g, 777, 0, shape["n_reads"], shape["read_len"], shape["err_ppm"])
     rec, roff = case.ctx.encode_batch(bases, off)
     n_check = min(shape["n_reads"], 3000)
@@ -215,11 +238,14 @@ def test_synthetic_config_shapes(cfg):
     assert (doff == off).all() and (db == bases).all()
     text, n_seqs = case.ctx.decode_fasta(rec, 1)
     assert n_seqs == shape["n_reads"]
-    head = helpers.fasta_text([bases[int(off[i]): int(off[i + 1])] for i in range(50)], 1)
+    head = helpers.fasta_text([bases[int(off[i]): int(off[i + 1])] for i in range(min(50, shape["n_reads"]))], 1)
     assert text[: len(head)] == head
 
 
+@pytest.mark.gpu
 def test_device_resident_api_with_torch(small_cases):
+    if small_cases[0].backend != "gpu":
+        pytest.skip("device pointers need a GPU")
     import torch
     case = small_cases[3]
     rng = np.random.default_rng(13)
