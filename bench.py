@@ -52,7 +52,7 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, device):
         super().__init__(daemon=True)
-        self.device, self.samples, self.reasons, self.max_mhz, self._stop = device, [], set(), None, threading.Event()
+        self.device, self.samples, self.reasons, self.max_mhz, self._halt = device, [], set(), None, threading.Event()
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -68,7 +68,7 @@ class ClockSampler(threading.Thread):
         nv = self.nv
         names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
                  nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
                 mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
@@ -80,7 +80,7 @@ class ClockSampler(threading.Thread):
             time.sleep(0.05)
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
         self.join(timeout=2)
         return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
@@ -174,7 +174,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C3", choices=["C2", "C3", "C4", "C5"])
     ap.add_argument("--reads", type=int, default=None, help="override reads per GPU (testing)")
-    ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU baseline work")
+    ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU baseline work (0 = skip)")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (profiling runs)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -303,16 +304,18 @@ def main():
         _lib.check(L.ntc_decode_fasta(ctx._h, h_rec.data_ptr(), n_rec_c.value, lo + 1, h_text.data_ptr(), out_cap, C.byref(n_bytes_c), C.byref(n_seqs_c)))
 
     e2e_steps = max(1, min(steps, 3))
-    e2e_step()
-    first = (b">seq.%d\n" % (lo + 1)) + bytes(h_bases[:read_len].numpy()) + b"\n"
-    if n_seqs_c.value != n_reads or bytes(h_text[: len(first)].numpy()) != first:
-        raise SystemExit("bench.py: end-to-end FASTA does not start with the first read")
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    t_e2e = float("nan")
+    if not args.no_e2e:
         e2e_step()
-    torch.cuda.synchronize()
-    t_e2e = time.perf_counter() - t0
+        first = (b">seq.%d\n" % (lo + 1)) + bytes(h_bases[:read_len].numpy()) + b"\n"
+        if n_seqs_c.value != n_reads or bytes(h_text[: len(first)].numpy()) != first:
+            raise SystemExit("bench.py: end-to-end FASTA does not start with the first read")
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        t_e2e = time.perf_counter() - t0
     te = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
@@ -353,7 +356,7 @@ def main():
     }
     # ---- CPU baseline beside it (rank 0, N = 1 only): literal oracle, one thread like the reference ----
     cpu = None
-    if world == 1:
+    if world == 1 and args.cpu_budget > 0:
         oracle = oracle_from(index)
         n_s = min(n_reads, 1 << 15)
         sb = h_bases[: n_s * read_len].numpy()

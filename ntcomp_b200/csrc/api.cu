@@ -82,8 +82,8 @@ int32_t encode_pipeline(ntc_ctx* ctx, int mode, const uint8_t* d_bases, const ui
         return NTC_OK;
     }
     const uint64_t n_words = n_bases / 32 + 2;
-    NTC_CUDA_TRY(ensure(&ctx->packed, n_words * 8));
-    NTC_CUDA_TRY(ensure(&ctx->scratch, std::max<uint64_t>(n_bases, 1) * 8));
+    NTC_CUDA_TRY(ensure(&ctx->packed, (n_words + 4) * 8));
+    NTC_CUDA_TRY(ensure(&ctx->scratch, scratch_entries(n_bases, n_reads) * 8));
     NTC_CUDA_TRY(ensure(&ctx->counts, n_reads * 4));
     NTC_CUDA_TRY(ensure(&ctx->tiles, scan_num_tiles(n_reads) * sizeof(Pair64)));
     uint64_t* rec_off = d_rec_offsets;
@@ -196,7 +196,7 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     build_rank_blocks(*idx, &rank, threads);
     build_jump_table(*idx, &jump, threads);
     std::vector<uint8_t> lcs(idx->lcs);
-    lcs.push_back(0);
+    lcs.resize((idx->lcs.size() / 16 + 2) * 16, 0);  // lcs[n] = 0 sentinel, padded for aligned 16-byte scans
     auto fail = [&](const char* what, cudaError_t err) {
         set_error(std::string(what) + ": " + cudaGetErrorString(err));
         ntc_ctx_destroy(ctx);

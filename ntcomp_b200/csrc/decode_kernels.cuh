@@ -93,6 +93,78 @@ __global__ void __launch_bounds__(256) seq_offsets_kernel(const uint64_t* __rest
                        (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
+// ---- leftward write combiner ---------------------------------------------------------------
+// A record's bases come out right-to-left, 16 per jump-table load.  Bytes are merged into aligned
+// 8-byte words so the interior of a segment is written with full u64 stores; only the two edges
+// of a segment (which share words with neighbouring segments / headers) use 4/2/1-byte stores.
+// (First version, ncu r1: 1.59 G single-byte stores made walk_kernel L1TEX-bound.)
+NTC_HD void store_lanes(uint8_t* word_addr, uint64_t w, uint32_t lo, uint32_t hi) {  // lanes [lo, hi) of the aligned word
+    if (lo == 0 && hi == 8) { *(uint64_t*)word_addr = w; return; }
+    uint32_t l = lo;
+    while (l < hi) {
+        if ((l & 3u) == 0 && l + 4 <= hi) { *(uint32_t*)(word_addr + l) = (uint32_t)(w >> (8 * l)); l += 4; }
+        else if ((l & 1u) == 0 && l + 2 <= hi) { *(uint16_t*)(word_addr + l) = (uint16_t)(w >> (8 * l)); l += 2; }
+        else { word_addr[l] = (uint8_t)(w >> (8 * l)); l += 1; }
+    }
+}
+
+struct LeftWriter {
+    uint8_t* out;   // 8-byte aligned base of the output buffer
+    uint64_t p;     // bytes [p, segment end) are done; pending bytes of the word holding p sit in acc
+    uint64_t acc;   // lanes [p & 7, top) of the aligned word at p & ~7
+    uint32_t top;
+
+    NTC_HD void init(uint8_t* base, uint64_t end) { out = base; p = end; acc = 0; top = (uint32_t)(end & 7); }
+    // x = the 8 bytes for positions [p-8, p)
+    NTC_HD void push8(uint64_t x) {
+        uint32_t q = (uint32_t)(p & 7);
+        if (q == 0) {
+            *(uint64_t*)(out + p - 8) = x;
+        } else {
+            uint32_t sh = 8 * q;
+            store_lanes(out + (p & ~7ull), acc | (x >> (64 - sh)), 0, top);
+            acc = x << sh;
+            top = 8;
+        }
+        p -= 8;
+    }
+    // x holds n < 8 bytes for positions [p-n, p) in its UPPER lanes; ends the segment
+    NTC_HD void push_last(uint64_t x, uint32_t n) {
+        uint32_t q = (uint32_t)(p & 7);
+        uint8_t* wa = out + (p & ~7ull);
+        if (n == 0) { if (q) store_lanes(wa, acc, q, top); return; }
+        if (q == 0) { store_lanes(wa - 8, x, 8 - n, 8); return; }
+        uint32_t sh = 8 * q;
+        uint64_t w = acc | (x >> (64 - sh));
+        if (n <= q) { store_lanes(wa, w, q - n, top); return; }
+        store_lanes(wa, w, 0, top);
+        store_lanes(wa - 8, x << sh, 8 - (n - q), 8);
+    }
+};
+
+// ASCII of four 2-bit codes (low byte of x), first code in the low byte of the result
+NTC_HD uint32_t ascii4(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    uint32_t sel = (x & 3u) | ((x & 0xCu) << 2) | ((x & 0x30u) << 4) | ((x & 0xC0u) << 6);
+    return __byte_perm(0x54474341u, 0u, sel);
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < 4; i++) r |= (uint32_t)code_ascii((x >> (2 * i)) & 3u) << (8 * i);
+    return r;
+#endif
+}
+NTC_HD uint64_t ascii8(uint32_t codes16) {  // eight 2-bit codes in the low 16 bits
+    return (uint64_t)ascii4(codes16 & 0xFFu) | ((uint64_t)ascii4((codes16 >> 8) & 0xFFu) << 32);
+}
+
+// emits the last `t` (<= 16) bases of `codes` (base i of the 16-base window at bits 2i..2i+1)
+NTC_HD void emit_codes(LeftWriter& w, uint32_t codes, uint32_t t, bool last) {
+    uint64_t hi = ascii8(codes >> 16), lo = ascii8(codes & 0xFFFFu);
+    if (t == 16) { w.push8(hi); w.push8(lo); if (last) w.push_last(0, 0); return; }
+    if (t >= 8) { w.push8(hi); w.push_last(lo, t - 8); }
+    else w.push_last(hi, t);
+}
+
 // one thread per record: walk / unpack and store ASCII bases (and FASTA header + newline on the
 // record that opens a sequence)
 NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, uint64_t n_rec, const uint64_t* __restrict__ base_off,
@@ -114,7 +186,6 @@ NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, ui
     // segment [A + B - E[i+1], A + B - E[i]) of the base stream
     uint64_t seg_end = A + B - base_off[i] - base0;
     uint64_t shift = fasta ? fasta_overhead(first_no, sid) : 0;
-    uint8_t* dst_end = out + seg_end + shift;
 
     if (fasta && (flag & 1u)) {  // header before the sequence, newline after it
         uint64_t seq_lo = A - base0 + shift, seq_hi = B - base0 + shift;
@@ -126,11 +197,23 @@ NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, ui
         h[5 + dg] = '\n';
         out[seq_hi] = '\n';
     }
+    if (L == 0) return;
+    // the output buffer may be misaligned by the caller: fold the misalignment into the position
+    const uint64_t mis = (uint64_t)((uintptr_t)out & 7u);
+    LeftWriter lw;
+    lw.init(out - mis, seg_end + shift + mis);
 
-    if (flag & 2u) {  // literal record, src/lib.rs:295-306
-        uint64_t bits = w;
-        uint8_t* dst = dst_end - L;
-        for (uint32_t q = 0; q < L; q++) dst[q] = (uint8_t)(0x54474341u >> (8 * ((bits >> (2 * q)) & 3u)));
+    if (flag & 2u) {  // literal record (<= 32 bases), src/lib.rs:295-306
+        uint64_t bits = w & ((1ull << (2 * L)) - 1ull);  // L <= 32 here; L == 32 keeps all 56 bits + zeros
+        if (L == 32) bits = w & 0x00FFFFFFFFFFFFFFull;
+        if (L > 16) {
+            uint32_t top_codes = (uint32_t)(bits >> (2 * (L - 16)));           // last 16 bases
+            emit_codes(lw, top_codes, 16, false);
+            uint32_t rest = L - 16;                                             // first `rest` bases, to the upper lanes of a window
+            emit_codes(lw, (uint32_t)(bits << (2 * (16 - rest))), rest, true);
+        } else {
+            emit_codes(lw, (uint32_t)(bits << (2 * (16 - L))), L, true);
+        }
         return;
     }
     uint32_t v = (uint32_t)w;
@@ -139,11 +222,9 @@ NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, ui
     while (remaining > 0) {
         uint64_t ent = NTC_LDG(ix.jump + v);
         uint32_t t = tmin(remaining, 16u);
-        uint32_t chars = (uint32_t)(ent >> 32) >> (2 * (16 - t));  // last t bases, earliest in the low bits
-        dst_end -= t;
-        for (uint32_t q = 0; q < t; q++) dst_end[q] = (uint8_t)(0x54474341u >> (8 * ((chars >> (2 * q)) & 3u)));
-        v = (uint32_t)ent;
         remaining -= t;
+        emit_codes(lw, (uint32_t)(ent >> 32), t, remaining == 0);
+        v = (uint32_t)ent;
     }
 }
 __global__ void __launch_bounds__(128) walk_kernel(DevIndex ix, const uint64_t* __restrict__ rec, uint64_t n_rec,

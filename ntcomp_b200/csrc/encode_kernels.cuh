@@ -96,14 +96,83 @@ NTC_HD uint32_t segment_read(const uint64_t* __restrict__ sc, uint32_t len, uint
 
 // ------------------------------------------------------------------------------------------
 // matching statistics + record count.  One thread per read.
+//
+// Flat state machine: every loop iteration issues ONE primary 16-byte load (plus a predicated second
+// one) whose address depends on the thread's state -- a rank entry while extending, an aligned LCS
+// chunk while contracting -- so the threads of a warp overlap their memory round trips even when
+// some extend and others contract.  (First version, ncu r1: an inner retry loop and byte-wise LCS
+// scans ran 60% of all issued instructions with ~1 active thread per warp.)
 // ------------------------------------------------------------------------------------------
 struct CountSink {
     uint32_t big = 0;
     NTC_HD void operator()(uint32_t L, uint32_t, uint32_t, uint32_t) { big |= (L >= (1u << 24)); }
 };
 
-NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offsets, uint64_t n_reads,
-                      uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t r) {
+// 0x80 in every byte of `a` that is (unsigned) less than the corresponding byte of `b`
+NTC_HD uint32_t bytes_lt(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+    return __vcmpltu4(a, b) & 0x80808080u;
+#else
+    const uint32_t H = 0x80808080u;
+    uint32_t dl = ((a & ~H) | H) - (b & ~H);
+    return ((~a & b) | (~(a ^ b) & ~dl)) & H;
+#endif
+}
+// byte-flag mask (bit 8i+7 set when byte i of the 16-byte chunk is < t)
+NTC_HD void chunk_lt(const uint4& v, uint32_t t, uint64_t* lo, uint64_t* hi) {
+    uint32_t t4 = t * 0x01010101u;
+    *lo = (uint64_t)bytes_lt(v.x, t4) | ((uint64_t)bytes_lt(v.y, t4) << 32);
+    *hi = (uint64_t)bytes_lt(v.z, t4) | ((uint64_t)bytes_lt(v.w, t4) << 32);
+}
+NTC_HD int clz64(uint64_t x) {
+#if defined(__CUDA_ARCH__)
+    return __clzll((long long)x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
+NTC_HD int ffs64(uint64_t x) {  // 1-based index of the lowest set bit, 0 if none
+#if defined(__CUDA_ARCH__)
+    return __ffsll((long long)x);
+#else
+    return x ? __builtin_ctzll(x) + 1 : 0;
+#endif
+}
+// highest byte index <= pos whose value < t, or -1
+NTC_HD int last_lt_upto(const uint4& v, uint32_t t, uint32_t pos) {
+    uint64_t lo, hi;
+    chunk_lt(v, t, &lo, &hi);
+    if (pos < 8) { hi = 0; lo &= (~0ull) >> (8 * (7 - pos)); }
+    else hi &= (~0ull) >> (8 * (15 - pos));
+    if (hi) return 8 + (63 - clz64(hi)) / 8;
+    if (lo) return (63 - clz64(lo)) / 8;
+    return -1;
+}
+// lowest byte index >= pos whose value < t, or -1
+NTC_HD int first_lt_from(const uint4& v, uint32_t t, uint32_t pos) {
+    uint64_t lo, hi;
+    chunk_lt(v, t, &lo, &hi);
+    if (pos < 8) lo &= (~0ull) << (8 * pos);
+    else { lo = 0; hi &= (~0ull) << (8 * (pos - 8)); }
+    if (lo) return (ffs64(lo) - 1) / 8;
+    if (hi) return 8 + (ffs64(hi) - 1) / 8;
+    return -1;
+}
+NTC_HD uint32_t chunk_byte(const uint4& v, uint32_t pos) {
+    uint32_t w = pos < 8 ? (pos < 4 ? v.x : v.y) : (pos < 12 ? v.z : v.w);
+    return (w >> (8 * (pos & 3))) & 0xFFu;
+}
+
+// scratch position of read r: its entries start on a 32-byte sector so that groups of four 8-byte
+// entries are written as one full sector (no read-for-fill in L2/DRAM)
+NTC_HD uint64_t scratch_base(uint64_t a, uint64_t r) { return (a + 4 * r) & ~3ull; }
+inline uint64_t scratch_entries(uint64_t n_bases, uint64_t n_reads) { return n_bases + 4 * n_reads + 8; }
+
+// `stage` = 4 x blockDim u64 staging slots of this thread's block (shared memory on the GPU),
+// indexed [slot * stride + lane]
+NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t* __restrict__ offsets, uint64_t n_reads,
+                      uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t r,
+                      uint64_t* stage, uint32_t stride) {
     if (r >= n_reads) return;
     const uint64_t base0 = NTC_LDG(offsets);
     const uint64_t a = offsets[r] - base0;
@@ -114,46 +183,96 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* __restrict__ packed, c
         return;
     }
     const uint32_t n = ix.n, k = ix.k;
-    uint64_t* __restrict__ sc = scratch + a;
-    uint32_t s = 0, e = n, d = 0, urun = 0;
-    bool absent = false;
-    uint64_t word = 0;
-    for (uint32_t j = 0; j < len; j++) {
-        uint64_t p = a + j;
-        if (j == 0 || (p & 31) == 0) word = NTC_LDG(packed + (p >> 5));
-        const uint32_t c = (uint32_t)(word >> ((p & 31) * 2)) & 3u;
-        const uint32_t prev_s = s, prev_d = d;
-        bool fresh = true;
-        for (;;) {
-            uint32_t bs = s / 48u, os = s - bs * 48u;
-            uint4 es = ldg_entry(ix.rank + (size_t)bs * 4 + c);
+    const uint4* __restrict__ lcs16 = (const uint4*)ix.lcs;
+    uint64_t* __restrict__ sc = scratch + scratch_base(a, r);
+    uint32_t s = 0, e = n, d = 0, urun = 0, prev_s = 0, prev_d = 0, t = 0, j = 0;
+    int mode = 0;                    // 0 extend (rank probes), 1 contraction: read LCS[s], LCS[e]; 2 contraction: keep scanning
+    bool fresh = true, go_s = false, go_e = false, absent = false;
+    uint64_t word = packed[a >> 5];
+    uint32_t c = (uint32_t)(word >> ((a & 31) * 2)) & 3u;
+    while (j < len) {
+        // ---- one primary + one predicated secondary 16-byte load, address by state ----
+        const uint4* pa;
+        const uint4* pb;
+        bool need_b;
+        uint32_t os = 0, oe = 0;
+        if (mode == 0) {
+            uint32_t bs = s / 48u, be = e / 48u;
+            os = s - bs * 48u; oe = e - be * 48u;
+            pa = ix.rank + (size_t)bs * 4 + c;
+            pb = ix.rank + (size_t)be * 4 + c;
+            need_b = be != bs;
+        } else {
+            pa = lcs16 + (s >> 4);
+            pb = lcs16 + (e >> 4);
+            need_b = go_e && (e >> 4) != (s >> 4);
+        }
+        const uint4 va = NTC_LDG(pa);
+        const uint4 vb = need_b ? NTC_LDG(pb) : va;
+
+        if (mode == 0) {
             if (fresh) {
                 // the block of the previous interval start also holds its Q bit: finish entry j-1
                 if (j > 0) {
-                    urun = (prev_d == k && entry_qbit(es, os)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
-                    sc[j - 1] = make_entry(prev_s, prev_d, urun);
+                    urun = (prev_d == k && entry_qbit(va, os)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
+                    uint32_t slot = (j - 1) & 3u;
+                    stage[slot * stride] = make_entry(prev_s, prev_d, urun);
+                    if (slot == 3u) {                                 // one full 32-byte sector
+                        ulonglong2 x0, x1;
+                        x0.x = stage[0]; x0.y = stage[stride]; x1.x = stage[2 * stride]; x1.y = stage[3 * stride];
+                        ulonglong2* dst = (ulonglong2*)(sc + (j - 4));
+                        dst[0] = x0; dst[1] = x1;
+                    }
                 }
                 fresh = false;
             }
-            uint32_t s2 = entry_rank(es, os);
-            uint32_t be = e / 48u, oe = e - be * 48u;
-            uint32_t e2;
-            if (be == bs) e2 = entry_rank(es, oe);
-            else { uint4 ee = ldg_entry(ix.rank + (size_t)be * 4 + c); e2 = entry_rank(ee, oe); }
-            if (s2 < e2) { s = s2; e = e2; d = tmin(d + 1u, k); break; }  // extend_right succeeded
-            if (s == 0 && e == n) { d = 0; break; }                        // base absent from the index
-            // contract_left until the interval can change: for targets above max(LCS[s], LCS[e])
-            // the reference loop re-probes the same empty interval (identical (d, I) result)
-            int ls = s > 0 ? (int)NTC_LDG(ix.lcs + s) : -1;
-            int le = e < n ? (int)NTC_LDG(ix.lcs + e) : -1;
-            uint32_t t = (uint32_t)tmin((int)d - 1, tmax(ls, le));
-            while (s > 0 && NTC_LDG(ix.lcs + s) >= t) s--;
-            while (e < n && NTC_LDG(ix.lcs + e) >= t) e++;
-            d = t;
+            uint32_t s2 = entry_rank(va, os), e2 = entry_rank(vb, oe);
+            if (s2 < e2) {                                            // extend_right succeeded
+                s = s2; e = e2; d = tmin(d + 1u, k);
+            } else if (s == 0 && e == n) {                            // base absent from the index
+                d = 0; absent = true;
+            } else {                                                  // contract_left
+                mode = 1; go_s = s > 0; go_e = e < n;
+                continue;
+            }
+            prev_s = s; prev_d = d; fresh = true;
+            j++;
+            if (j < len) {
+                uint64_t p = a + j;
+                if ((p & 31) == 0) word = packed[p >> 5];
+                c = (uint32_t)(word >> ((p & 31) * 2)) & 3u;
+            }
+        } else {
+            if (mode == 1) {
+                // for targets above max(LCS[s], LCS[e]) the reference loop re-probes the same empty
+                // interval, so d jumps straight to that level (identical (d, I) afterwards)
+                int ls = go_s ? (int)chunk_byte(va, s & 15u) : -1;
+                int le = go_e ? (int)chunk_byte(vb, e & 15u) : -1;
+                t = (uint32_t)tmin((int)d - 1, tmax(ls, le));
+                d = t;
+                mode = 2;
+                if (t == 0) { s = 0; e = n; mode = 0; continue; }     // LCS >= 0 everywhere
+            }
+            // lcs[0] == 0 and lcs[n] == 0 stop both scans for t >= 1
+            if (go_s) {
+                int idx = last_lt_upto(va, t, s & 15u);
+                if (idx >= 0) { s = (s & ~15u) + (uint32_t)idx; go_s = false; }
+                else s = (s & ~15u) - 1u;
+            }
+            if (go_e) {
+                int idx = first_lt_from(vb, t, e & 15u);
+                if (idx >= 0) { e = (e & ~15u) + (uint32_t)idx; go_e = false; }
+                else e = (e & ~15u) + 16u;
+            }
+            if (!go_s && !go_e) mode = 0;
         }
-        absent |= (d == 0);
     }
-    sc[len - 1] = make_entry(s, d, 0);
+    // tail: entries of the last, partial group of four + the final position
+    {
+        uint32_t first_unflushed = (len - 1) & ~3u;                    // entries [first_unflushed, len-1) are staged
+        for (uint32_t q = first_unflushed; q + 1 < len; q++) sc[q] = stage[(q & 3u) * stride];
+        sc[len - 1] = make_entry(prev_s, prev_d, 0);
+    }
     if (absent) {                                                     // lib.rs:207 would underflow (Q3)
         if (counts) counts[r] = 0;
         NTC_ATOMIC_OR(status, (uint32_t)ST_BAD_BASE);
@@ -166,11 +285,63 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* __restrict__ packed, c
     }
 }
 
-__global__ void __launch_bounds__(kMsThreads) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
+#if defined(__CUDACC__)
+// 1-D bulk TMA (cp.async.bulk) of `bytes` (multiple of 16) from global to shared memory, completion
+// on an mbarrier; issued by one thread.
+__device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    uint32_t dst = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(gmem_src),
+                 "r"(bytes), "r"(b)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(b), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(b),
+        "r"(parity)
+        : "memory");
+}
+#endif
+
+constexpr uint32_t kMsStageWords = 1024;  // 8 KB of packed reads per block (128 reads x up to 256 bases); longer reads load from global
+
+__global__ void __launch_bounds__(kMsThreads, 12) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
                                                         const uint64_t* __restrict__ offsets, uint64_t n_reads,
                                                         uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts,
                                                         uint32_t* __restrict__ status) {
-    ms_thread(ix, packed, offsets, n_reads, scratch, counts, status, (uint64_t)blockIdx.x * kMsThreads + threadIdx.x);
+    __shared__ __align__(16) uint64_t s_packed[kMsStageWords];
+    __shared__ uint64_t s_stage[4 * kMsThreads];
+    __shared__ __align__(8) uint64_t s_bar;
+    const uint64_t r0 = (uint64_t)blockIdx.x * kMsThreads;
+    const uint64_t r1 = r0 + kMsThreads < n_reads ? r0 + kMsThreads : n_reads;
+    // the block's reads are one contiguous run of the packed stream: stage it with one bulk TMA copy
+    const uint64_t base0 = offsets[0];
+    const uint64_t w_lo = ((offsets[r0] - base0) >> 5) & ~1ull;              // 16-byte aligned
+    const uint64_t w_hi = (((offsets[r1] - base0) >> 5) + 2) & ~1ull;        // exclusive, 16-byte aligned (buffer is padded)
+    const bool staged = (w_hi - w_lo) <= kMsStageWords;
+    if (staged) {
+        if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+        __syncthreads();
+        if (threadIdx.x == 0) tma_load_1d(s_packed, packed + w_lo, (uint32_t)((w_hi - w_lo) * 8), &s_bar);
+        mbar_wait(&s_bar, 0);
+    }
+    const uint64_t* pk = staged ? (s_packed - w_lo) : packed;                // generic pointer: shared or global
+    ms_thread(ix, pk, offsets, n_reads, scratch, counts, status, r0 + threadIdx.x, s_stage + threadIdx.x, kMsThreads);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -214,7 +385,7 @@ NTC_HD void emit_thread(const DevIndex& ix, const uint64_t* __restrict__ packed,
     const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
     if (rec_offsets[r + 1] > cap) { NTC_ATOMIC_OR(status, (uint32_t)ST_CAPACITY); return; }
     EmitSink<MODE> sink{ix, packed, out, a, rec_offsets[r], 1};
-    segment_read(scratch + a, len, ix.k, sink);
+    segment_read(scratch + scratch_base(a, r), len, ix.k, sink);
 }
 
 template <int MODE>
@@ -251,14 +422,18 @@ __global__ void __launch_bounds__(256) dict_pack_kernel(DevIndex ix, const uint6
     dict_pack_thread(ix, triples, n, out, status, (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
-// per-base (d, start) dump for the matching-statistics parity entry point
-__global__ void __launch_bounds__(256) ms_dump_kernel(const uint64_t* __restrict__ scratch, uint64_t n_bases,
-                                                      uint8_t* __restrict__ d_out, uint32_t* __restrict__ s_out) {
-    uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
-    if (i >= n_bases) return;
-    uint64_t e = scratch[i];
-    d_out[i] = (uint8_t)entry_d(e);
-    s_out[i] = entry_s(e);
+// per-base (d, start) dump for the matching-statistics parity entry point (diagnostic, one thread per read)
+__global__ void __launch_bounds__(256) ms_dump_kernel(const uint64_t* __restrict__ scratch, const uint64_t* __restrict__ offsets,
+                                                      uint64_t n_reads, uint8_t* __restrict__ d_out, uint32_t* __restrict__ s_out) {
+    uint64_t r = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (r >= n_reads) return;
+    const uint64_t a = offsets[r] - offsets[0];
+    const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
+    const uint64_t* sc = scratch + scratch_base(a, r);
+    for (uint32_t j = 0; j < len; j++) {
+        d_out[a + j] = (uint8_t)entry_d(sc[j]);
+        s_out[a + j] = entry_s(sc[j]);
+    }
 }
 
 }  // namespace ntc

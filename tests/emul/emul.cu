@@ -15,6 +15,7 @@ struct EmulIndex {
     std::vector<uint32_t> rank;
     std::vector<uint64_t> jump;
     std::vector<uint8_t> lcs;
+    size_t lcs_off = 0;
     DevIndex dix;
 };
 
@@ -25,9 +26,13 @@ void* emul_index_create(const ntc_index* idx) {
     build_rank_blocks(*idx, &e->rank, 2);
     build_jump_table(*idx, &e->jump, 2);
     e->lcs = idx->lcs;
-    e->lcs.push_back(0);
+    e->lcs.resize((idx->lcs.size() / 16 + 2) * 16 + 16, 0);
+    // 16-byte aligned view for the vectorised LCS scans
+    size_t mis = (16 - ((uintptr_t)e->lcs.data() & 15)) & 15;
+    e->lcs.insert(e->lcs.begin(), mis, 0);
+    e->lcs_off = mis;
     e->dix.rank = (const uint4*)e->rank.data();
-    e->dix.lcs = e->lcs.data();
+    e->dix.lcs = e->lcs.data() + e->lcs_off;
     e->dix.jump = e->jump.data();
     e->dix.n = (uint32_t)idx->n;
     e->dix.k = idx->k;
@@ -36,12 +41,16 @@ void* emul_index_create(const ntc_index* idx) {
 void emul_index_free(void* p) { delete (EmulIndex*)p; }
 
 static void run_ms(const EmulIndex* e, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads, std::vector<uint64_t>* packed,
-                   std::vector<uint64_t>* scratch, uint32_t* counts, uint32_t* status) {
+                   std::vector<uint64_t>* scratch, uint64_t** scratch_aligned, uint32_t* counts, uint32_t* status) {
     uint64_t nb = offsets[n_reads] - offsets[0];
-    packed->assign(nb / 32 + 2, 0);
-    scratch->assign(nb + 1, 0);
+    packed->assign(nb / 32 + 6, 0);
+    scratch->assign(scratch_entries(nb, n_reads) + 4, 0);
     for (uint64_t w = 0; w < (nb + 31) / 32; w++) pack2bit_thread(bases, offsets, nb, packed->data(), status, w);
-    for (uint64_t r = 0; r < n_reads; r++) ms_thread(e->dix, packed->data(), offsets, n_reads, scratch->data(), counts, status, r);
+    uint64_t* sc = scratch->data();
+    sc += (4 - (((uintptr_t)sc / 8) & 3)) & 3;                       // 32-byte aligned, like cudaMalloc
+    *scratch_aligned = sc;
+    uint64_t stage[4];
+    for (uint64_t r = 0; r < n_reads; r++) ms_thread(e->dix, packed->data(), offsets, n_reads, sc, counts, status, r, stage, 1);
 }
 
 // mode 0 records, 1 triples.  Returns the accumulated status bits.
@@ -51,12 +60,13 @@ uint32_t emul_encode(void* ep, const uint8_t* bases, const uint64_t* offsets, ui
     uint32_t status = 0;
     std::vector<uint64_t> packed, scratch;
     std::vector<uint32_t> counts(n_reads + 1, 0);
-    run_ms(e, bases, offsets, n_reads, &packed, &scratch, counts.data(), &status);
+    uint64_t* sc = nullptr;
+    run_ms(e, bases, offsets, n_reads, &packed, &scratch, &sc, counts.data(), &status);
     std::vector<uint64_t> roff(n_reads + 1, 0);
     for (uint64_t r = 0; r < n_reads; r++) roff[r + 1] = roff[r] + counts[r];   // exclusive scan (scan.cuh on the GPU)
     for (uint64_t r = 0; r < n_reads; r++) {
-        if (mode == 0) emit_thread<0>(e->dix, packed.data(), offsets, n_reads, scratch.data(), counts.data(), roff.data(), out, cap, &status, r);
-        else emit_thread<1>(e->dix, packed.data(), offsets, n_reads, scratch.data(), counts.data(), roff.data(), out, cap, &status, r);
+        if (mode == 0) emit_thread<0>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), out, cap, &status, r);
+        else emit_thread<1>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), out, cap, &status, r);
     }
     *n_records = roff[n_reads];
     if (rec_offsets) memcpy(rec_offsets, roff.data(), (n_reads + 1) * 8);
@@ -67,9 +77,13 @@ uint32_t emul_ms(void* ep, const uint8_t* bases, const uint64_t* offsets, uint64
     const EmulIndex* e = (const EmulIndex*)ep;
     uint32_t status = 0;
     std::vector<uint64_t> packed, scratch;
-    run_ms(e, bases, offsets, n_reads, &packed, &scratch, nullptr, &status);
-    uint64_t nb = offsets[n_reads] - offsets[0];
-    for (uint64_t i = 0; i < nb; i++) { d_out[i] = (uint8_t)entry_d(scratch[i]); s_out[i] = entry_s(scratch[i]); }
+    uint64_t* sc = nullptr;
+    run_ms(e, bases, offsets, n_reads, &packed, &scratch, &sc, nullptr, &status);
+    for (uint64_t r = 0; r < n_reads; r++) {
+        uint64_t a = offsets[r] - offsets[0];
+        const uint64_t* rs = sc + scratch_base(a, r);
+        for (uint64_t j = 0; j < offsets[r + 1] - offsets[r]; j++) { d_out[a + j] = (uint8_t)entry_d(rs[j]); s_out[a + j] = entry_s(rs[j]); }
+    }
     return status;
 }
 

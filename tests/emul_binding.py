@@ -94,7 +94,7 @@ class EmulContext:
     def decode_batch(self, records):
         rec = np.ascontiguousarray(records, dtype=np.uint64)
         nb, ns, _ = self.decode_bound(rec)
-        bases = np.zeros(max(nb, 1) + 64, dtype=np.uint8)
+        bases = np.zeros(max(nb, 1) + 72, dtype=np.uint8)[3:]       # deliberately misaligned output buffer
         soff = np.zeros(ns + 1, dtype=np.uint64)
         cnt = np.zeros(2, dtype=np.uint64)
         _raise(lib().emul_decode(self._h, _ptr(rec), len(rec), 1, 0, _ptr(bases), nb, _ptr(soff), ns, _ptr(cnt)))

@@ -140,6 +140,28 @@ def test_decode_drops_records_before_first_flag(small_cases):
     assert len(empty_b) == 0 and list(empty_off) == [0]
 
 
+def test_decode_handcrafted_literals_up_to_32_bases(small_cases):
+    """literal records longer than the encoder's 11 (flag length field is 6 bits; from_2bit takes <= 32)"""
+    case = small_cases[2]
+    rng = np.random.default_rng(21)
+    recs = []
+    for L in list(range(1, 29)) + [33, 40, 63]:          # 7 payload bytes hold 28 bases; > 32 decodes to nothing (lib.rs:303)
+        bits = int(rng.integers(0, 1 << 56))
+        bits &= (1 << (2 * min(L, 28))) - 1
+        first = int(rng.integers(0, 2)) if recs else 1
+        recs.append(bits | (((first + 2) | (L << 2)) << 56))
+    good = bytes(case.contigs[0][100:180])
+    ref_rec, _ = case.oracle.encode_reads(*nt.concat_reads([good]), fast=True)
+    stream = np.array(recs + list(ref_rec) + recs[::-1], dtype=np.uint64)
+    stream[len(recs)] |= np.uint64(1 << 56)
+    db, doff = case.ctx.decode_batch(stream)
+    ob_, ooff = case.oracle.decode(stream, fast=False)
+    assert (doff == ooff).all() and (db == ob_).all()
+    text, n = case.ctx.decode_fasta(stream, 7)
+    seqs = [bytes(ob_[int(ooff[i]): int(ooff[i + 1])]) for i in range(len(ooff) - 1)]
+    assert text == helpers.fasta_text(seqs, 7) and n == len(seqs)
+
+
 def test_fixture_c1_shape_roundtrip(backend):
     """BASELINE config #1: tests/fasta_data.rs shape (7 contigs < 2000 bp, k = 255, block size 3)."""
     contigs, k, block = helpers.fixture_c1()
@@ -273,3 +295,9 @@ def test_device_resident_api_with_torch(small_cases):
     assert int(d_cnt[0].item()) == len(reads) and int(d_cnt[1].item()) == len(bases)
     assert (d_out[: len(bases)].cpu().numpy() == bases).all()
     assert (d_soff.cpu().numpy().view(np.uint64) == off).all()
+    for mis in (1, 3, 5, 6):                              # caller-misaligned output buffer
+        d_out.zero_()
+        case.ctx.decode_device(d_rec.data_ptr(), n_rec, 99, True, d_out.data_ptr() + mis, len(bases) + 40 * len(reads), 0, 0, d_cnt.data_ptr(), stream)
+        case.ctx.status(stream)
+        nbytes = int(d_cnt[1].item())
+        assert bytes(d_out[mis: mis + nbytes].cpu().numpy()) == helpers.fasta_text(reads, 99)
