@@ -195,15 +195,15 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     std::vector<uint64_t> jump;
     build_rank_blocks(*idx, &rank, threads);
     build_jump_table(*idx, &jump, threads);
-    std::vector<uint8_t> lcs(idx->lcs);
-    lcs.resize((idx->lcs.size() / 16 + 2) * 16, 0);  // lcs[n] = 0 sentinel, padded for aligned 16-byte scans
+    std::vector<uint32_t> lcs;
+    build_lcs_words(*idx, &lcs);
     auto fail = [&](const char* what, cudaError_t err) {
         set_error(std::string(what) + ": " + cudaGetErrorString(err));
         ntc_ctx_destroy(ctx);
         return NTC_ERR_CUDA;
     };
     ctx->index_bytes[0] = rank.size() * 4;
-    ctx->index_bytes[1] = lcs.size();
+    ctx->index_bytes[1] = lcs.size() * 4;
     ctx->index_bytes[2] = jump.size() * 8;
     if ((e = cudaMalloc(&ctx->d_rank, ctx->index_bytes[0])) != cudaSuccess) return fail("cudaMalloc rank", e);
     if ((e = cudaMalloc(&ctx->d_lcs, ctx->index_bytes[1])) != cudaSuccess) return fail("cudaMalloc lcs", e);
@@ -219,7 +219,7 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     cudaMemset(ctx->d_counts, 0, 32);
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
     ctx->dix.rank = (const uint4*)ctx->d_rank;
-    ctx->dix.lcs = (const uint8_t*)ctx->d_lcs;
+    ctx->dix.lcsx = (const uint32_t*)ctx->d_lcs;
     ctx->dix.jump = (const uint64_t*)ctx->d_jump;
     ctx->dix.n = (uint32_t)idx->n;
     ctx->dix.k = idx->k;

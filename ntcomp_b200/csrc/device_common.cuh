@@ -36,7 +36,7 @@ enum : uint32_t {
 struct DevIndex {
     const uint4* rank;     // [(n/48+1) * 4] entries {C[c] + ones before block, row bits 0-31,
                            //   row bits 32-47 | Q bits 0-15 << 16, Q bits 16-47}; c = entry index & 3
-    const uint8_t* lcs;    // [n + 1], lcs[n] = 0
+    const uint32_t* lcsx;  // [n + 1] LCS | dist to previous smaller LCS << 8 | dist to next smaller LCS << 16; [n] = 0
     const uint64_t* jump;  // [n] pred^16 | chars16 << 32
     uint32_t n;
     uint32_t k;

@@ -97,76 +97,27 @@ NTC_HD uint32_t segment_read(const uint64_t* __restrict__ sc, uint32_t len, uint
 // ------------------------------------------------------------------------------------------
 // matching statistics + record count.  One thread per read.
 //
-// Flat state machine: every loop iteration issues ONE primary 16-byte load (plus a predicated second
-// one) whose address depends on the thread's state -- a rank entry while extending, an aligned LCS
-// chunk while contracting -- so the threads of a warp overlap their memory round trips even when
-// some extend and others contract.  (First version, ncu r1: an inner retry loop and byte-wise LCS
-// scans ran 60% of all issued instructions with ~1 active thread per warp.)
+// Flat loop, one memory round trip per iteration for every thread of the warp: the rank entry of
+// the interval start (plus the entry of the interval end when it falls in another block) and,
+// speculatively, the LCS words of both interval ends.  If extend_right fails, contract_left is pure
+// arithmetic on the words already loaded -- LCS value plus the precomputed distances to the previous /
+// next strictly smaller LCS value -- and the same base is probed again in the next iteration.
+//   ncu r1 v1: inner retry loop + byte-wise LCS scans = 60% of issued instructions at ~1 thread/warp
+//   ncu r1 v2: vectorised scans in a separate state   = 51% of issued instructions at ~2 threads/warp
 // ------------------------------------------------------------------------------------------
 struct CountSink {
     uint32_t big = 0;
     NTC_HD void operator()(uint32_t L, uint32_t, uint32_t, uint32_t) { big |= (L >= (1u << 24)); }
 };
 
-// 0x80 in every byte of `a` that is (unsigned) less than the corresponding byte of `b`
-NTC_HD uint32_t bytes_lt(uint32_t a, uint32_t b) {
-#if defined(__CUDA_ARCH__)
-    return __vcmpltu4(a, b) & 0x80808080u;
-#else
-    const uint32_t H = 0x80808080u;
-    uint32_t dl = ((a & ~H) | H) - (b & ~H);
-    return ((~a & b) | (~(a ^ b) & ~dl)) & H;
-#endif
-}
-// byte-flag mask (bit 8i+7 set when byte i of the 16-byte chunk is < t)
-NTC_HD void chunk_lt(const uint4& v, uint32_t t, uint64_t* lo, uint64_t* hi) {
-    uint32_t t4 = t * 0x01010101u;
-    *lo = (uint64_t)bytes_lt(v.x, t4) | ((uint64_t)bytes_lt(v.y, t4) << 32);
-    *hi = (uint64_t)bytes_lt(v.z, t4) | ((uint64_t)bytes_lt(v.w, t4) << 32);
-}
-NTC_HD int clz64(uint64_t x) {
-#if defined(__CUDA_ARCH__)
-    return __clzll((long long)x);
-#else
-    return x ? __builtin_clzll(x) : 64;
-#endif
-}
-NTC_HD int ffs64(uint64_t x) {  // 1-based index of the lowest set bit, 0 if none
-#if defined(__CUDA_ARCH__)
-    return __ffsll((long long)x);
-#else
-    return x ? __builtin_ctzll(x) + 1 : 0;
-#endif
-}
-// highest byte index <= pos whose value < t, or -1
-NTC_HD int last_lt_upto(const uint4& v, uint32_t t, uint32_t pos) {
-    uint64_t lo, hi;
-    chunk_lt(v, t, &lo, &hi);
-    if (pos < 8) { hi = 0; lo &= (~0ull) >> (8 * (7 - pos)); }
-    else hi &= (~0ull) >> (8 * (15 - pos));
-    if (hi) return 8 + (63 - clz64(hi)) / 8;
-    if (lo) return (63 - clz64(lo)) / 8;
-    return -1;
-}
-// lowest byte index >= pos whose value < t, or -1
-NTC_HD int first_lt_from(const uint4& v, uint32_t t, uint32_t pos) {
-    uint64_t lo, hi;
-    chunk_lt(v, t, &lo, &hi);
-    if (pos < 8) lo &= (~0ull) << (8 * pos);
-    else { lo = 0; hi &= (~0ull) << (8 * (pos - 8)); }
-    if (lo) return (ffs64(lo) - 1) / 8;
-    if (hi) return 8 + (ffs64(hi) - 1) / 8;
-    return -1;
-}
-NTC_HD uint32_t chunk_byte(const uint4& v, uint32_t pos) {
-    uint32_t w = pos < 8 ? (pos < 4 ? v.x : v.y) : (pos < 12 ? v.z : v.w);
-    return (w >> (8 * (pos & 3))) & 0xFFu;
-}
-
 // scratch position of read r: its entries start on a 32-byte sector so that groups of four 8-byte
 // entries are written as one full sector (no read-for-fill in L2/DRAM)
 NTC_HD uint64_t scratch_base(uint64_t a, uint64_t r) { return (a + 4 * r) & ~3ull; }
 inline uint64_t scratch_entries(uint64_t n_bases, uint64_t n_reads) { return n_bases + 4 * n_reads + 8; }
+
+// LCS word of node i: bits 0-7 LCS[i], 8-15 min(255, i - PSV(i)), 16-23 min(255, NSV(i) - i) where
+// PSV / NSV are the nearest positions left / right whose LCS is strictly smaller than LCS[i].
+NTC_HD uint32_t lcsx_lcs(uint32_t x) { return x & 0xFFu; }
 
 // `stage` = 4 x blockDim u64 staging slots of this thread's block (shared memory on the GPU),
 // indexed [slot * stride + lane]
@@ -183,88 +134,63 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         return;
     }
     const uint32_t n = ix.n, k = ix.k;
-    const uint4* __restrict__ lcs16 = (const uint4*)ix.lcs;
     uint64_t* __restrict__ sc = scratch + scratch_base(a, r);
-    uint32_t s = 0, e = n, d = 0, urun = 0, prev_s = 0, prev_d = 0, t = 0, j = 0;
-    int mode = 0;                    // 0 extend (rank probes), 1 contraction: read LCS[s], LCS[e]; 2 contraction: keep scanning
-    bool fresh = true, go_s = false, go_e = false, absent = false;
+    uint32_t s = 0, e = n, d = 0, urun = 0, prev_s = 0, prev_d = 0, j = 0;
+    bool fresh = true, absent = false;
     uint64_t word = packed[a >> 5];
     uint32_t c = (uint32_t)(word >> ((a & 31) * 2)) & 3u;
     while (j < len) {
-        // ---- one primary + one predicated secondary 16-byte load, address by state ----
-        const uint4* pa;
-        const uint4* pb;
-        bool need_b;
-        uint32_t os = 0, oe = 0;
-        if (mode == 0) {
-            uint32_t bs = s / 48u, be = e / 48u;
-            os = s - bs * 48u; oe = e - be * 48u;
-            pa = ix.rank + (size_t)bs * 4 + c;
-            pb = ix.rank + (size_t)be * 4 + c;
-            need_b = be != bs;
-        } else {
-            pa = lcs16 + (s >> 4);
-            pb = lcs16 + (e >> 4);
-            need_b = go_e && (e >> 4) != (s >> 4);
-        }
-        const uint4 va = NTC_LDG(pa);
-        const uint4 vb = need_b ? NTC_LDG(pb) : va;
-
-        if (mode == 0) {
-            if (fresh) {
-                // the block of the previous interval start also holds its Q bit: finish entry j-1
-                if (j > 0) {
-                    urun = (prev_d == k && entry_qbit(va, os)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
-                    uint32_t slot = (j - 1) & 3u;
-                    stage[slot * stride] = make_entry(prev_s, prev_d, urun);
-                    if (slot == 3u) {                                 // one full 32-byte sector
-                        ulonglong2 x0, x1;
-                        x0.x = stage[0]; x0.y = stage[stride]; x1.x = stage[2 * stride]; x1.y = stage[3 * stride];
-                        ulonglong2* dst = (ulonglong2*)(sc + (j - 4));
-                        dst[0] = x0; dst[1] = x1;
-                    }
+        const uint32_t bs = s / 48u, be = e / 48u;
+        const uint32_t os = s - bs * 48u, oe = e - be * 48u;
+        const uint4 va = NTC_LDG(ix.rank + (size_t)bs * 4 + c);
+        const uint32_t xs = NTC_LDG(ix.lcsx + s), xe = NTC_LDG(ix.lcsx + e);   // speculative: only used if the probe fails
+        const uint4 vb = (be != bs) ? NTC_LDG(ix.rank + (size_t)be * 4 + c) : va;
+        if (fresh) {
+            // the block of the previous interval start also holds its Q bit: finish entry j-1
+            if (j > 0) {
+                urun = (prev_d == k && entry_qbit(va, os)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
+                uint32_t slot = (j - 1) & 3u;
+                stage[slot * stride] = make_entry(prev_s, prev_d, urun);
+                if (slot == 3u) {                                     // one full 32-byte sector
+                    ulonglong2 x0, x1;
+                    x0.x = stage[0]; x0.y = stage[stride]; x1.x = stage[2 * stride]; x1.y = stage[3 * stride];
+                    ulonglong2* dst = (ulonglong2*)(sc + (j - 4));
+                    dst[0] = x0; dst[1] = x1;
                 }
-                fresh = false;
             }
-            uint32_t s2 = entry_rank(va, os), e2 = entry_rank(vb, oe);
-            if (s2 < e2) {                                            // extend_right succeeded
-                s = s2; e = e2; d = tmin(d + 1u, k);
-            } else if (s == 0 && e == n) {                            // base absent from the index
-                d = 0; absent = true;
-            } else {                                                  // contract_left
-                mode = 1; go_s = s > 0; go_e = e < n;
-                continue;
+            fresh = false;
+        }
+        const uint32_t s2 = entry_rank(va, os), e2 = entry_rank(vb, oe);
+        if (s2 >= e2 && !(s == 0 && e == n)) {
+            // contract_left (sbwt LcsArray): the interval is maximal for its level d, so both boundary
+            // LCS values are < d and the reference's loop -- which re-probes the same empty interval for
+            // every target above max(LCS[s], LCS[e]) -- ends up at that level with the interval widened
+            // to the nearest strictly smaller LCS on the side(s) that hold the maximum.
+            const int ls = s > 0 ? (int)lcsx_lcs(xs) : -1;
+            const int le = e < n ? (int)lcsx_lcs(xe) : -1;
+            const int t = tmax(ls, le);
+            if (t <= 0) { s = 0; e = n; d = 0; continue; }             // LCS >= 0 everywhere
+            if (ls == t) {
+                uint32_t dl = (xs >> 8) & 0xFFu;
+                s -= dl;
+                if (dl == 255u) while (s > 0 && lcsx_lcs(NTC_LDG(ix.lcsx + s)) >= (uint32_t)t) s--;
             }
-            prev_s = s; prev_d = d; fresh = true;
-            j++;
-            if (j < len) {
-                uint64_t p = a + j;
-                if ((p & 31) == 0) word = packed[p >> 5];
-                c = (uint32_t)(word >> ((p & 31) * 2)) & 3u;
+            if (le == t) {
+                uint32_t dr = (xe >> 16) & 0xFFu;
+                e += dr;
+                if (dr == 255u) while (e < n && lcsx_lcs(NTC_LDG(ix.lcsx + e)) >= (uint32_t)t) e++;
             }
-        } else {
-            if (mode == 1) {
-                // for targets above max(LCS[s], LCS[e]) the reference loop re-probes the same empty
-                // interval, so d jumps straight to that level (identical (d, I) afterwards)
-                int ls = go_s ? (int)chunk_byte(va, s & 15u) : -1;
-                int le = go_e ? (int)chunk_byte(vb, e & 15u) : -1;
-                t = (uint32_t)tmin((int)d - 1, tmax(ls, le));
-                d = t;
-                mode = 2;
-                if (t == 0) { s = 0; e = n; mode = 0; continue; }     // LCS >= 0 everywhere
-            }
-            // lcs[0] == 0 and lcs[n] == 0 stop both scans for t >= 1
-            if (go_s) {
-                int idx = last_lt_upto(va, t, s & 15u);
-                if (idx >= 0) { s = (s & ~15u) + (uint32_t)idx; go_s = false; }
-                else s = (s & ~15u) - 1u;
-            }
-            if (go_e) {
-                int idx = first_lt_from(vb, t, e & 15u);
-                if (idx >= 0) { e = (e & ~15u) + (uint32_t)idx; go_e = false; }
-                else e = (e & ~15u) + 16u;
-            }
-            if (!go_s && !go_e) mode = 0;
+            d = (uint32_t)t;
+            continue;
+        }
+        if (s2 < e2) { s = s2; e = e2; d = tmin(d + 1u, k); }         // extend_right succeeded
+        else { d = 0; absent = true; }                                // base absent from the index
+        prev_s = s; prev_d = d; fresh = true;
+        j++;
+        if (j < len) {
+            uint64_t p = a + j;
+            if ((p & 31) == 0) word = packed[p >> 5];
+            c = (uint32_t)(word >> ((p & 31) * 2)) & 3u;
         }
     }
     // tail: entries of the last, partial group of four + the final position
@@ -366,7 +292,7 @@ struct EmitSink {
             out[o] = word;
         } else {
             uint32_t end = v + 1;                                     // all nodes sharing the d-suffix
-            while (end < ix.n && NTC_LDG(ix.lcs + end) >= d_orig) end++;
+            while (end < ix.n && lcsx_lcs(NTC_LDG(ix.lcsx + end)) >= d_orig) end++;
             out[3 * o] = L; out[3 * o + 1] = v; out[3 * o + 2] = end;
         }
         o++;

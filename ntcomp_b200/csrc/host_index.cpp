@@ -99,6 +99,27 @@ void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out, int n_t
     });
 }
 
+void build_lcs_words(const ntc_index& idx, std::vector<uint32_t>* out) {
+    const uint64_t n = idx.n;
+    out->assign(n + 1, 0);
+    std::vector<uint32_t> stack;  // indices with strictly increasing LCS
+    std::vector<uint32_t> psv(n, 0);
+    for (uint64_t i = 0; i < n; i++) {
+        while (!stack.empty() && idx.lcs[stack.back()] >= idx.lcs[i]) stack.pop_back();
+        psv[i] = stack.empty() ? 0u : stack.back();
+        stack.push_back((uint32_t)i);
+    }
+    stack.clear();
+    for (uint64_t ii = n; ii-- > 0;) {
+        while (!stack.empty() && idx.lcs[stack.back()] >= idx.lcs[ii]) stack.pop_back();
+        uint64_t nsv = stack.empty() ? n : stack.back();  // LCS[n] = 0 sentinel is smaller than any LCS >= 1
+        uint32_t dl = idx.lcs[ii] ? (uint32_t)std::min<uint64_t>(255, ii - psv[ii]) : 0u;
+        uint32_t dr = idx.lcs[ii] ? (uint32_t)std::min<uint64_t>(255, nsv - ii) : 0u;
+        (*out)[ii] = (uint32_t)idx.lcs[ii] | (dl << 8) | (dr << 16);
+        stack.push_back((uint32_t)ii);
+    }
+}
+
 void build_jump_table(const ntc_index& idx, std::vector<uint64_t>* out, int n_threads) {
     const uint64_t n = idx.n;
     // one inverse-LF step: pred[C[c] + j] = position of the j-th one of row c; in-label = c

@@ -14,8 +14,7 @@ using namespace ntc;
 struct EmulIndex {
     std::vector<uint32_t> rank;
     std::vector<uint64_t> jump;
-    std::vector<uint8_t> lcs;
-    size_t lcs_off = 0;
+    std::vector<uint32_t> lcs;
     DevIndex dix;
 };
 
@@ -25,14 +24,9 @@ void* emul_index_create(const ntc_index* idx) {
     EmulIndex* e = new EmulIndex();
     build_rank_blocks(*idx, &e->rank, 2);
     build_jump_table(*idx, &e->jump, 2);
-    e->lcs = idx->lcs;
-    e->lcs.resize((idx->lcs.size() / 16 + 2) * 16 + 16, 0);
-    // 16-byte aligned view for the vectorised LCS scans
-    size_t mis = (16 - ((uintptr_t)e->lcs.data() & 15)) & 15;
-    e->lcs.insert(e->lcs.begin(), mis, 0);
-    e->lcs_off = mis;
+    build_lcs_words(*idx, &e->lcs);
     e->dix.rank = (const uint4*)e->rank.data();
-    e->dix.lcs = e->lcs.data() + e->lcs_off;
+    e->dix.lcsx = e->lcs.data();
     e->dix.jump = e->jump.data();
     e->dix.n = (uint32_t)idx->n;
     e->dix.k = idx->k;

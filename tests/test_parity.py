@@ -45,6 +45,11 @@ def small_cases(backend):
     cases = []
     for k, sizes in [(12, [400, 90]), (16, [3000]), (31, [20000, 500, 31, 30]), (91, [30000, 2000]), (255, [1500, 900, 300])]:
         cases.append(Case(backend, [helpers.random_seq(rng, n) for n in sizes], k))
+    # skewed index: almost no T, so a T in a read forces contract_left down to very short contexts
+    # (LCS runs longer than 255 nodes: the saturated-distance fallback of ms_kernel, and t == 0)
+    g = helpers.ALPHA[rng.integers(0, 3, size=30000)]
+    g[[5000, 12000, 12001, 20000, 29000]] = ord("T")
+    cases.append(Case(backend, [g], 16, add_revcomp=False))
     return cases
 
 
@@ -295,9 +300,12 @@ def test_device_resident_api_with_torch(small_cases):
     assert int(d_cnt[0].item()) == len(reads) and int(d_cnt[1].item()) == len(bases)
     assert (d_out[: len(bases)].cpu().numpy() == bases).all()
     assert (d_soff.cpu().numpy().view(np.uint64) == off).all()
+    want = helpers.fasta_text(reads, 99)
+    d_text = torch.zeros(len(want) + 64, dtype=torch.uint8, device=dev)
     for mis in (1, 3, 5, 6):                              # caller-misaligned output buffer
-        d_out.zero_()
-        case.ctx.decode_device(d_rec.data_ptr(), n_rec, 99, True, d_out.data_ptr() + mis, len(bases) + 40 * len(reads), 0, 0, d_cnt.data_ptr(), stream)
+        d_text.zero_()
+        case.ctx.decode_device(d_rec.data_ptr(), n_rec, 99, True, d_text.data_ptr() + mis, len(want), 0, 0, d_cnt.data_ptr(), stream)
         case.ctx.status(stream)
-        nbytes = int(d_cnt[1].item())
-        assert bytes(d_out[mis: mis + nbytes].cpu().numpy()) == helpers.fasta_text(reads, 99)
+        assert int(d_cnt[1].item()) == len(want)
+        assert bytes(d_text[mis: mis + len(want)].cpu().numpy()) == want
+        assert int(d_text[:mis].sum().item()) == 0 and int(d_text[mis + len(want):].sum().item()) == 0   # nothing outside the range
