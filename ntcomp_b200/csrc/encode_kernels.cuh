@@ -19,6 +19,7 @@ namespace ntc {
 
 constexpr int kPackThreads = 256;
 constexpr int kMsThreads = 128;
+constexpr uint32_t kSpecDepth = 20;   // speculate LCS loads while d < this (random matches in a 10^7-node index are ~12 long)
 constexpr uint32_t kLiteralMax = 11;  // bitnuc_threshold, src/encode.rs:137
 
 // ------------------------------------------------------------------------------------------
@@ -143,7 +144,12 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         const uint32_t bs = s / 48u, be = e / 48u;
         const uint32_t os = s - bs * 48u, oe = e - be * 48u;
         const uint4 va = NTC_LDG(ix.rank + (size_t)bs * 4 + c);
-        const uint32_t xs = NTC_LDG(ix.lcsx + s), xe = NTC_LDG(ix.lcsx + e);   // speculative: only used if the probe fails
+        // LCS words of both interval ends: loaded speculatively while the match is short (after a
+        // mismatch nearly every extension fails once or twice), on demand otherwise (rare) -- ncu r1 v3
+        // showed unconditional speculation doubling L2 sector traffic to 76% of the measured peak
+        const bool spec = d < kSpecDepth;
+        uint32_t xs = 0, xe = 0;
+        if (spec) { xs = NTC_LDG(ix.lcsx + s); xe = NTC_LDG(ix.lcsx + e); }
         const uint4 vb = (be != bs) ? NTC_LDG(ix.rank + (size_t)be * 4 + c) : va;
         if (fresh) {
             // the block of the previous interval start also holds its Q bit: finish entry j-1
@@ -166,6 +172,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
             // LCS values are < d and the reference's loop -- which re-probes the same empty interval for
             // every target above max(LCS[s], LCS[e]) -- ends up at that level with the interval widened
             // to the nearest strictly smaller LCS on the side(s) that hold the maximum.
+            if (!spec) { xs = NTC_LDG(ix.lcsx + s); xe = NTC_LDG(ix.lcsx + e); }
             const int ls = s > 0 ? (int)lcsx_lcs(xs) : -1;
             const int le = e < n ? (int)lcsx_lcs(xe) : -1;
             const int t = tmax(ls, le);
@@ -246,7 +253,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 
 constexpr uint32_t kMsStageWords = 1024;  // 8 KB of packed reads per block (128 reads x up to 256 bases); longer reads load from global
 
-__global__ void __launch_bounds__(kMsThreads, 12) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
+__global__ void __launch_bounds__(kMsThreads, 10) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
                                                         const uint64_t* __restrict__ offsets, uint64_t n_reads,
                                                         uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts,
                                                         uint32_t* __restrict__ status) {
