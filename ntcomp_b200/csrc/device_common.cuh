@@ -77,6 +77,70 @@ NTC_HD uint64_t packed_slice(const uint64_t* __restrict__ packed, uint64_t p, ui
     return len >= 32 ? v : (v & ((1ull << (2 * len)) - 1ull));
 }
 
+// ---- L2 residency control -------------------------------------------------------------------
+// The index (rank blocks, LCS words, jump table) is re-read at random and must stay in the 126 MB L2;
+// scratch / record / FASTA streams pass through once.  ncu r1 v4 showed 14.5 GB of DRAM reads in
+// ms_kernel -- index lines evicted by the 12 GB scratch stream -- so index loads carry an evict_last
+// policy and streaming stores an evict_first one (createpolicy + .L2::cache_hint).
+struct CachePolicy {
+    uint64_t keep, stream;
+};
+NTC_HD CachePolicy make_policies() {
+    CachePolicy p{0, 0};
+#if defined(__CUDA_ARCH__)
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p.keep));
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p.stream));
+#endif
+    return p;
+}
+NTC_HD uint4 ld16_keep(const uint4* ptr, uint64_t pol) {
+#if defined(__CUDA_ARCH__)
+    uint4 v;
+    asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr), "l"(pol));
+    return v;
+#else
+    (void)pol;
+    return *ptr;
+#endif
+}
+NTC_HD uint32_t ld4_keep(const uint32_t* ptr, uint64_t pol) {
+#if defined(__CUDA_ARCH__)
+    uint32_t v;
+    asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(ptr), "l"(pol));
+    return v;
+#else
+    (void)pol;
+    return *ptr;
+#endif
+}
+NTC_HD uint64_t ld8_keep(const uint64_t* ptr, uint64_t pol) {
+#if defined(__CUDA_ARCH__)
+    uint64_t v;
+    asm volatile("ld.global.nc.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(ptr), "l"(pol));
+    return v;
+#else
+    (void)pol;
+    return *ptr;
+#endif
+}
+// one full 32-byte sector in a single 256-bit store (sm_100: STG.E.256); dst 32-byte aligned
+NTC_HD void st32_stream(uint64_t* dst, uint64_t a, uint64_t b, uint64_t c, uint64_t d, uint64_t pol) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.L2::cache_hint.v4.b64 [%0], {%1,%2,%3,%4}, %5;" ::"l"(dst), "l"(a), "l"(b), "l"(c), "l"(d), "l"(pol) : "memory");
+#else
+    (void)pol;
+    dst[0] = a; dst[1] = b; dst[2] = c; dst[3] = d;
+#endif
+}
+NTC_HD void st8_stream(uint64_t* dst, uint64_t v, uint64_t pol) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.L2::cache_hint.b64 [%0], %1, %2;" ::"l"(dst), "l"(v), "l"(pol) : "memory");
+#else
+    (void)pol;
+    *dst = v;
+#endif
+}
+
 // ASCII of a 2-bit code
 NTC_HD uint8_t code_ascii(uint32_t c) { return (uint8_t)(0x54474341u >> (8 * (c & 3u))); }
 

@@ -135,6 +135,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         return;
     }
     const uint32_t n = ix.n, k = ix.k;
+    const CachePolicy pol = make_policies();
     uint64_t* __restrict__ sc = scratch + scratch_base(a, r);
     uint32_t s = 0, e = n, d = 0, urun = 0, prev_s = 0, prev_d = 0, j = 0;
     bool fresh = true, absent = false;
@@ -143,14 +144,14 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
     while (j < len) {
         const uint32_t bs = s / 48u, be = e / 48u;
         const uint32_t os = s - bs * 48u, oe = e - be * 48u;
-        const uint4 va = NTC_LDG(ix.rank + (size_t)bs * 4 + c);
+        const uint4 va = ld16_keep(ix.rank + (size_t)bs * 4 + c, pol.keep);
         // LCS words of both interval ends: loaded speculatively while the match is short (after a
         // mismatch nearly every extension fails once or twice), on demand otherwise (rare) -- ncu r1 v3
         // showed unconditional speculation doubling L2 sector traffic to 76% of the measured peak
         const bool spec = d < kSpecDepth;
         uint32_t xs = 0, xe = 0;
-        if (spec) { xs = NTC_LDG(ix.lcsx + s); xe = NTC_LDG(ix.lcsx + e); }
-        const uint4 vb = (be != bs) ? NTC_LDG(ix.rank + (size_t)be * 4 + c) : va;
+        if (spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = ld4_keep(ix.lcsx + e, pol.keep); }
+        const uint4 vb = (be != bs) ? ld16_keep(ix.rank + (size_t)be * 4 + c, pol.keep) : va;
         if (fresh) {
             // the block of the previous interval start also holds its Q bit: finish entry j-1
             if (j > 0) {
@@ -158,10 +159,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
                 uint32_t slot = (j - 1) & 3u;
                 stage[slot * stride] = make_entry(prev_s, prev_d, urun);
                 if (slot == 3u) {                                     // one full 32-byte sector
-                    ulonglong2 x0, x1;
-                    x0.x = stage[0]; x0.y = stage[stride]; x1.x = stage[2 * stride]; x1.y = stage[3 * stride];
-                    ulonglong2* dst = (ulonglong2*)(sc + (j - 4));
-                    dst[0] = x0; dst[1] = x1;
+                    st32_stream(sc + (j - 4), stage[0], stage[stride], stage[2 * stride], stage[3 * stride], pol.stream);
                 }
             }
             fresh = false;
@@ -172,7 +170,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
             // LCS values are < d and the reference's loop -- which re-probes the same empty interval for
             // every target above max(LCS[s], LCS[e]) -- ends up at that level with the interval widened
             // to the nearest strictly smaller LCS on the side(s) that hold the maximum.
-            if (!spec) { xs = NTC_LDG(ix.lcsx + s); xe = NTC_LDG(ix.lcsx + e); }
+            if (!spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = ld4_keep(ix.lcsx + e, pol.keep); }
             const int ls = s > 0 ? (int)lcsx_lcs(xs) : -1;
             const int le = e < n ? (int)lcsx_lcs(xe) : -1;
             const int t = tmax(ls, le);
