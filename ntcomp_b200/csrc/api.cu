@@ -23,6 +23,7 @@ struct CountLoad {
 };
 
 inline unsigned blocks_for(uint64_t n, unsigned per) { return (unsigned)((n + per - 1) / per); }
+constexpr uint64_t kMaxDecodeChunks = 256;
 
 // Brackets the launches of one kernel class with CUDA events on the launching stream when
 // profiling is on; always counts launches.
@@ -69,31 +70,35 @@ int32_t status_to_code(uint32_t st) {
 }
 
 // ------------------------------------------------------------------------------------------
-// encode pipeline on device buffers.  MODE 0 records, 1 triples.  carry (device, 2 x u64, may be
-// null) is added to every record offset; the grand total lands in totals_out (device, 2 x u64).
+// encode pipeline on device buffers, using the workspaces of `lane` on stream `st`.
+// MODE 0 records, 1 triples.  carry (device, 2 x u64, may be null) is added to every record
+// offset; the grand total lands in totals_out (device, 2 x u64).  `rel` (device u64, may be null):
+// records are written at out[offset - *rel] (chunked host path: out is the chunk's staging buffer).
+// wait_scan: an event the scan must wait for (the previous chunk's scan on the other lane).
 // ------------------------------------------------------------------------------------------
-int32_t encode_pipeline(ntc_ctx* ctx, int mode, const uint8_t* d_bases, const uint64_t* d_offsets, uint64_t n_reads,
+int32_t encode_pipeline(ntc_ctx* ctx, Lane& lane, int mode, const uint8_t* d_bases, const uint64_t* d_offsets, uint64_t n_reads,
                         uint64_t n_bases, uint64_t* d_out, uint64_t cap, uint64_t* d_rec_offsets, const uint64_t* carry,
-                        uint64_t* totals_out, cudaStream_t st) {
+                        uint64_t* totals_out, const uint64_t* rel, cudaEvent_t wait_scan, cudaStream_t st) {
     if (n_reads == 0) {
+        if (wait_scan) NTC_CUDA_TRY(cudaStreamWaitEvent(st, wait_scan, 0));
         NTC_CUDA_TRY(cudaMemsetAsync(totals_out, 0, 16, st));
         if (carry) NTC_CUDA_TRY(cudaMemcpyAsync(totals_out, carry, 16, cudaMemcpyDeviceToDevice, st));
         if (d_rec_offsets) NTC_CUDA_TRY(cudaMemcpyAsync(d_rec_offsets, totals_out, 8, cudaMemcpyDeviceToDevice, st));
         return NTC_OK;
     }
     const uint64_t n_words = n_bases / 32 + 2;
-    NTC_CUDA_TRY(ensure(&ctx->packed, (n_words + 4) * 8));
-    NTC_CUDA_TRY(ensure(&ctx->scratch, scratch_entries(n_bases, n_reads) * 8));
-    NTC_CUDA_TRY(ensure(&ctx->counts, n_reads * 4));
-    NTC_CUDA_TRY(ensure(&ctx->tiles, scan_num_tiles(n_reads) * sizeof(Pair64)));
+    NTC_CUDA_TRY(ensure(&lane.packed, (n_words + 4) * 8));
+    NTC_CUDA_TRY(ensure(&lane.scratch, scratch_entries(n_bases, n_reads) * 8));
+    NTC_CUDA_TRY(ensure(&lane.counts, n_reads * 4));
+    NTC_CUDA_TRY(ensure(&lane.tiles, scan_num_tiles(n_reads) * sizeof(Pair64)));
     uint64_t* rec_off = d_rec_offsets;
     if (!rec_off) {
-        NTC_CUDA_TRY(ensure(&ctx->rec_off, (n_reads + 1) * 8));
-        rec_off = (uint64_t*)ctx->rec_off.p;
+        NTC_CUDA_TRY(ensure(&lane.rec_off, (n_reads + 1) * 8));
+        rec_off = (uint64_t*)lane.rec_off.p;
     }
-    uint64_t* packed = (uint64_t*)ctx->packed.p;
-    uint64_t* scratch = (uint64_t*)ctx->scratch.p;
-    uint32_t* counts = (uint32_t*)ctx->counts.p;
+    uint64_t* packed = (uint64_t*)lane.packed.p;
+    uint64_t* scratch = (uint64_t*)lane.scratch.p;
+    uint32_t* counts = (uint32_t*)lane.counts.p;
 
     if (n_bases) {
         Timed t(ctx, KC_PACK, st);
@@ -105,44 +110,41 @@ int32_t encode_pipeline(ntc_ctx* ctx, int mode, const uint8_t* d_bases, const ui
         ms_kernel<<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
                                                                           ctx->d_status);
     }
+    if (wait_scan) NTC_CUDA_TRY(cudaStreamWaitEvent(st, wait_scan, 0));
     {
         Timed t(ctx, KC_SCAN, st, 3);
-        exclusive_scan_pairs(CountLoad{counts}, n_reads, (Pair64*)ctx->tiles.p, carry, totals_out, rec_off, nullptr, st);
+        exclusive_scan_pairs(CountLoad{counts}, n_reads, (Pair64*)lane.tiles.p, carry, totals_out, rec_off, nullptr, st);
     }
+    if (lane.ev_scan) NTC_CUDA_TRY(cudaEventRecord(lane.ev_scan, st));
     {
         Timed t(ctx, KC_EMIT, st);
         if (mode == 0)
             emit_kernel<0><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                                   rec_off, d_out, cap, ctx->d_status);
+                                                                                   rec_off, rel, d_out, cap, ctx->d_status);
         else
             emit_kernel<1><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                                   rec_off, d_out, cap, ctx->d_status);
+                                                                                   rec_off, rel, d_out, cap, ctx->d_status);
     }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
 }
 
 // ------------------------------------------------------------------------------------------
-// decode pipeline on device buffers
+// decode on device buffers: scans + sequence bookkeeping, then the walk over records [i0, i1)
 // ------------------------------------------------------------------------------------------
-int32_t decode_pipeline(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* d_out,
-                        uint64_t cap, uint64_t* d_seq_offsets, uint64_t cap_seqs, uint64_t* d_counts, cudaStream_t st) {
-    if (n_rec == 0) {
-        NTC_CUDA_TRY(cudaMemsetAsync(d_counts, 0, 16, st));
-        if (d_seq_offsets) NTC_CUDA_TRY(cudaMemsetAsync(d_seq_offsets, 0, 8, st));
-        return NTC_OK;
-    }
+int32_t decode_prepare(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint64_t cap,
+                       uint64_t* d_seq_offsets, uint64_t cap_seqs, uint64_t* d_counts, cudaStream_t st) {
     NTC_CUDA_TRY(ensure(&ctx->base_off, (n_rec + 1) * 8));
     NTC_CUDA_TRY(ensure(&ctx->seq_idx, (n_rec + 1) * 8));
     NTC_CUDA_TRY(ensure(&ctx->seq_first, (n_rec + 1) * 8));
-    NTC_CUDA_TRY(ensure(&ctx->tiles, scan_num_tiles(n_rec) * sizeof(Pair64)));
+    NTC_CUDA_TRY(ensure(&ctx->dec_tiles, scan_num_tiles(n_rec) * sizeof(Pair64)));
     uint64_t* base_off = (uint64_t*)ctx->base_off.p;
     uint64_t* seq_idx = (uint64_t*)ctx->seq_idx.p;
     uint64_t* seq_first = (uint64_t*)ctx->seq_first.p;
-    uint64_t* totals = ctx->d_totals + 4;
+    uint64_t* totals = ctx->d_totals + 6;
     {
         Timed t(ctx, KC_DSCAN, st, 3);
-        exclusive_scan_pairs(RecordLoad{d_records}, n_rec, (Pair64*)ctx->tiles.p, nullptr, totals, base_off, seq_idx, st);
+        exclusive_scan_pairs(RecordLoad{d_records}, n_rec, (Pair64*)ctx->dec_tiles.p, nullptr, totals, base_off, seq_idx, st);
     }
     {
         Timed t(ctx, KC_SEQ, st, 2);
@@ -150,13 +152,31 @@ int32_t decode_pipeline(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec,
         seq_offsets_kernel<<<blocks_for(n_rec + 1, 256), 256, 0, st>>>(base_off, seq_first, totals, n_rec, d_seq_offsets, cap_seqs, first_no,
                                                                        fasta, cap, d_counts, ctx->d_status);
     }
-    {
-        Timed t(ctx, KC_WALK, st);
-        walk_kernel<<<blocks_for(n_rec, 128), 128, 0, st>>>(ctx->dix, d_records, n_rec, base_off, seq_idx, seq_first, totals, first_no, fasta,
-                                                            d_out, cap, d_counts, ctx->d_status);
-    }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
+}
+
+int32_t decode_walk(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* d_out, uint64_t cap,
+                    const uint64_t* d_counts, uint64_t i0, uint64_t i1, cudaStream_t st) {
+    if (i1 <= i0) return NTC_OK;
+    Timed t(ctx, KC_WALK, st);
+    walk_kernel<<<blocks_for(i1 - i0, 128), 128, 0, st>>>(ctx->dix, d_records, n_rec, (const uint64_t*)ctx->base_off.p,
+                                                          (const uint64_t*)ctx->seq_idx.p, (const uint64_t*)ctx->seq_first.p,
+                                                          ctx->d_totals + 6, first_no, fasta, d_out, cap, d_counts, ctx->d_status, i0, i1);
+    NTC_CUDA_TRY(cudaGetLastError());
+    return NTC_OK;
+}
+
+int32_t decode_pipeline(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* d_out,
+                        uint64_t cap, uint64_t* d_seq_offsets, uint64_t cap_seqs, uint64_t* d_counts, cudaStream_t st) {
+    if (n_rec == 0) {
+        NTC_CUDA_TRY(cudaMemsetAsync(d_counts, 0, 16, st));
+        if (d_seq_offsets) NTC_CUDA_TRY(cudaMemsetAsync(d_seq_offsets, 0, 8, st));
+        return NTC_OK;
+    }
+    int32_t rc = decode_prepare(ctx, d_records, n_rec, first_no, fasta, cap, d_seq_offsets, cap_seqs, d_counts, st);
+    if (rc) return rc;
+    return decode_walk(ctx, d_records, n_rec, first_no, fasta, d_out, cap, d_counts, 0, n_rec, st);
 }
 
 int32_t read_status(ntc_ctx* ctx, cudaStream_t st) {
@@ -188,7 +208,7 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     ctx->n = idx->n;
     if (const char* env = getenv("NTC_MAX_CHUNK_BASES")) {
         unsigned long long v = strtoull(env, nullptr, 10);
-        if (v >= 1024) ctx->max_chunk_bases = v;
+        if (v >= 1024) { ctx->max_chunk_bases = v; ctx->max_chunk_bytes = v; }
     }
     int threads = (int)std::max(1u, std::thread::hardware_concurrency());
     std::vector<uint32_t> rank;
@@ -217,7 +237,15 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     cudaMemset(ctx->d_status, 0, 16);
     cudaMemset(ctx->d_totals, 0, 64);
     cudaMemset(ctx->d_counts, 0, 32);
-    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+    for (Lane& ln : ctx->lanes) {
+        if ((e = cudaStreamCreateWithFlags(&ln.stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+        if ((e = cudaEventCreateWithFlags(&ln.ev_scan, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&ln.ev_done, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+        if ((e = cudaHostAlloc((void**)&ln.h_land, 64, cudaHostAllocDefault)) != cudaSuccess) return fail("cudaHostAlloc", e);
+    }
+    ctx->stream = ctx->lanes[0].stream;
+    if ((e = cudaEventCreateWithFlags(&ctx->ev_walk, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaHostAlloc((void**)&ctx->h_bounds, 2 * 8 * (kMaxDecodeChunks + 2), cudaHostAllocDefault)) != cudaSuccess) return fail("cudaHostAlloc", e);
     ctx->dix.rank = (const uint4*)ctx->d_rank;
     ctx->dix.lcsx = (const uint32_t*)ctx->d_lcs;
     ctx->dix.jump = (const uint64_t*)ctx->d_jump;
@@ -230,11 +258,22 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
 void ntc_ctx_destroy(ntc_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+    cudaDeviceSynchronize();
+    for (Lane& ln : ctx->lanes) {
+        if (ln.stream) cudaStreamDestroy(ln.stream);
+        if (ln.ev_scan) cudaEventDestroy(ln.ev_scan);
+        if (ln.ev_done) cudaEventDestroy(ln.ev_done);
+        if (ln.h_land) cudaFreeHost(ln.h_land);
+        DevBuf* lb[] = {&ln.packed, &ln.scratch, &ln.counts, &ln.tiles, &ln.rec_off, &ln.st_in, &ln.st_off, &ln.st_out, &ln.st_out2};
+        for (DevBuf* b : lb) release(b);
+    }
+    if (ctx->ev_walk) cudaEventDestroy(ctx->ev_walk);
+    if (ctx->h_bounds) cudaFreeHost(ctx->h_bounds);
+    for (auto& sp : ctx->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
+    for (auto ev : ctx->event_pool) cudaEventDestroy(ev);
     cudaFree(ctx->d_rank); cudaFree(ctx->d_lcs); cudaFree(ctx->d_jump);
     cudaFree(ctx->d_status); cudaFree(ctx->d_totals); cudaFree(ctx->d_counts);
-    DevBuf* bufs[] = {&ctx->packed, &ctx->scratch, &ctx->counts, &ctx->tiles, &ctx->rec_off, &ctx->base_off, &ctx->seq_idx,
-                      &ctx->seq_first, &ctx->st_in, &ctx->st_off, &ctx->st_out, &ctx->st_out2};
+    DevBuf* bufs[] = {&ctx->base_off, &ctx->seq_idx, &ctx->seq_first, &ctx->dec_tiles, &ctx->bounds};
     for (DevBuf* b : bufs) release(b);
     delete ctx;
 }
@@ -255,7 +294,8 @@ int32_t ntc_encode_device(ntc_ctx* ctx, const uint8_t* d_bases, const uint64_t* 
     if (!ctx || !d_offsets || (!d_records && cap)) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
     NTC_CUDA_TRY(cudaSetDevice(ctx->device));
     cudaStream_t st = (cudaStream_t)stream;
-    int32_t rc = encode_pipeline(ctx, 0, d_bases, d_offsets, n_reads, n_bases, d_records, cap, d_rec_offsets, nullptr, ctx->d_totals, st);
+    int32_t rc = encode_pipeline(ctx, ctx->lanes[0], 0, d_bases, d_offsets, n_reads, n_bases, d_records, cap, d_rec_offsets, nullptr,
+                                 ctx->d_totals, nullptr, nullptr, st);
     if (rc) return rc;
     if (d_counts) { Timed t(ctx, KC_MISC, st); copy_totals_kernel<<<1, 1, 0, st>>>(ctx->d_totals, d_counts); }
     return NTC_OK;

@@ -20,9 +20,14 @@ struct DevBuf {
     size_t cap = 0;
 };
 
-struct PinBuf {
-    void* p = nullptr;
-    size_t cap = 0;
+// One pipeline lane of the host-buffer API: its own stream, encode workspaces and staging buffers, so
+// chunk i+1's H2D copy and kernels overlap chunk i's D2H copy (two lanes, ping-pong).
+struct Lane {
+    cudaStream_t stream = nullptr;
+    DevBuf packed, scratch, counts, tiles, rec_off;   // encode workspaces
+    DevBuf st_in, st_off, st_out, st_out2;            // staging for host buffers
+    cudaEvent_t ev_scan = nullptr, ev_done = nullptr;
+    uint64_t* h_land = nullptr;                       // pinned landing zone: [0..1] totals, [2] status
 };
 }  // namespace ntc
 
@@ -37,18 +42,18 @@ struct ntc_ctx {
     uint64_t n = 0;
 
     uint32_t* d_status = nullptr;   // [4]
-    uint64_t* d_totals = nullptr;   // [8]: ping-pong scan totals (2 x Pair64) + spare
+    uint64_t* d_totals = nullptr;   // [8]: ring of 3 encode scan totals (Pair64 each) + decode totals at [6]
     uint64_t* d_counts = nullptr;   // [4]: internal counts for the host-buffer API
     uint64_t launches = 0;
-    uint64_t max_chunk_bases = 1ull << 30;
+    uint64_t max_chunk_bases = 96ull << 20;   // host-buffer API chunk (overlap granularity); NTC_MAX_CHUNK_BASES overrides
+    uint64_t max_chunk_bytes = 128ull << 20;  // decode output chunk for D2H overlap
 
-    // encode workspaces
-    ntc::DevBuf packed, scratch, counts, tiles, rec_off;
+    ntc::Lane lanes[2];             // lanes[0] also serves the device-resident API (on the caller's stream)
     // decode workspaces
-    ntc::DevBuf base_off, seq_idx, seq_first;
-    // staging for the host-buffer API
-    ntc::DevBuf st_in, st_off, st_out, st_out2;
-    cudaStream_t stream = nullptr;  // internal stream of the host-buffer API
+    ntc::DevBuf base_off, seq_idx, seq_first, dec_tiles, bounds;
+    uint64_t* h_bounds = nullptr;   // pinned, decode chunk bounds
+    cudaStream_t stream = nullptr;  // == lanes[0].stream
+    cudaEvent_t ev_walk = nullptr;
 
     // optional per-kernel-class timing with CUDA events on the launching stream (bench.py roofline)
     bool profiling = false;

@@ -232,9 +232,35 @@ __global__ void __launch_bounds__(128) walk_kernel(DevIndex ix, const uint64_t* 
                                                    const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_idx,
                                                    const uint64_t* __restrict__ seq_first, const uint64_t* __restrict__ totals,
                                                    uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes,
-                                                   const uint64_t* __restrict__ counts, uint32_t* __restrict__ status) {
-    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_first, totals, first_no, fasta, out, cap_bytes, counts, status,
-                (uint64_t)blockIdx.x * 128 + threadIdx.x);
+                                                   const uint64_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t i0,
+                                                   uint64_t i1) {
+    // records [i0, i1): the host-buffer API walks the stream in chunks so D2H overlaps the next chunk
+    uint64_t i = i0 + (uint64_t)blockIdx.x * 128 + threadIdx.x;
+    if (i >= i1) return;
+    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_first, totals, first_no, fasta, out, cap_bytes, counts, status, i);
+}
+
+// chunk plan for the host-buffer API: chunk j covers sequences [j*S, (j+1)*S); writes the first record
+// and the first output byte of every chunk (entry n_chunks = end)
+NTC_HD void chunk_bounds_thread(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
+                                const uint64_t* __restrict__ totals, const uint64_t* __restrict__ counts, uint64_t n_rec,
+                                uint64_t first_no, int fasta, uint64_t seqs_per_chunk, uint64_t n_chunks, uint64_t* __restrict__ bounds,
+                                uint64_t j) {
+    if (j > n_chunks) return;
+    const uint64_t n_seqs = totals[1];
+    uint64_t sj = j * seqs_per_chunk;
+    if (sj >= n_seqs || j == n_chunks) { bounds[2 * j] = n_rec; bounds[2 * j + 1] = counts[1]; return; }
+    const uint64_t base0 = base_off[seq_first[0]];
+    uint64_t byte = base_off[seq_first[sj]] - base0;
+    if (fasta) byte += fasta_overhead(first_no, sj) - (6 + dec_digits(first_no + sj));   // start of the header line
+    bounds[2 * j] = seq_first[sj];
+    bounds[2 * j + 1] = byte;
+}
+__global__ void chunk_bounds_kernel(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
+                                    const uint64_t* __restrict__ totals, const uint64_t* __restrict__ counts, uint64_t n_rec,
+                                    uint64_t first_no, int fasta, uint64_t seqs_per_chunk, uint64_t n_chunks, uint64_t* __restrict__ bounds) {
+    chunk_bounds_thread(base_off, seq_first, totals, counts, n_rec, first_no, fasta, seqs_per_chunk, n_chunks, bounds,
+                        (uint64_t)blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 }  // namespace ntc

@@ -308,14 +308,17 @@ struct EmitSink {
 template <int MODE>
 NTC_HD void emit_thread(const DevIndex& ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offsets, uint64_t n_reads,
                         const uint64_t* __restrict__ scratch, const uint32_t* __restrict__ counts, const uint64_t* __restrict__ rec_offsets,
-                        uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status, uint64_t r) {
+                        const uint64_t* __restrict__ rel, uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status, uint64_t r) {
+    // rec_offsets are absolute (a carry from earlier chunks is folded in); `out` is this chunk's
+    // buffer, so positions are taken relative to *rel (the number of records before the chunk)
     if (r >= n_reads) return;
     if (counts[r] == 0) return;
+    const uint64_t rel0 = rel ? NTC_LDG(rel) : 0;
     const uint64_t base0 = NTC_LDG(offsets);
     const uint64_t a = offsets[r] - base0;
     const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
-    if (rec_offsets[r + 1] > cap) { NTC_ATOMIC_OR(status, (uint32_t)ST_CAPACITY); return; }
-    EmitSink<MODE> sink{ix, packed, out, a, rec_offsets[r], 1};
+    if (rec_offsets[r + 1] - rel0 > cap) { NTC_ATOMIC_OR(status, (uint32_t)ST_CAPACITY); return; }
+    EmitSink<MODE> sink{ix, packed, out, a, rec_offsets[r] - rel0, 1};
     segment_read(scratch + scratch_base(a, r), len, ix.k, sink);
 }
 
@@ -323,9 +326,9 @@ template <int MODE>
 __global__ void __launch_bounds__(kMsThreads) emit_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
                                                           const uint64_t* __restrict__ offsets, uint64_t n_reads,
                                                           const uint64_t* __restrict__ scratch, const uint32_t* __restrict__ counts,
-                                                          const uint64_t* __restrict__ rec_offsets, uint64_t* __restrict__ out,
-                                                          uint64_t cap, uint32_t* __restrict__ status) {
-    emit_thread<MODE>(ix, packed, offsets, n_reads, scratch, counts, rec_offsets, out, cap, status,
+                                                          const uint64_t* __restrict__ rec_offsets, const uint64_t* __restrict__ rel,
+                                                          uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status) {
+    emit_thread<MODE>(ix, packed, offsets, n_reads, scratch, counts, rec_offsets, rel, out, cap, status,
                       (uint64_t)blockIdx.x * kMsThreads + threadIdx.x);
 }
 

@@ -59,8 +59,8 @@ uint32_t emul_encode(void* ep, const uint8_t* bases, const uint64_t* offsets, ui
     std::vector<uint64_t> roff(n_reads + 1, 0);
     for (uint64_t r = 0; r < n_reads; r++) roff[r + 1] = roff[r] + counts[r];   // exclusive scan (scan.cuh on the GPU)
     for (uint64_t r = 0; r < n_reads; r++) {
-        if (mode == 0) emit_thread<0>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), out, cap, &status, r);
-        else emit_thread<1>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), out, cap, &status, r);
+        if (mode == 0) emit_thread<0>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), nullptr, out, cap, &status, r);
+        else emit_thread<1>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), nullptr, out, cap, &status, r);
     }
     *n_records = roff[n_reads];
     if (rec_offsets) memcpy(rec_offsets, roff.data(), (n_reads + 1) * 8);

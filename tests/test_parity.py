@@ -240,6 +240,16 @@ def test_chunked_host_path_matches_unchunked(monkeypatch, small_cases):
     tri, _ = case0.ctx.encode_sequence_batch(bases, off)
     tri2, _ = ctx2.encode_sequence_batch(bases, off)
     assert (tri == tri2).all()
+    # chunked decode (walk per chunk of sequences, D2H overlapped) == one-shot decode == input
+    db, doff = ctx2.decode_batch(rec2)
+    assert (db == bases).all() and (doff == off).all()
+    text, n = ctx2.decode_fasta(rec2, 12345)
+    assert text == helpers.fasta_text(reads, 12345) and n == len(reads)
+    with pytest.raises(nt.NtcError) as e:                        # an error in a middle chunk drains both lanes cleanly
+        ctx2.encode_batch(*nt.concat_reads(reads[:200] + [b"ACGTNNNN"] + reads[200:]))
+    assert e.value.code == 5
+    rec3, roff3 = ctx2.encode_batch(bases, off)
+    assert (rec3 == rec).all() and (roff3 == roff).all()
 
 
 @pytest.mark.parametrize("cfg", ["C2-small", "C3-small", "C5-small"])
