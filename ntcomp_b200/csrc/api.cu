@@ -251,6 +251,7 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     ctx->dix.jump = (const uint64_t*)ctx->d_jump;
     ctx->dix.n = (uint32_t)idx->n;
     ctx->dix.k = idx->k;
+    spec_window(idx->n, &ctx->dix.spec_lo, &ctx->dix.spec_span);
     *out = ctx;
     return NTC_OK;
 }

@@ -36,10 +36,11 @@ enum : uint32_t {
 struct DevIndex {
     const uint4* rank;     // [(n/48+1) * 4] entries {C[c] + ones before block, row bits 0-31,
                            //   row bits 32-47 | Q bits 0-15 << 16, Q bits 16-47}; c = entry index & 3
-    const uint32_t* lcsx;  // [n + 1] LCS | dist to previous smaller LCS << 8 | dist to next smaller LCS << 16; [n] = 0
+    const uint32_t* lcsx;  // [n + 1] LCS[i] | dist to previous smaller << 8 | LCS[i+1] << 16 | dist to next smaller of i+1 << 24
     const uint64_t* jump;  // [n] pred^16 | chars16 << 32
     uint32_t n;
     uint32_t k;
+    uint32_t spec_lo, spec_span;  // ms_kernel speculates LCS loads while spec_lo <= d < spec_lo + spec_span
 };
 
 // scratch entry written by the matching-statistics pass, one per base:

@@ -19,7 +19,6 @@ namespace ntc {
 
 constexpr int kPackThreads = 256;
 constexpr int kMsThreads = 128;
-constexpr uint32_t kSpecDepth = 20;   // speculate LCS loads while d < this (random matches in a 10^7-node index are ~12 long)
 constexpr uint32_t kLiteralMax = 11;  // bitnuc_threshold, src/encode.rs:137
 
 // ------------------------------------------------------------------------------------------
@@ -116,8 +115,10 @@ struct CountSink {
 NTC_HD uint64_t scratch_base(uint64_t a, uint64_t r) { return (a + 4 * r) & ~3ull; }
 inline uint64_t scratch_entries(uint64_t n_bases, uint64_t n_reads) { return n_bases + 4 * n_reads + 8; }
 
-// LCS word of node i: bits 0-7 LCS[i], 8-15 min(255, i - PSV(i)), 16-23 min(255, NSV(i) - i) where
-// PSV / NSV are the nearest positions left / right whose LCS is strictly smaller than LCS[i].
+// LCS word i: bits 0-7 LCS[i], 8-15 min(255, i - PSV(i)), 16-23 LCS[i+1], 24-31 min(255, NSV(i+1) - (i+1)),
+// PSV / NSV = nearest position left / right whose LCS is strictly smaller.  A singleton interval
+// [s, s+1) -- the common case -- finds everything contract_left needs in the single word s; a wider
+// interval [s, e) reads words s and e-1.
 NTC_HD uint32_t lcsx_lcs(uint32_t x) { return x & 0xFFu; }
 
 // `stage` = 4 x blockDim u64 staging slots of this thread's block (shared memory on the GPU),
@@ -145,12 +146,14 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         const uint32_t bs = s / 48u, be = e / 48u;
         const uint32_t os = s - bs * 48u, oe = e - be * 48u;
         const uint4 va = ld16_keep(ix.rank + (size_t)bs * 4 + c, pol.keep);
-        // LCS words of both interval ends: loaded speculatively while the match is short (after a
-        // mismatch nearly every extension fails once or twice), on demand otherwise (rare) -- ncu r1 v3
-        // showed unconditional speculation doubling L2 sector traffic to 76% of the measured peak
-        const bool spec = d < kSpecDepth;
+        // LCS words of the interval ends: loaded speculatively only while d is in the window where
+        // extensions of chance matches fail (around log4(n_sets), set by the host), on demand otherwise
+        // (ncu r1 v3: unconditional speculation doubled the sector traffic; v5: d < 20 still spent 39% of
+        // all load sectors on it)
+        const bool spec = d - ix.spec_lo < ix.spec_span;   // unsigned: spec_lo <= d < spec_lo + spec_span
+        const bool single = e == s + 1u;
         uint32_t xs = 0, xe = 0;
-        if (spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = ld4_keep(ix.lcsx + e, pol.keep); }
+        if (spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = single ? xs : ld4_keep(ix.lcsx + (e - 1u), pol.keep); }
         const uint4 vb = (be != bs) ? ld16_keep(ix.rank + (size_t)be * 4 + c, pol.keep) : va;
         if (fresh) {
             // the block of the previous interval start also holds its Q bit: finish entry j-1
@@ -170,9 +173,9 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
             // LCS values are < d and the reference's loop -- which re-probes the same empty interval for
             // every target above max(LCS[s], LCS[e]) -- ends up at that level with the interval widened
             // to the nearest strictly smaller LCS on the side(s) that hold the maximum.
-            if (!spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = ld4_keep(ix.lcsx + e, pol.keep); }
-            const int ls = s > 0 ? (int)lcsx_lcs(xs) : -1;
-            const int le = e < n ? (int)lcsx_lcs(xe) : -1;
+            if (!spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = single ? xs : ld4_keep(ix.lcsx + (e - 1u), pol.keep); }
+            const int ls = s > 0 ? (int)lcsx_lcs(xs) : -1;              // LCS[s]   (low half of word s)
+            const int le = e < n ? (int)((xe >> 16) & 0xFFu) : -1;      // LCS[e]   (high half of word e-1)
             const int t = tmax(ls, le);
             if (t <= 0) { s = 0; e = n; d = 0; continue; }             // LCS >= 0 everywhere
             if (ls == t) {
@@ -181,7 +184,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
                 if (dl == 255u) while (s > 0 && lcsx_lcs(NTC_LDG(ix.lcsx + s)) >= (uint32_t)t) s--;
             }
             if (le == t) {
-                uint32_t dr = (xe >> 16) & 0xFFu;
+                uint32_t dr = xe >> 24;
                 e += dr;
                 if (dr == 255u) while (e < n && lcsx_lcs(NTC_LDG(ix.lcsx + e)) >= (uint32_t)t) e++;
             }

@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cstdio>
+#include <cmath>
 #include <cstring>
 #include <thread>
 
@@ -101,23 +102,35 @@ void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out, int n_t
 
 void build_lcs_words(const ntc_index& idx, std::vector<uint32_t>* out) {
     const uint64_t n = idx.n;
-    out->assign(n + 1, 0);
+    std::vector<uint8_t> dl(n + 1, 0), dr(n + 1, 0);
     std::vector<uint32_t> stack;  // indices with strictly increasing LCS
-    std::vector<uint32_t> psv(n, 0);
     for (uint64_t i = 0; i < n; i++) {
         while (!stack.empty() && idx.lcs[stack.back()] >= idx.lcs[i]) stack.pop_back();
-        psv[i] = stack.empty() ? 0u : stack.back();
+        uint64_t psv = stack.empty() ? 0 : stack.back();
+        dl[i] = idx.lcs[i] ? (uint8_t)std::min<uint64_t>(255, i - psv) : 0;
         stack.push_back((uint32_t)i);
     }
     stack.clear();
-    for (uint64_t ii = n; ii-- > 0;) {
-        while (!stack.empty() && idx.lcs[stack.back()] >= idx.lcs[ii]) stack.pop_back();
+    for (uint64_t i = n; i-- > 0;) {
+        while (!stack.empty() && idx.lcs[stack.back()] >= idx.lcs[i]) stack.pop_back();
         uint64_t nsv = stack.empty() ? n : stack.back();  // LCS[n] = 0 sentinel is smaller than any LCS >= 1
-        uint32_t dl = idx.lcs[ii] ? (uint32_t)std::min<uint64_t>(255, ii - psv[ii]) : 0u;
-        uint32_t dr = idx.lcs[ii] ? (uint32_t)std::min<uint64_t>(255, nsv - ii) : 0u;
-        (*out)[ii] = (uint32_t)idx.lcs[ii] | (dl << 8) | (dr << 16);
-        stack.push_back((uint32_t)ii);
+        dr[i] = idx.lcs[i] ? (uint8_t)std::min<uint64_t>(255, nsv - i) : 0;
+        stack.push_back((uint32_t)i);
     }
+    out->assign(n + 1, 0);
+    for (uint64_t i = 0; i <= n; i++) {
+        uint32_t lo = i < n ? ((uint32_t)idx.lcs[i] | ((uint32_t)dl[i] << 8)) : 0u;
+        uint32_t hi = i + 1 < n ? ((uint32_t)idx.lcs[i + 1] | ((uint32_t)dr[i + 1] << 8)) : 0u;
+        (*out)[i] = lo | (hi << 16);
+    }
+}
+
+// window of match lengths in which extensions of chance matches keep failing: around log4(n_sets)
+void spec_window(uint64_t n_sets, uint32_t* lo, uint32_t* span) {
+    double l4 = std::log((double)std::max<uint64_t>(n_sets, 4)) / std::log(4.0);
+    int a = (int)std::floor(l4) - 3;
+    *lo = (uint32_t)std::max(1, a);
+    *span = 7;
 }
 
 void build_jump_table(const ntc_index& idx, std::vector<uint64_t>* out, int n_threads) {

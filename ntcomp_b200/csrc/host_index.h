@@ -36,10 +36,11 @@ int32_t build_index(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n
 // One rank probe = one aligned 16-byte load = one 32-byte L2 sector.
 void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out /* 16 u32 per block */, int n_threads);
 
-// LCS words for O(1) contract_left: u32 per node = LCS[i] | min(255, i - PSV(i)) << 8 |
-// min(255, NSV(i) - i) << 16, PSV / NSV = nearest position left / right with a strictly smaller LCS
-// (entry n_sets = 0 is the sentinel).  Saturated distances fall back to a scan on the device.
+// LCS words for O(1) contract_left: u32 word i = LCS[i] | min(255, i - PSV(i)) << 8 | LCS[i+1] << 16 |
+// min(255, NSV(i+1) - (i+1)) << 24, PSV / NSV = nearest position left / right with a strictly smaller
+// LCS (LCS[n_sets] = 0 is the sentinel).  Saturated distances fall back to a scan on the device.
 void build_lcs_words(const ntc_index& idx, std::vector<uint32_t>* out);
+void spec_window(uint64_t n_sets, uint32_t* lo, uint32_t* span);
 
 // Decode jump table: one u64 per node = pred^16(v) (low 32 bits) | last 16 bases of node v's k-mer
 // (high 32 bits, base at string position k-16+i in bits 2i..2i+1).  Root and '$' positions code 0.

@@ -30,6 +30,7 @@ void* emul_index_create(const ntc_index* idx) {
     e->dix.jump = e->jump.data();
     e->dix.n = (uint32_t)idx->n;
     e->dix.k = idx->k;
+    spec_window(idx->n, &e->dix.spec_lo, &e->dix.spec_span);
     return e;
 }
 void emul_index_free(void* p) { delete (EmulIndex*)p; }
