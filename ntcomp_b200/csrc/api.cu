@@ -252,6 +252,8 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     ctx->dix.n = (uint32_t)idx->n;
     ctx->dix.k = idx->k;
     spec_window(idx->n, &ctx->dix.spec_lo, &ctx->dix.spec_span);
+    if (const char* env = getenv("NTC_SPEC_LO")) ctx->dix.spec_lo = (uint32_t)strtoul(env, nullptr, 10);      // tuning knobs
+    if (const char* env = getenv("NTC_SPEC_SPAN")) ctx->dix.spec_span = (uint32_t)strtoul(env, nullptr, 10);
     *out = ctx;
     return NTC_OK;
 }

@@ -139,7 +139,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
     const CachePolicy pol = make_policies();
     uint64_t* __restrict__ sc = scratch + scratch_base(a, r);
     uint32_t s = 0, e = n, d = 0, urun = 0, prev_s = 0, prev_d = 0, j = 0;
-    bool fresh = true, absent = false;
+    bool fresh = true, absent = false, force = false;
     uint64_t word = packed[a >> 5];
     uint32_t c = (uint32_t)(word >> ((a & 31) * 2)) & 3u;
     while (j < len) {
@@ -150,7 +150,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         // extensions of chance matches fail (around log4(n_sets), set by the host), on demand otherwise
         // (ncu r1 v3: unconditional speculation doubled the sector traffic; v5: d < 20 still spent 39% of
         // all load sectors on it)
-        const bool spec = d - ix.spec_lo < ix.spec_span;   // unsigned: spec_lo <= d < spec_lo + spec_span
+        const bool spec = force || (d - ix.spec_lo < ix.spec_span);   // unsigned: spec_lo <= d < spec_lo + spec_span
         const bool single = e == s + 1u;
         uint32_t xs = 0, xe = 0;
         if (spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = single ? xs : ld4_keep(ix.lcsx + (e - 1u), pol.keep); }
@@ -173,7 +173,11 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
             // LCS values are < d and the reference's loop -- which re-probes the same empty interval for
             // every target above max(LCS[s], LCS[e]) -- ends up at that level with the interval widened
             // to the nearest strictly smaller LCS on the side(s) that hold the maximum.
-            if (!spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = single ? xs : ld4_keep(ix.lcsx + (e - 1u), pol.keep); }
+            // no LCS words at hand (failure outside the speculation window, e.g. the first mismatch of
+            // a long match): do NOT load them here -- a dependent load on this divergent path stalls the
+            // whole warp for a memory round trip (ncu r1 v6) -- re-run the iteration with the load forced
+            if (!spec) { force = true; continue; }
+            force = false;
             const int ls = s > 0 ? (int)lcsx_lcs(xs) : -1;              // LCS[s]   (low half of word s)
             const int le = e < n ? (int)((xe >> 16) & 0xFFu) : -1;      // LCS[e]   (high half of word e-1)
             const int t = tmax(ls, le);
