@@ -35,7 +35,9 @@ enum {
     NTC_ERR_LEN24 = 6,       /* a record length >= 2^24, src/lib.rs:226 */
     NTC_ERR_IO = 7,
     NTC_ERR_BAD_RECORD = 8,  /* colex rank >= n_sets in a record handed to decode */
-    NTC_ERR_UNSUPPORTED = 9  /* k outside [12,255] or n_sets >= 2^32 (src/encode.rs:147 truncates to u32, Q2) */
+    NTC_ERR_UNSUPPORTED = 9, /* k outside [12,255] or n_sets >= 2^32 (src/encode.rs:147 truncates to u32, Q2) */
+    NTC_ERR_EMPTY_COLUMN = 10 /* a block without a literal or without a reference record cannot be coded: the
+                                reference's write_block_to returns Err and main.rs:170 drops the block (Q4) */
 };
 
 const char* ntc_last_error(void);
@@ -108,6 +110,20 @@ int32_t ntc_decode_fasta(ntc_ctx* ctx, const uint64_t* records, uint64_t n_recor
 /* exact output sizes for a record stream (host scan of the flag/len fields) */
 void ntc_decode_bound(const uint64_t* records, uint64_t n_records, uint64_t first_seq_number, uint64_t* n_bases,
                       uint64_t* n_seqs, uint64_t* fasta_bytes);
+
+/* ---------------- block container, host side ("next" row f1: src/lib.rs:232-252,320-363) ----------
+ * ntc_block_write == write_block_to: splits the records into the four columns, codes them (minimal
+ * binary, Rice, Rice, minimal binary), gzips each and prepends the 32-byte headers.  DEFLATE bytes
+ * come from the system zlib (the reference links zlib-rs): members inflate to identical words.
+ * ntc_block_read == decode_block up to (not including) decode_sequence; *consumed == 0 at EOF. */
+uint64_t ntc_block_bound(uint64_t n_records);
+int32_t ntc_block_write(const uint64_t* records, uint64_t n_records, uint64_t num_reads, uint8_t* out, uint64_t cap,
+                        uint64_t* n_bytes);
+int32_t ntc_block_read(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records,
+                       uint64_t* consumed);
+/* one column through rice_encode / minimal_binary_encode (src/encode.rs:59-94): rice != 0 selects Rice */
+int32_t ntc_column_code(const uint64_t* values, uint64_t n, int32_t rice, uint64_t* words, uint64_t cap, uint64_t* n_words,
+                        uint64_t* param);
 
 /* ---------------- device-resident variants (buffers already in HBM, stream-ordered) ----------
  * Same semantics; all pointers are device pointers on ctx's GPU, `stream` is a cudaStream_t (0 =

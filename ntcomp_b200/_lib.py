@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libntcomp_b200.so")
 NTC_OK = 0
 ERROR_NAMES = {
     1: "NTC_ERR_INVALID_ARG", 2: "NTC_ERR_CUDA", 3: "NTC_ERR_CAPACITY", 4: "NTC_ERR_EMPTY_READ", 5: "NTC_ERR_BAD_BASE",
-    6: "NTC_ERR_LEN24", 7: "NTC_ERR_IO", 8: "NTC_ERR_BAD_RECORD", 9: "NTC_ERR_UNSUPPORTED",
+    6: "NTC_ERR_LEN24", 7: "NTC_ERR_IO", 8: "NTC_ERR_BAD_RECORD", 9: "NTC_ERR_UNSUPPORTED", 10: "NTC_ERR_EMPTY_COLUMN",
 }
 
 # every symbol include/ntcomp_b200.h declares: (restype, argtypes)
@@ -42,6 +42,10 @@ SIGNATURES = {
     "ntc_decode_batch": (_i32, [_vp, _vp, _u64, _vp, _u64, _vp, _u64, _vp]),
     "ntc_decode_fasta": (_i32, [_vp, _vp, _u64, _u64, _vp, _u64, _vp, _vp]),
     "ntc_decode_bound": (None, [_vp, _u64, _u64, _vp, _vp, _vp]),
+    "ntc_block_bound": (_u64, [_u64]),
+    "ntc_block_write": (_i32, [_vp, _u64, _u64, _vp, _u64, _vp]),
+    "ntc_block_read": (_i32, [_vp, _u64, _vp, _u64, _vp, _vp]),
+    "ntc_column_code": (_i32, [_vp, _u64, _i32, _vp, _u64, _vp, _vp]),
     "ntc_encode_device": (_i32, [_vp, _vp, _vp, _u64, _u64, _vp, _u64, _vp, _vp, _vp]),
     "ntc_decode_device": (_i32, [_vp, _vp, _u64, _u64, _i32, _vp, _u64, _vp, _u64, _vp, _vp]),
     "ntc_ctx_status": (_i32, [_vp, _vp]),

@@ -128,9 +128,9 @@ void build_lcs_words(const ntc_index& idx, std::vector<uint32_t>* out) {
 // window of match lengths in which extensions of chance matches keep failing: around log4(n_sets)
 void spec_window(uint64_t n_sets, uint32_t* lo, uint32_t* span) {
     double l4 = std::log((double)std::max<uint64_t>(n_sets, 4)) / std::log(4.0);
-    int a = (int)std::floor(l4) - 3;
+    int a = (int)std::floor(l4) - 1;   // swept on B200 (tools/sweep_spec.py, C3 shape): [10,16) best at n = 10^7
     *lo = (uint32_t)std::max(1, a);
-    *span = 7;
+    *span = 6;
 }
 
 void build_jump_table(const ntc_index& idx, std::vector<uint64_t>* out, int n_threads) {

@@ -155,7 +155,8 @@ bool split_encoded_dictionary(const uint64_t* rec, uint64_t n, Columns* c) {
             c->len.push_back((rec[i] >> 32) & 0xFFFFFFull);
         } else {
             uint64_t length = (flag & 0xFC) >> 2;
-            for (uint64_t j = 0; j < length && j < 32; j++) lit.push_back((uint8_t)((rec[i] >> (2 * j)) & 3));
+            const uint64_t payload = rec[i] & 0x00FFFFFFFFFFFFFFull;               // arr1[0..7], encode.rs:215-216
+            for (uint64_t j = 0; j < length && j < 32; j++) lit.push_back((uint8_t)((payload >> (2 * j)) & 3));
         }
         c->flags.push_back(flag);
     }

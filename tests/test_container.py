@@ -1,0 +1,95 @@
+"""Host block container of the product (ntcomp_b200/csrc/container.cpp) against the oracle's
+restatement (P2: header fields and inflated payload words identical; both link system zlib so the
+members are byte-identical here too)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import helpers
+import ntcomp_b200 as nt
+from ntcomp_b200 import _lib
+from oracle import binding as ob
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def column_code(values, rice):
+    v = np.ascontiguousarray(values, dtype=np.uint64)
+    cap = 2 * len(v) + 1024
+    words = np.zeros(cap, dtype=np.uint64)
+    nw, param = C.c_uint64(0), C.c_uint64(0)
+    rc = _lib.lib().ntc_column_code(_ptr(v), len(v), int(rice), _ptr(words), cap, C.byref(nw), C.byref(param))
+    return rc, words[: nw.value].copy(), param.value
+
+
+def block_write(rec, num_reads):
+    rec = np.ascontiguousarray(rec, dtype=np.uint64)
+    cap = int(_lib.lib().ntc_block_bound(len(rec)))
+    out = np.zeros(cap, dtype=np.uint8)
+    nb = C.c_uint64(0)
+    rc = _lib.lib().ntc_block_write(_ptr(rec), len(rec), num_reads, _ptr(out), cap, C.byref(nb))
+    return rc, out[: nb.value].tobytes()
+
+
+def block_read(data, offset=0):
+    buf = np.frombuffer(data, dtype=np.uint8)[offset:].copy()
+    cap = 8 * len(buf) + 1024
+    rec = np.zeros(cap, dtype=np.uint64)
+    n, used = C.c_uint64(0), C.c_uint64(0)
+    rc = _lib.lib().ntc_block_read(_ptr(buf) if len(buf) else None, len(buf), _ptr(rec), cap, C.byref(n), C.byref(used))
+    return rc, rec[: n.value].copy(), used.value
+
+
+def test_column_coders_match_oracle():
+    rng = np.random.default_rng(1)
+    for _ in range(30):
+        n = int(rng.integers(1, 4000))
+        vals = rng.integers(0, int(rng.choice([2, 48, 300, 1 << 12, 1 << 24, 1 << 32])), size=n).astype(np.uint64)
+        for rice in (False, True):
+            if rice and vals.max() > (1 << 16):
+                continue
+            rc, w, p = column_code(vals, rice)
+            ow, op = ob.code_column(vals, rice)
+            assert rc == 0 and p == op and (w == ow).all()
+    rc, _, _ = column_code(np.zeros(0, dtype=np.uint64), False)
+    assert rc == 10                                                  # NTC_ERR_EMPTY_COLUMN (Q4)
+    rc, w, p = column_code(np.array([5, 0, 1 << 20], dtype=np.uint64), True)   # long unary run
+    ow, op = ob.code_column(np.array([5, 0, 1 << 20], dtype=np.uint64), True)
+    assert rc == 0 and p == op and (w == ow).all()
+
+
+def test_block_write_read_matches_oracle():
+    rng = np.random.default_rng(2)
+    g = helpers.random_seq(rng, 6000)
+    o = ob.OracleIndex.build([g], 20, True)
+    for n_reads, rate in [(300, 0.03), (40, 0.0), (1000, 0.1)]:
+        reads = helpers.sample_reads(rng, [g], n_reads, [150, 30, 400], [rate], 20)
+        bases, off = ob.concat_reads(reads)
+        rec, _ = o.encode_reads(bases, off, fast=True, threads=4)
+        rc, blob = block_write(rec, n_reads)
+        oblob = ob.write_block(rec, n_reads)
+        if oblob is None:
+            assert rc == 10
+            continue
+        assert rc == 0 and blob == oblob
+        n_lit = int((((rec >> np.uint64(56)) & np.uint64(2)) >> np.uint64(1) * ((rec >> np.uint64(58)) & np.uint64(63))).sum())
+        rc, rec2, used = block_read(blob + b"\0" * 7)
+        orec = ob.read_block(blob) if True else None
+        if n_lit % 31 == 0 and n_lit:                               # Q5: the reference decoder panics
+            assert rc == 7
+        else:
+            assert rc == 0 and used == len(blob) and (rec2 == rec).all() and (orec[0] == rec).all()
+    rc, rec2, used = block_read(b"")                                 # EOF
+    assert rc == 0 and used == 0 and len(rec2) == 0
+    rc, _, _ = block_read(blob[: len(blob) // 2])                    # truncated
+    assert rc == 7
+
+
+def test_q4_blocks_are_refused_like_the_reference():
+    rec = np.array([5 | (20 << 32) | (1 << 56), 9 | (30 << 32)], dtype=np.uint64)     # reference records only
+    assert block_write(rec, 1)[0] == 10
+    lit = np.array([(0b1101 | ((1 + 2) | (2 << 2)) << 56)], dtype=np.uint64)          # literal records only
+    assert block_write(lit, 1)[0] == 10
