@@ -121,6 +121,10 @@ int32_t ntc_block_write(const uint64_t* records, uint64_t n_records, uint64_t nu
                         uint64_t* n_bytes);
 int32_t ntc_block_read(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records,
                        uint64_t* consumed);
+/* write_block_to with the column split and the Rice / minimal-binary bit packing on the GPU (prefix sum
+ * of code lengths + atomic OR into the MSB-first stream); gzip on the host.  Same bytes as ntc_block_write. */
+int32_t ntc_block_write_gpu(ntc_ctx* ctx, const uint64_t* records, uint64_t n_records, uint64_t num_reads, uint8_t* out,
+                            uint64_t cap, uint64_t* n_bytes);
 /* one column through rice_encode / minimal_binary_encode (src/encode.rs:59-94): rice != 0 selects Rice */
 int32_t ntc_column_code(const uint64_t* values, uint64_t n, int32_t rice, uint64_t* words, uint64_t cap, uint64_t* n_words,
                         uint64_t* param);

@@ -7,6 +7,8 @@
 #include <vector>
 
 #include "../../include/ntcomp_b200.h"
+#include "column_kernels.cuh"
+#include "container.h"
 #include "ctx.h"
 #include "decode_kernels.cuh"
 #include "encode_kernels.cuh"
@@ -189,6 +191,8 @@ int32_t read_status(ntc_ctx* ctx, cudaStream_t st) {
 
 }  // namespace
 
+void free_column_work(ntc_ctx* ctx);
+
 extern "C" {
 
 int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
@@ -270,6 +274,7 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
         DevBuf* lb[] = {&ln.packed, &ln.scratch, &ln.counts, &ln.tiles, &ln.rec_off, &ln.st_in, &ln.st_off, &ln.st_out, &ln.st_out2};
         for (DevBuf* b : lb) release(b);
     }
+    free_column_work(ctx);
     if (ctx->ev_walk) cudaEventDestroy(ctx->ev_walk);
     if (ctx->h_bounds) cudaFreeHost(ctx->h_bounds);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
@@ -418,4 +423,5 @@ extern "C" int32_t ntc_l2_random_bench(ntc_ctx* ctx, uint64_t buffer_bytes, uint
     return NTC_OK;
 }
 
+#include "api_columns.inc"
 #include "api_host.inc"

@@ -54,6 +54,7 @@ struct ntc_ctx {
     uint64_t* h_bounds = nullptr;   // pinned, decode chunk bounds
     cudaStream_t stream = nullptr;  // == lanes[0].stream
     cudaEvent_t ev_walk = nullptr;
+    void* colwork = nullptr;        // workspaces of the GPU column codec (api_columns.inc)
 
     // optional per-kernel-class timing with CUDA events on the launching stream (bench.py roofline)
     bool profiling = false;

@@ -5,6 +5,8 @@
 #include <cstring>
 #include <vector>
 
+#include "../../ntcomp_b200/csrc/column_kernels.cuh"
+#include "../../ntcomp_b200/csrc/container.h"
 #include "../../ntcomp_b200/csrc/decode_kernels.cuh"
 #include "../../ntcomp_b200/csrc/encode_kernels.cuh"
 #include "../../ntcomp_b200/csrc/host_index.h"
@@ -107,6 +109,42 @@ uint32_t emul_decode(void* ep, const uint64_t* rec, uint64_t n_rec, uint64_t fir
     for (uint64_t i = 0; i < n_rec; i++)
         walk_thread(e->dix, rec, n_rec, base_off.data(), seq_idx.data(), seq_first.data(), totals, first_no, fasta, out, cap, counts, &status, i);
     return status;
+}
+
+// GPU column codec bodies (column_kernels.cuh) on the CPU: returns the four coded columns back to back
+// in `words` (sizes in n_words[4], parameters in params[4]); -1 when a column is empty (Q4).
+int emul_block_columns(const uint64_t* rec, uint64_t n, uint64_t* words, uint64_t cap, uint64_t* n_words, uint64_t* params) {
+    std::vector<uint64_t> ref_idx(n + 1), lit_off(n + 1), colex(n), len(n), flags(n);
+    std::vector<unsigned long long> lits(n * 32 / 31 + 2, 0), red(3, 0);
+    SplitLoad load{rec};
+    uint64_t a = 0, b = 0;
+    for (uint64_t i = 0; i < n; i++) { ref_idx[i] = a; lit_off[i] = b; Pair64 p = load(i); a += p.a; b += p.b; }
+    for (uint64_t i = 0; i < n; i++) split_thread(rec, n, ref_idx.data(), lit_off.data(), colex.data(), len.data(), flags.data(), lits.data(), red.data(), i);
+    const uint64_t n_ref = a, n_lw = (b + 30) / 31;
+    if (n_ref == 0 || n_lw == 0) return -1;
+    uint64_t max_lit = 0;
+    for (uint64_t i = 0; i < n_lw; i++) max_lit = std::max<uint64_t>(max_lit, lits[i]);
+    const uint64_t* vals[4] = {colex.data(), len.data(), flags.data(), (const uint64_t*)lits.data()};
+    const uint64_t cnt[4] = {n_ref, n_ref, n, n_lw};
+    CodeParams cp[4];
+    unsigned l; uint64_t limit;
+    minimal_binary_shape(red[0] + 2, &l, &limit); cp[0] = CodeParams{0, 0, l, limit}; params[0] = red[0] + 2;
+    params[1] = rice_parameter(n_ref, red[1]); cp[1] = CodeParams{1, (uint32_t)params[1], 0, 0};
+    params[2] = rice_parameter(n, red[2]); cp[2] = CodeParams{1, (uint32_t)params[2], 0, 0};
+    minimal_binary_shape(max_lit + 2, &l, &limit); cp[3] = CodeParams{0, 0, l, limit}; params[3] = max_lit + 2;
+    uint64_t pos = 0;
+    for (int q = 0; q < 4; q++) {
+        std::vector<uint64_t> off(cnt[q] + 1);
+        uint64_t bits = 0;
+        for (uint64_t i = 0; i < cnt[q]; i++) { off[i] = bits; bits += code_bits(cp[q], vals[q][i]); }
+        std::vector<unsigned long long> w((bits + 63) / 64 + 2, 0);
+        for (uint64_t i = 0; i < cnt[q]; i++) pack_thread(cp[q], vals[q], cnt[q], off.data(), w.data(), i);
+        n_words[q] = (bits + 63) / 64;
+        if (pos + n_words[q] > cap) return -2;
+        for (uint64_t i = 0; i < n_words[q]; i++) words[pos + i] = __builtin_bswap64(w[i]);
+        pos += n_words[q];
+    }
+    return 0;
 }
 
 }  // extern "C"

@@ -93,3 +93,59 @@ def test_q4_blocks_are_refused_like_the_reference():
     assert block_write(rec, 1)[0] == 10
     lit = np.array([(0b1101 | ((1 + 2) | (2 << 2)) << 56)], dtype=np.uint64)          # literal records only
     assert block_write(lit, 1)[0] == 10
+
+
+def _columns_of(rec):
+    """(words, param) of the four columns through the host coder, via the oracle's split"""
+    cols = ob.split(rec)
+    return [column_code(cols[q], rice)[1:] for q, rice in enumerate((False, True, True, False))]
+
+
+def test_gpu_column_codec_bodies_on_cpu_emulation():
+    """column_kernels.cuh (split + prefix-summed bit packing) run on the CPU == sequential coders"""
+    from emul_binding import lib as emul_lib
+    L = emul_lib()
+    L.emul_block_columns.restype = C.c_int
+    L.emul_block_columns.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    rng = np.random.default_rng(3)
+    g = helpers.random_seq(rng, 8000)
+    o = ob.OracleIndex.build([g], 20, True)
+    for n_reads, rate, lens in [(400, 0.03, [150]), (50, 0.2, [40, 400]), (800, 0.01, [150, 2000])]:
+        reads = helpers.sample_reads(rng, [g], n_reads, lens, [rate], 20)
+        rec, _ = o.encode_reads(*ob.concat_reads(reads), fast=True, threads=4)
+        words = np.zeros(4 * len(rec) + 4096, dtype=np.uint64)
+        nw = np.zeros(4, dtype=np.uint64)
+        params = np.zeros(4, dtype=np.uint64)
+        rc = L.emul_block_columns(_ptr(rec), len(rec), _ptr(words), len(words), _ptr(nw), _ptr(params))
+        assert rc == 0
+        pos = 0
+        for q, (w, p) in enumerate(_columns_of(rec)):
+            assert int(params[q]) == p and int(nw[q]) == len(w), q
+            assert (words[pos: pos + len(w)] == w).all(), q
+            pos += len(w)
+
+
+@pytest.mark.gpu
+def test_block_write_gpu_is_byte_identical_to_host():
+    rng = np.random.default_rng(4)
+    g = helpers.random_seq(rng, 30000)
+    idx = nt.Index.build([g], 31)
+    ctx = nt.Context(idx, 0)
+    for n_reads, rate, lens in [(3000, 0.01, [150]), (65536, 0.01, [150]), (200, 0.3, [60, 1000])]:
+        reads = helpers.sample_reads(rng, [g], n_reads, lens, [rate], 31)
+        rec, _ = ctx.encode_batch(*nt.concat_reads(reads))
+        rc, blob = block_write(rec, n_reads)
+        cap = int(_lib.lib().ntc_block_bound(len(rec)))
+        out = np.zeros(cap, dtype=np.uint8)
+        nb = C.c_uint64(0)
+        rc2 = _lib.lib().ntc_block_write_gpu(ctx._h, _ptr(rec), len(rec), n_reads, _ptr(out), cap, C.byref(nb))
+        assert rc2 == rc
+        if rc == 0:
+            assert out[: nb.value].tobytes() == blob
+            rc3, rec2, used = block_read(blob)
+            n_lit = int((np.where(((rec >> np.uint64(56)) & np.uint64(2)) != 0, (rec >> np.uint64(58)) & np.uint64(63), 0)).sum())
+            if n_lit % 31:
+                assert rc3 == 0 and (rec2 == rec).all()
+    only_ref = rec[((rec >> np.uint64(56)) & np.uint64(2)) == 0]
+    nb = C.c_uint64(0)
+    assert _lib.lib().ntc_block_write_gpu(ctx._h, _ptr(only_ref), len(only_ref), 1, _ptr(out), cap, C.byref(nb)) == 10
