@@ -176,7 +176,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
             // no LCS words at hand (failure outside the speculation window, e.g. the first mismatch of
             // a long match): do NOT load them here -- a dependent load on this divergent path stalls the
             // whole warp for a memory round trip (ncu r1 v6) -- re-run the iteration with the load forced
-            if (!spec) { force = true; continue; }
+            if (!spec) { force = true; continue; }   // (a B200 sweep found on-demand loads here no faster for any window)
             force = false;
             const int ls = s > 0 ? (int)lcsx_lcs(xs) : -1;              // LCS[s]   (low half of word s)
             const int le = e < n ? (int)((xe >> 16) & 0xFFu) : -1;      // LCS[e]   (high half of word e-1)

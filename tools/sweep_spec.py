@@ -14,8 +14,8 @@ d_rec = torch.empty(nb // 6, dtype=torch.int64, device=dev); d_roff = torch.empt
 d_cnt = torch.zeros(4, dtype=torch.int64, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 first = True
-for lo, span in [(0, 0), (0, 20), (8, 7), (9, 5), (9, 7), (10, 4), (10, 6), (7, 10), (0, 255), (6, 14)]:
-    os.environ["NTC_SPEC_LO"] = str(lo); os.environ["NTC_SPEC_SPAN"] = str(span)
+for lo, span, od in [(10, 6, 0), (0, 0, 0), (0, 20, 0), (9, 7, 0), (10, 4, 0), (11, 5, 0), (0, 255, 0)]:
+    os.environ["NTC_SPEC_LO"] = str(lo); os.environ["NTC_SPEC_SPAN"] = str(span); os.environ["NTC_SPEC_ONDEMAND"] = str(od)
     ctx = nt.Context(idx, 0)
     if first:
         _lib.check(_lib.lib().ntc_synth_reads_device(ctx._h, d_g.data_ptr(), G, 999, 0, n_reads, L, 10_000, d_bases.data_ptr(), st)); first = False
@@ -26,5 +26,5 @@ for lo, span in [(0, 0), (0, 20), (8, 7), (9, 5), (9, 7), (10, 4), (10, 6), (7, 
     for _ in range(5):
         ctx.encode_device(d_bases.data_ptr(), d_off.data_ptr(), n_reads, nb, d_rec.data_ptr(), d_rec.numel(), d_roff.data_ptr(), d_cnt.data_ptr(), st)
     ctx.status(st); t = ctx.kernel_times()
-    print("spec [%d,%d): ms_kernel %.3f ms  (%.1f Gbases/s)  records %d" % (lo, lo + span, t["ms"][0] / t["ms"][1], nb / (t["ms"][0] / t["ms"][1]) / 1e6, int(d_cnt[0].item())), flush=True)
+    print("ondemand=%d " % od, end=""); print("spec [%d,%d): ms_kernel %.3f ms  (%.1f Gbases/s)  records %d" % (lo, lo + span, t["ms"][0] / t["ms"][1], nb / (t["ms"][0] / t["ms"][1]) / 1e6, int(d_cnt[0].item())), flush=True)
     ctx.close()
