@@ -38,6 +38,19 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def load_traffic(cfg_name, kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/), or None"""
+    try:
+        rounds = sorted(d for d in os.listdir(os.path.join(ROOT, "profiles")) if d.startswith("r"))
+        for rd in reversed(rounds):
+            path = os.path.join(ROOT, "profiles", rd, "traffic.json")
+            if os.path.exists(path):
+                return json.load(open(path)).get(cfg_name, {}).get(kernel)
+    except Exception:
+        pass
+    return None
+
+
 def config_of(name, reads_override=None):
     from ntcomp_b200 import synth
     cfg = dict(synth.CONFIGS[name])
@@ -342,7 +355,8 @@ def main():
     roofline = {
         "kernel": "ms_kernel (k-bounded matching statistics)", "bound": "hbm",
         "achieved": n_bases * (1.0 + 8.0 * rec_per_base) / ms_avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
-        "frac": n_bases * (1.0 + 8.0 * rec_per_base) / ms_avg_s / 1e9 / hbm_peak, "peak_source": peak_src, "traffic": None,
+        "frac": n_bases * (1.0 + 8.0 * rec_per_base) / ms_avg_s / 1e9 / hbm_peak, "peak_source": peak_src,
+        "traffic": load_traffic(cfg["name"], "ms_kernel") if args.reads is None else None,
         "note": "path is bound by random 32 B L2 sectors, not HBM (index is L2 resident); see l2_random",
         "l2_random": {"algorithmic_bytes_per_base": 64, "achieved": n_bases * 64.0 / ms_avg_s / 1e9, "peak": l2_peak_gbs, "unit": "GB/s",
                       "frac": n_bases * 64.0 / ms_avg_s / 1e9 / l2_peak_gbs,

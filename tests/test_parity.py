@@ -319,3 +319,35 @@ def test_device_resident_api_with_torch(small_cases):
         assert int(d_cnt[1].item()) == len(want)
         assert bytes(d_text[mis: mis + len(want)].cpu().numpy()) == want
         assert int(d_text[:mis].sum().item()) == 0 and int(d_text[mis + len(want):].sum().item()) == 0   # nothing outside the range
+
+
+@pytest.mark.gpu
+def test_config_c2_full_size_round_trip_and_sampled_parity():
+    """BASELINE config C2 at full size (5 Mbp genome, k = 31, 1 M x 150 bp, 1 % substitutions): the
+    whole batch must round-trip bit-exactly (size-independent property), the record stream of a sample
+    must equal the oracle's, and shard-wise encoding must concatenate to the single-batch stream."""
+    from ntcomp_b200 import sharding
+    cfg = synth.CONFIGS["C2"]
+    g = synth.genome(cfg["genome"])
+    index = nt.Index.build([g], cfg["k"])
+    ctx = nt.Context(index, 0)
+    bases, off = synth.reads(g, cfg["seed"], 0, cfg["n_reads"], cfg["read_len"], cfg["err_ppm"])
+    rec, roff = ctx.encode_batch(bases, off)
+    assert int(roff[-1]) == len(rec)
+    db, doff = ctx.decode_batch(rec)
+    assert (doff == off).all() and (db == bases).all()
+    text, n_seqs = ctx.decode_fasta(rec, 1)
+    header_bytes = sum((6 + d + 1) * c for d, c in [(1, 9), (2, 90), (3, 900), (4, 9000), (5, 90000), (6, 900000), (7, 1)])
+    assert n_seqs == cfg["n_reads"] == 1_000_000 and len(text) == len(bases) + header_bytes
+    assert text.endswith(bytes(bases[-150:]) + b"\n") and text.startswith(b">seq.1\n" + bytes(bases[:150]) + b"\n>seq.2\n")
+    oracle = ob.OracleIndex.from_arrays(index.k, index.n_sets, index.rows(), index.lcs())
+    for lo in (0, 500_000, 999_000):
+        hi = lo + 1000
+        orec, _ = oracle.encode_reads(bases[int(off[lo]): int(off[hi])], off[lo: hi + 1] - off[lo], fast=True, threads=8)
+        assert (rec[int(roff[lo]): int(roff[hi])] == orec).all()
+    # two shards on 65,536-read boundaries, encoded separately, concatenate to the same stream
+    parts = []
+    for lo, hi in sharding.shard_bounds(cfg["n_reads"], 2):
+        r, _ = ctx.encode_batch(bases[int(off[lo]): int(off[hi])], off[lo: hi + 1] - off[lo])
+        parts.append(r)
+    assert (sharding.concat_in_rank_order(parts) == rec).all()
