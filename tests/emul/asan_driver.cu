@@ -1,0 +1,72 @@
+// tests/emul/asan_driver.cu -- TEST INFRASTRUCTURE: runs the kernel bodies (via emul.cu) over random
+// inputs in a stand-alone executable built with AddressSanitizer, so out-of-bounds reads/writes in the
+// per-thread code show up on the CPU (compute-sanitizer is closed on the GPU pool).  Buffers are sized
+// exactly like the GPU workspaces.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <random>
+#include <vector>
+
+#include "../../include/ntcomp_b200.h"
+
+extern "C" {
+void* emul_index_create(const ntc_index* idx);
+void emul_index_free(void* p);
+uint32_t emul_encode(void* ep, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads, int mode, uint64_t* out, uint64_t cap,
+                     uint64_t* n_records, uint64_t* rec_offsets);
+uint32_t emul_decode(void* ep, const uint64_t* rec, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* out, uint64_t cap,
+                     uint64_t* seq_offsets, uint64_t cap_seqs, uint64_t* counts);
+int emul_block_columns(const uint64_t* rec, uint64_t n, uint64_t* words, uint64_t cap, uint64_t* n_words, uint64_t* params);
+}
+
+int main() {
+    std::mt19937_64 rng(7);
+    const char* alpha = "ACGT";
+    for (int round = 0; round < 6; round++) {
+        const uint32_t k = round % 3 == 0 ? 12 : (round % 3 == 1 ? 31 : 91);
+        std::vector<uint8_t> g(3000 + 2000 * round);
+        for (auto& b : g) b = (uint8_t)alpha[rng() & 3];
+        const uint8_t* seqs[1] = {g.data()};
+        uint64_t lens[1] = {g.size()};
+        ntc_index* idx = nullptr;
+        if (ntc_index_build(seqs, lens, 1, k, 1, 2, &idx)) { fprintf(stderr, "build failed: %s\n", ntc_last_error()); return 2; }
+        void* e = emul_index_create(idx);
+        std::vector<uint8_t> bases;
+        std::vector<uint64_t> off(1, 0);
+        for (int r = 0; r < 300; r++) {
+            uint64_t L = 1 + rng() % (r % 7 == 0 ? 700 : 160);
+            L = std::min<uint64_t>(L, g.size());
+            uint64_t a = rng() % (g.size() - L + 1);
+            for (uint64_t j = 0; j < L; j++) {
+                uint8_t b = g[a + j];
+                if (rng() % 100 < (uint64_t)(round * 3)) b = (uint8_t)alpha[rng() & 3];
+                bases.push_back(b);
+            }
+            off.push_back(bases.size());
+        }
+        const uint64_t n_reads = off.size() - 1, nb = bases.size();
+        std::vector<uint64_t> rec(nb), roff(n_reads + 1), tri(3 * nb);
+        uint64_t n_rec = 0, n_tri = 0;
+        if (emul_encode(e, bases.data(), off.data(), n_reads, 0, rec.data(), nb, &n_rec, roff.data())) return 3;
+        if (emul_encode(e, bases.data(), off.data(), n_reads, 1, tri.data(), nb, &n_tri, nullptr)) return 4;
+        rec.resize(n_rec);   // exact-size buffers: one element past the end is poisoned
+        for (uint64_t first_no : {1ull, 99ull, 99999ull}) {
+            uint64_t nbases = 0, nseqs = 0, fbytes = 0;
+            ntc_decode_bound(rec.data(), n_rec, first_no, &nbases, &nseqs, &fbytes);
+            std::vector<uint8_t> out(nbases), text(fbytes);
+            std::vector<uint64_t> soff(nseqs + 1);
+            uint64_t counts[2];
+            if (emul_decode(e, rec.data(), n_rec, 1, 0, out.data(), nbases, soff.data(), nseqs, counts)) return 5;
+            if (counts[1] != nb || memcmp(out.data(), bases.data(), nb)) { fprintf(stderr, "round trip mismatch\n"); return 6; }
+            if (emul_decode(e, rec.data(), n_rec, first_no, 1, text.data(), fbytes, nullptr, 0, counts)) return 7;
+            if (counts[1] != fbytes) return 8;
+        }
+        std::vector<uint64_t> words(4 * n_rec + 64), nw(4), params(4);
+        emul_block_columns(rec.data(), n_rec, words.data(), words.size(), nw.data(), params.data());
+        emul_index_free(e);
+        ntc_index_free(idx);
+    }
+    printf("ASAN_DRIVER_OK\n");
+    return 0;
+}

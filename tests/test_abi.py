@@ -63,3 +63,15 @@ def test_bounds_helpers():
     nb, ns, fb = nt.Context.decode_bound(ctxless, rec, 9)
     assert (nb, ns) == (35, 2)
     assert fb == 35 + len(b">seq.9\n\n") + len(b">seq.10\n\n")
+
+
+def test_kernel_bodies_under_address_sanitizer():
+    """compute-sanitizer is closed on the GPU pool, so the per-thread kernel bodies are run on the CPU
+    under AddressSanitizer with exactly-sized buffers (tests/emul/asan_driver.cu)."""
+    import subprocess
+    emul = os.path.join(ROOT, "tests", "emul")
+    _lib.lib()
+    subprocess.check_call(["make", "-C", emul, "-s", "asan_driver"], stderr=subprocess.DEVNULL)
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0:protect_shadow_gap=0")
+    out = subprocess.run([os.path.join(emul, "asan_driver")], capture_output=True, text=True, env=env, timeout=600)
+    assert out.returncode == 0 and "ASAN_DRIVER_OK" in out.stdout, out.stdout[-1500:] + out.stderr[-3000:]
