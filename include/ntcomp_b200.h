@@ -74,6 +74,12 @@ void ntc_ctx_destroy(ntc_ctx* ctx);
 /* bytes of HBM held by the re-laid-out index: [0]=rank blocks, [1]=LCS, [2]=decode jump table */
 void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]);
 
+/* Matching-statistics tile length.  A read longer than the tile is processed as independent tiles of
+ * that many positions, each warmed up on the k-1 bases before it (long reads, BASELINE config C5: a
+ * 10 kbp read is ~20 chains instead of one); the output is identical for every tile length.
+ * 0 (default) = chosen per batch; otherwise >= 256, rounded up to a multiple of 4. */
+int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len);
+
 /* ---------------- encode ------------------------------------------------------------------- */
 
 /* flat_map(encode_dictionary . encode_sequence) over a batch of reads: src/main.rs:166,169 with

@@ -143,6 +143,10 @@ class Context:
 
     KERNEL_CLASSES = ["pack2bit", "ms", "scan", "emit", "decode_scan", "seq_offsets", "walk", "misc"]
 
+    def set_tile_len(self, tile_len=0):
+        """matching-statistics tile length (0 = automatic); results do not depend on it"""
+        check(_lib.lib().ntc_ctx_set_tile_len(self._h, int(tile_len)))
+
     def set_profiling(self, on=True):
         check(_lib.lib().ntc_ctx_set_profiling(self._h, int(on)))
 

@@ -71,6 +71,45 @@ int32_t status_to_code(uint32_t st) {
     return NTC_OK;
 }
 
+// Tile length for a batch: long reads are cut into tiles (encode_kernels.cuh) so that a batch holds
+// enough independent chains to fill the GPU and balance its tail (>= ~1.5 M work items when the batch
+// allows); a tile costs k-1 warm-up bases, so tiles are never shorter than 512 positions by default.
+// Reads no longer than the tile are one item each -- short-read batches are unaffected.
+uint32_t tile_len_for(const ntc_ctx* ctx, uint64_t n_bases) {
+    if (ctx->tile_len) return ctx->tile_len;
+    uint64_t t = std::max<uint64_t>(512, n_bases / 1500000);
+    t = std::min<uint64_t>((t + 63) & ~63ull, 1u << 22);
+    return (uint32_t)t;
+}
+
+// matching statistics of a packed batch: tiles per read -> scan -> item descriptors -> ms_kernel over
+// the items -> record counts of multi-tile reads.  counts may be null (diagnostic entry point).
+int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint64_t* d_offsets, uint64_t n_reads, uint64_t n_bases,
+                    uint32_t T, uint64_t* scratch, uint32_t* counts, uint32_t* status, cudaStream_t st) {
+    const uint64_t max_items = n_reads + n_bases / T;                 // sum over reads of max(1, ceil(len / T)) is at most this
+    NTC_CUDA_TRY(ensure(&lane.tile_off, (n_reads + 2) * 8 + 16));
+    NTC_CUDA_TRY(ensure(&lane.desc, (max_items + 1) * 8));
+    NTC_CUDA_TRY(ensure(&lane.tiles, scan_num_tiles(n_reads) * sizeof(Pair64)));
+    uint64_t* tile_off = (uint64_t*)lane.tile_off.p;
+    uint64_t* tile_tot = tile_off + n_reads + 2;                      // 2 x u64 scan totals
+    {
+        Timed t(ctx, KC_SCAN, st, 4);
+        exclusive_scan_pairs(TileLoad{d_offsets, T}, n_reads, (Pair64*)lane.tiles.p, nullptr, tile_tot, tile_off, nullptr, st);
+        tile_desc_kernel<<<blocks_for(n_reads, 256), 256, 0, st>>>(d_offsets, n_reads, tile_off, T, (uint64_t*)lane.desc.p);
+    }
+    {
+        Timed t(ctx, KC_MS, st);
+        ms_kernel<<<blocks_for(max_items, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, (const uint64_t*)lane.desc.p,
+                                                                            tile_off + n_reads, T, scratch, counts, status);
+    }
+    if (counts && n_bases > (uint64_t)T) {                            // no read can exceed T otherwise
+        Timed t(ctx, KC_SCAN, st);
+        count_kernel<<<blocks_for(n_reads, 256), 256, 0, st>>>(ctx->dix, d_offsets, n_reads, T, scratch, counts, status);
+    }
+    NTC_CUDA_TRY(cudaGetLastError());
+    return NTC_OK;
+}
+
 // ------------------------------------------------------------------------------------------
 // encode pipeline on device buffers, using the workspaces of `lane` on stream `st`.
 // MODE 0 records, 1 triples.  carry (device, 2 x u64, may be null) is added to every record
@@ -107,11 +146,9 @@ int32_t encode_pipeline(ntc_ctx* ctx, Lane& lane, int mode, const uint8_t* d_bas
         pack2bit_kernel<<<blocks_for((n_bases + 31) / 32, kPackThreads), kPackThreads, 0, st>>>(d_bases, d_offsets, n_bases, packed,
                                                                                                 ctx->d_status);
     }
-    {
-        Timed t(ctx, KC_MS, st);
-        ms_kernel<<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                          ctx->d_status);
-    }
+    const uint32_t T = tile_len_for(ctx, n_bases);
+    int32_t rc = ms_pipeline(ctx, lane, packed, d_offsets, n_reads, n_bases, T, scratch, counts, ctx->d_status, st);
+    if (rc) return rc;
     if (wait_scan) NTC_CUDA_TRY(cudaStreamWaitEvent(st, wait_scan, 0));
     {
         Timed t(ctx, KC_SCAN, st, 3);
@@ -122,10 +159,10 @@ int32_t encode_pipeline(ntc_ctx* ctx, Lane& lane, int mode, const uint8_t* d_bas
         Timed t(ctx, KC_EMIT, st);
         if (mode == 0)
             emit_kernel<0><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                                   rec_off, rel, d_out, cap, ctx->d_status);
+                                                                                   rec_off, rel, d_out, cap, ctx->d_status, T);
         else
             emit_kernel<1><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                                   rec_off, rel, d_out, cap, ctx->d_status);
+                                                                                   rec_off, rel, d_out, cap, ctx->d_status, T);
     }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
@@ -256,6 +293,7 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     ctx->dix.n = (uint32_t)idx->n;
     ctx->dix.k = idx->k;
     spec_window(idx->n, &ctx->dix.spec_lo, &ctx->dix.spec_span);
+    if (const char* env = getenv("NTC_TILE_LEN")) ntc_ctx_set_tile_len(ctx, (uint32_t)strtoul(env, nullptr, 10));
     if (const char* env = getenv("NTC_SPEC_LO")) ctx->dix.spec_lo = (uint32_t)strtoul(env, nullptr, 10);      // tuning knobs
     if (const char* env = getenv("NTC_SPEC_SPAN")) ctx->dix.spec_span = (uint32_t)strtoul(env, nullptr, 10);
     *out = ctx;
@@ -271,7 +309,7 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
         if (ln.ev_scan) cudaEventDestroy(ln.ev_scan);
         if (ln.ev_done) cudaEventDestroy(ln.ev_done);
         if (ln.h_land) cudaFreeHost(ln.h_land);
-        DevBuf* lb[] = {&ln.packed, &ln.scratch, &ln.counts, &ln.tiles, &ln.rec_off, &ln.st_in, &ln.st_off, &ln.st_out, &ln.st_out2};
+        DevBuf* lb[] = {&ln.packed, &ln.scratch, &ln.counts, &ln.tiles, &ln.rec_off, &ln.tile_off, &ln.desc, &ln.st_in, &ln.st_off, &ln.st_out, &ln.st_out2};
         for (DevBuf* b : lb) release(b);
     }
     free_column_work(ctx);
@@ -288,6 +326,14 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
 
 void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]) { memcpy(out, ctx->index_bytes, 24); }
 uint64_t ntc_ctx_launch_count(const ntc_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len) {
+    if (!ctx) { set_error("null ctx"); return NTC_ERR_INVALID_ARG; }
+    if (tile_len && tile_len < kTileMin) { set_error("tile length must be 0 (automatic) or >= 256"); return NTC_ERR_INVALID_ARG; }
+    if (tile_len > (1u << 22)) tile_len = 1u << 22;
+    ctx->tile_len = (tile_len + 3u) & ~3u;
+    return NTC_OK;
+}
 
 int32_t ntc_ctx_status(ntc_ctx* ctx, void* stream) {
     if (!ctx) { set_error("null ctx"); return NTC_ERR_INVALID_ARG; }

@@ -25,6 +25,7 @@ struct DevBuf {
 struct Lane {
     cudaStream_t stream = nullptr;
     DevBuf packed, scratch, counts, tiles, rec_off;   // encode workspaces
+    DevBuf tile_off, desc;                            // tiles per read (scanned) and work-item descriptors of ms_kernel
     DevBuf st_in, st_off, st_out, st_out2;            // staging for host buffers
     cudaEvent_t ev_scan = nullptr, ev_done = nullptr;
     uint64_t* h_land = nullptr;                       // pinned landing zone: [0..1] totals, [2] status
@@ -46,6 +47,7 @@ struct ntc_ctx {
     uint64_t* d_counts = nullptr;   // [4]: internal counts for the host-buffer API
     uint64_t launches = 0;
     uint64_t max_chunk_bases = 96ull << 20;   // host-buffer API chunk (overlap granularity); NTC_MAX_CHUNK_BASES overrides
+    uint32_t tile_len = 0;                    // matching-statistics tile length; 0 = chosen per batch (ntc_ctx_set_tile_len)
     uint64_t max_chunk_bytes = 128ull << 20;  // decode output chunk for D2H overlap
 
     ntc::Lane lanes[2];             // lanes[0] also serves the device-resident API (on the caller's stream)

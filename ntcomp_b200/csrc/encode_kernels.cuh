@@ -14,6 +14,7 @@
 // Kernel bodies are per-thread NTC_HD functions (`*_thread`) so tests/emul can run them on the CPU.
 #pragma once
 #include "device_common.cuh"
+#include "scan.cuh"
 
 namespace ntc {
 
@@ -69,14 +70,31 @@ __global__ void __launch_bounds__(kPackThreads) pack2bit_kernel(const uint8_t* _
 // segmentation of one read from its scratch entries; calls sink(L, start, end_pos, d_orig)
 // for each record in reference order (read END first).  Returns the record count.
 // ------------------------------------------------------------------------------------------
+// Length (capped at `limit`) of the run of "unique predecessor" positions ending at q.  A read longer
+// than the tile length T is processed as independent tiles of T positions (ms_thread), each counting
+// its runs from its own first position; a run that reaches the start of its tile continues with the
+// run ending at the last position of the previous tile.
+NTC_HD uint32_t unique_run(const uint64_t* __restrict__ sc, uint32_t q, uint32_t T, uint32_t limit) {
+    uint32_t run = entry_urun(sc[q]);
+    uint32_t total = run;
+    while (total < limit) {
+        uint32_t p0 = q - q % T;                                      // first position of q's tile
+        if (p0 == 0 || run != q - p0 + 1) break;
+        q = p0 - 1;
+        run = entry_urun(sc[q]);
+        total += run;
+    }
+    return tmin(total, limit);
+}
+
 template <typename Sink>
-NTC_HD uint32_t segment_read(const uint64_t* __restrict__ sc, uint32_t len, uint32_t k, Sink&& sink) {
+NTC_HD uint32_t segment_read(const uint64_t* __restrict__ sc, uint32_t len, uint32_t k, uint32_t T, Sink&& sink) {
     uint32_t i = len, cnt = 0;
     while (i > 0) {
         uint64_t ent = sc[i - 1];
         uint32_t d = entry_d(ent), v = entry_s(ent);
         if (d == k && i > k + 1) {                                    // src/lib.rs:180
-            uint32_t ext = tmin(i - k - 1, entry_urun(sc[i - 2]));    // left_extend_kmer, src/lib.rs:186
+            uint32_t ext = unique_run(sc, i - 2, T, i - k - 1);       // left_extend_kmer, src/lib.rs:186
             uint32_t new_len = k + ext, m = new_len, old_i = i;
             for (;;) {                                                // hop loop, src/lib.rs:193-203
                 uint32_t dd = entry_d(sc[i - 1]);
@@ -121,12 +139,38 @@ inline uint64_t scratch_entries(uint64_t n_bases, uint64_t n_reads) { return n_b
 // interval [s, e) reads words s and e-1.
 NTC_HD uint32_t lcsx_lcs(uint32_t x) { return x & 0xFFu; }
 
+// ---- tiles ------------------------------------------------------------------------------------
+// MS at position j depends only on the k-1 bases before it, so a read longer
+// than the tile length T is cut into tiles of T positions; the thread of tile t > 0 starts k-1 bases
+// early from the empty match (warm-up, nothing stored) and is exact from the tile's first position on.
+// A 10 kbp read (BASELINE config C5) is then ~20 independent chains instead of one.  T is a multiple
+// of 4 (full-sector scratch stores) and >= kTileMin >= k_max - 1.
+constexpr uint32_t kTileMin = 256;
+constexpr uint32_t kDescTileBits = 24;   // item descriptor: read << 24 | tile
+NTC_HD uint32_t tiles_of(uint32_t len, uint32_t T) { return len <= T ? 1u : (len + T - 1u) / T; }
+
+// scan input: tiles per read
+struct TileLoad {
+    const uint64_t* offsets;
+    uint32_t T;
+    NTC_HD Pair64 operator()(uint64_t r) const { return Pair64{tiles_of((uint32_t)(offsets[r + 1] - offsets[r]), T), 0}; }
+};
+
+NTC_HD void tile_desc_thread(const uint64_t* __restrict__ offsets, uint64_t n_reads, const uint64_t* __restrict__ tile_off, uint32_t T,
+                             uint64_t* __restrict__ desc, uint64_t r) {
+    if (r >= n_reads) return;
+    const uint32_t nt = tiles_of((uint32_t)(offsets[r + 1] - offsets[r]), T);
+    uint64_t* d = desc + tile_off[r];
+    for (uint32_t t = 0; t < nt; t++) d[t] = (r << kDescTileBits) | t;
+}
+
 // `stage` = 4 x blockDim u64 staging slots of this thread's block (shared memory on the GPU),
 // indexed [slot * stride + lane]
-NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t* __restrict__ offsets, uint64_t n_reads,
-                      uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t r,
+NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t* __restrict__ offsets, uint64_t item_desc, uint32_t T,
+                      uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts, uint32_t* __restrict__ status,
                       uint64_t* stage, uint32_t stride) {
-    if (r >= n_reads) return;
+    const uint64_t r = item_desc >> kDescTileBits;
+    const uint32_t tile = (uint32_t)item_desc & ((1u << kDescTileBits) - 1u);
     const uint64_t base0 = NTC_LDG(offsets);
     const uint64_t a = offsets[r] - base0;
     const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
@@ -136,13 +180,17 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         return;
     }
     const uint32_t n = ix.n, k = ix.k;
+    const bool multi = len > T;                                       // counted by count_kernel once every tile is done
+    const uint32_t p0 = tile * T;                                     // first stored position
+    const uint32_t p1 = multi ? tmin(len, p0 + T) : len;              // end of the tile
     const CachePolicy pol = make_policies();
     uint64_t* __restrict__ sc = scratch + scratch_base(a, r);
-    uint32_t s = 0, e = n, d = 0, urun = 0, prev_s = 0, prev_d = 0, j = 0;
+    uint32_t s = 0, e = n, d = 0, urun = 0, prev_s = 0, prev_d = 0;
+    uint32_t j = tile ? p0 - (k - 1u) : 0u;                           // warm-up start
     bool fresh = true, absent = false, force = false;
-    uint64_t word = packed[a >> 5];
-    uint32_t c = (uint32_t)(word >> ((a & 31) * 2)) & 3u;
-    while (j < len) {
+    uint64_t word = packed[(a + j) >> 5];
+    uint32_t c = (uint32_t)(word >> (((a + j) & 31) * 2)) & 3u;
+    while (j < p1) {
         const uint32_t bs = s / 48u, be = e / 48u;
         const uint32_t os = s - bs * 48u, oe = e - be * 48u;
         const uint4 va = ld16_keep(ix.rank + (size_t)bs * 4 + c, pol.keep);
@@ -157,7 +205,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         const uint4 vb = (be != bs) ? ld16_keep(ix.rank + (size_t)be * 4 + c, pol.keep) : va;
         if (fresh) {
             // the block of the previous interval start also holds its Q bit: finish entry j-1
-            if (j > 0) {
+            if (j > p0) {
                 urun = (prev_d == k && entry_qbit(va, os)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
                 uint32_t slot = (j - 1) & 3u;
                 stage[slot * stride] = make_entry(prev_s, prev_d, urun);
@@ -199,28 +247,46 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         else { d = 0; absent = true; }                                // base absent from the index
         prev_s = s; prev_d = d; fresh = true;
         j++;
-        if (j < len) {
+        if (j < p1) {
             uint64_t p = a + j;
             if ((p & 31) == 0) word = packed[p >> 5];
             c = (uint32_t)(word >> ((p & 31) * 2)) & 3u;
         }
     }
-    // tail: entries of the last, partial group of four + the final position
+    // tail: entries of the last, partial group of four + the tile's final position
     {
-        uint32_t first_unflushed = (len - 1) & ~3u;                    // entries [first_unflushed, len-1) are staged
-        for (uint32_t q = first_unflushed; q + 1 < len; q++) sc[q] = stage[(q & 3u) * stride];
-        sc[len - 1] = make_entry(prev_s, prev_d, 0);
+        uint32_t first_unflushed = (p1 - 1) & ~3u;                     // entries [first_unflushed, p1-1) are staged (>= p0: p0 % 4 == 0)
+        for (uint32_t q = first_unflushed; q + 1 < p1; q++) sc[q] = stage[(q & 3u) * stride];
+        uint32_t last_run = 0;                                         // urun of a read's last position is never read (ext looks at i-2)
+        if (p1 < len) {                                                // ... but the next tile's runs may continue this one
+            const uint4 vq = ld16_keep(ix.rank + (size_t)(prev_s / 48u) * 4, pol.keep);
+            last_run = (prev_d == k && entry_qbit(vq, prev_s % 48u)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
+        }
+        sc[p1 - 1] = make_entry(prev_s, prev_d, last_run);
     }
     if (absent) {                                                     // lib.rs:207 would underflow (Q3)
-        if (counts) counts[r] = 0;
+        if (counts && !multi) counts[r] = 0;
         NTC_ATOMIC_OR(status, (uint32_t)ST_BAD_BASE);
         return;
     }
-    if (counts) {
+    if (counts && !multi) {
         CountSink sink;
-        counts[r] = segment_read(sc, len, k, sink);
+        counts[r] = segment_read(sc, len, k, T, sink);
         if (sink.big) NTC_ATOMIC_OR(status, (uint32_t)ST_LEN24);      // src/lib.rs:226
     }
+}
+
+// record count of a read that was processed as several tiles (single-tile reads are counted by ms_thread)
+NTC_HD void count_thread(const DevIndex& ix, const uint64_t* __restrict__ offsets, uint64_t n_reads, uint32_t T,
+                         const uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t r) {
+    if (r >= n_reads) return;
+    const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
+    if (len <= T) return;
+    if (*status & ST_BAD_BASE) { counts[r] = 0; return; }             // some d == 0: segmentation would not terminate (Q3)
+    const uint64_t a = offsets[r] - NTC_LDG(offsets);
+    CountSink sink;
+    counts[r] = segment_read(scratch + scratch_base(a, r), len, ix.k, T, sink);
+    if (sink.big) NTC_ATOMIC_OR(status, (uint32_t)ST_LEN24);
 }
 
 #if defined(__CUDACC__)
@@ -259,18 +325,29 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 constexpr uint32_t kMsStageWords = 1024;  // 8 KB of packed reads per block (128 reads x up to 256 bases); longer reads load from global
 
 __global__ void __launch_bounds__(kMsThreads, 10) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
-                                                        const uint64_t* __restrict__ offsets, uint64_t n_reads,
+                                                        const uint64_t* __restrict__ offsets, const uint64_t* __restrict__ desc,
+                                                        const uint64_t* __restrict__ n_items, uint32_t T,
                                                         uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts,
                                                         uint32_t* __restrict__ status) {
     __shared__ __align__(16) uint64_t s_packed[kMsStageWords];
     __shared__ uint64_t s_stage[4 * kMsThreads];
     __shared__ __align__(8) uint64_t s_bar;
-    const uint64_t r0 = (uint64_t)blockIdx.x * kMsThreads;
-    const uint64_t r1 = r0 + kMsThreads < n_reads ? r0 + kMsThreads : n_reads;
-    // the block's reads are one contiguous run of the packed stream: stage it with one bulk TMA copy
+    // the grid covers an upper bound of the item count (n_reads + n_bases / T); the exact count is on the device
+    const uint64_t total = *n_items;
+    const uint64_t i0 = (uint64_t)blockIdx.x * kMsThreads;
+    if (i0 >= total) return;
+    const uint64_t i1 = i0 + kMsThreads < total ? i0 + kMsThreads : total;
+    // the block's items are one contiguous run of the packed stream (tiles of one read overlap by their
+    // warm-up): stage it with one bulk TMA copy when it fits (always for short reads)
     const uint64_t base0 = offsets[0];
-    const uint64_t w_lo = ((offsets[r0] - base0) >> 5) & ~1ull;              // 16-byte aligned
-    const uint64_t w_hi = (((offsets[r1] - base0) >> 5) + 2) & ~1ull;        // exclusive, 16-byte aligned (buffer is padded)
+    const uint64_t da = desc[i0], db = desc[i1 - 1];
+    const uint64_t ra = da >> kDescTileBits, rb = db >> kDescTileBits;
+    const uint32_t ta = (uint32_t)da & ((1u << kDescTileBits) - 1u), tb = (uint32_t)db & ((1u << kDescTileBits) - 1u);
+    const uint64_t len_b = offsets[rb + 1] - offsets[rb];
+    const uint64_t lo = offsets[ra] - base0 + (ta ? (uint64_t)ta * T - (ix.k - 1u) : 0);
+    const uint64_t hi = offsets[rb] - base0 + (len_b > T ? tmin<uint64_t>(len_b, ((uint64_t)tb + 1) * T) : len_b);
+    const uint64_t w_lo = (lo >> 5) & ~1ull;                                 // 16-byte aligned
+    const uint64_t w_hi = ((hi >> 5) + 2) & ~1ull;                           // exclusive, 16-byte aligned (buffer is padded)
     const bool staged = (w_hi - w_lo) <= kMsStageWords;
     if (staged) {
         if (threadIdx.x == 0) mbar_init(&s_bar, 1);
@@ -279,7 +356,20 @@ __global__ void __launch_bounds__(kMsThreads, 10) ms_kernel(DevIndex ix, const u
         mbar_wait(&s_bar, 0);
     }
     const uint64_t* pk = staged ? (s_packed - w_lo) : packed;                // generic pointer: shared or global
-    ms_thread(ix, pk, offsets, n_reads, scratch, counts, status, r0 + threadIdx.x, s_stage + threadIdx.x, kMsThreads);
+    const uint64_t i = i0 + threadIdx.x;
+    if (i >= i1) return;
+    ms_thread(ix, pk, offsets, desc[i], T, scratch, counts, status, s_stage + threadIdx.x, kMsThreads);
+}
+
+__global__ void __launch_bounds__(256) tile_desc_kernel(const uint64_t* __restrict__ offsets, uint64_t n_reads,
+                                                        const uint64_t* __restrict__ tile_off, uint32_t T, uint64_t* __restrict__ desc) {
+    tile_desc_thread(offsets, n_reads, tile_off, T, desc, (uint64_t)blockIdx.x * 256 + threadIdx.x);
+}
+
+__global__ void __launch_bounds__(256) count_kernel(DevIndex ix, const uint64_t* __restrict__ offsets, uint64_t n_reads, uint32_t T,
+                                                    const uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts,
+                                                    uint32_t* __restrict__ status) {
+    count_thread(ix, offsets, n_reads, T, scratch, counts, status, (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -315,7 +405,8 @@ struct EmitSink {
 template <int MODE>
 NTC_HD void emit_thread(const DevIndex& ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offsets, uint64_t n_reads,
                         const uint64_t* __restrict__ scratch, const uint32_t* __restrict__ counts, const uint64_t* __restrict__ rec_offsets,
-                        const uint64_t* __restrict__ rel, uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status, uint64_t r) {
+                        const uint64_t* __restrict__ rel, uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status, uint32_t T,
+                        uint64_t r) {
     // rec_offsets are absolute (a carry from earlier chunks is folded in); `out` is this chunk's
     // buffer, so positions are taken relative to *rel (the number of records before the chunk)
     if (r >= n_reads) return;
@@ -326,7 +417,7 @@ NTC_HD void emit_thread(const DevIndex& ix, const uint64_t* __restrict__ packed,
     const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
     if (rec_offsets[r + 1] - rel0 > cap) { NTC_ATOMIC_OR(status, (uint32_t)ST_CAPACITY); return; }
     EmitSink<MODE> sink{ix, packed, out, a, rec_offsets[r] - rel0, 1};
-    segment_read(scratch + scratch_base(a, r), len, ix.k, sink);
+    segment_read(scratch + scratch_base(a, r), len, ix.k, T, sink);
 }
 
 template <int MODE>
@@ -334,8 +425,8 @@ __global__ void __launch_bounds__(kMsThreads) emit_kernel(DevIndex ix, const uin
                                                           const uint64_t* __restrict__ offsets, uint64_t n_reads,
                                                           const uint64_t* __restrict__ scratch, const uint32_t* __restrict__ counts,
                                                           const uint64_t* __restrict__ rec_offsets, const uint64_t* __restrict__ rel,
-                                                          uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status) {
-    emit_thread<MODE>(ix, packed, offsets, n_reads, scratch, counts, rec_offsets, rel, out, cap, status,
+                                                          uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status, uint32_t T) {
+    emit_thread<MODE>(ix, packed, offsets, n_reads, scratch, counts, rec_offsets, rel, out, cap, status, T,
                       (uint64_t)blockIdx.x * kMsThreads + threadIdx.x);
 }
 

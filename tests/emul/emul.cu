@@ -14,6 +14,7 @@
 using namespace ntc;
 
 struct EmulIndex {
+    uint32_t tile_len = 1u << 22;
     std::vector<uint32_t> rank;
     std::vector<uint64_t> jump;
     std::vector<uint32_t> lcs;
@@ -36,6 +37,7 @@ void* emul_index_create(const ntc_index* idx) {
     return e;
 }
 void emul_index_free(void* p) { delete (EmulIndex*)p; }
+void emul_set_tile_len(void* p, uint32_t T) { ((EmulIndex*)p)->tile_len = T ? (T + 3u) & ~3u : 1u << 22; }
 
 static void run_ms(const EmulIndex* e, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads, std::vector<uint64_t>* packed,
                    std::vector<uint64_t>* scratch, uint64_t** scratch_aligned, uint32_t* counts, uint32_t* status) {
@@ -46,8 +48,17 @@ static void run_ms(const EmulIndex* e, const uint8_t* bases, const uint64_t* off
     uint64_t* sc = scratch->data();
     sc += (4 - (((uintptr_t)sc / 8) & 3)) & 3;                       // 32-byte aligned, like cudaMalloc
     *scratch_aligned = sc;
+    // the host side of ms_pipeline (api.cu): tiles per read -> exclusive scan -> item descriptors -> items -> counts
+    const uint32_t T = e->tile_len;
+    std::vector<uint64_t> tile_off(n_reads + 1, 0);
+    TileLoad tl{offsets, T};
+    for (uint64_t r = 0; r < n_reads; r++) tile_off[r + 1] = tile_off[r] + tl(r).a;
+    std::vector<uint64_t> desc(tile_off[n_reads] + 1, ~0ull);
+    for (uint64_t r = 0; r < n_reads; r++) tile_desc_thread(offsets, n_reads, tile_off.data(), T, desc.data(), r);
     uint64_t stage[4];
-    for (uint64_t r = 0; r < n_reads; r++) ms_thread(e->dix, packed->data(), offsets, n_reads, sc, counts, status, r, stage, 1);
+    // items in reverse order: tiles of a read must not depend on the order in which they run
+    for (uint64_t i = tile_off[n_reads]; i-- > 0;) ms_thread(e->dix, packed->data(), offsets, desc[i], T, sc, counts, status, stage, 1);
+    if (counts) for (uint64_t r = 0; r < n_reads; r++) count_thread(e->dix, offsets, n_reads, T, sc, counts, status, r);
 }
 
 // mode 0 records, 1 triples.  Returns the accumulated status bits.
@@ -62,8 +73,8 @@ uint32_t emul_encode(void* ep, const uint8_t* bases, const uint64_t* offsets, ui
     std::vector<uint64_t> roff(n_reads + 1, 0);
     for (uint64_t r = 0; r < n_reads; r++) roff[r + 1] = roff[r] + counts[r];   // exclusive scan (scan.cuh on the GPU)
     for (uint64_t r = 0; r < n_reads; r++) {
-        if (mode == 0) emit_thread<0>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), nullptr, out, cap, &status, r);
-        else emit_thread<1>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), nullptr, out, cap, &status, r);
+        if (mode == 0) emit_thread<0>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), nullptr, out, cap, &status, e->tile_len, r);
+        else emit_thread<1>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), nullptr, out, cap, &status, e->tile_len, r);
     }
     *n_records = roff[n_reads];
     if (rec_offsets) memcpy(rec_offsets, roff.data(), (n_reads + 1) * 8);

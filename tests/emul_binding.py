@@ -27,6 +27,7 @@ def lib():
         L.emul_index_create.restype = vp
         L.emul_index_create.argtypes = [vp]
         L.emul_index_free.argtypes = [vp]
+        L.emul_set_tile_len.argtypes = [vp, u32]
         L.emul_encode.restype = u32
         L.emul_encode.argtypes = [vp, vp, vp, u64, i32, vp, u64, vp, vp]
         L.emul_ms.restype = u32
@@ -60,6 +61,9 @@ class EmulContext:
             lib().emul_index_free(self._h)
         except Exception:
             pass
+
+    def set_tile_len(self, tile_len=0):
+        lib().emul_set_tile_len(self._h, int(tile_len))
 
     def _encode(self, bases, offsets, mode, cap=None):
         bases = np.ascontiguousarray(bases, dtype=np.uint8)

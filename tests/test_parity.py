@@ -88,6 +88,34 @@ def test_encode_records_parity_literal_oracle(small_cases):
         assert (rec == orec).all(), case.k
 
 
+def test_tile_length_invariance(small_cases):
+    """Long reads are cut into tiles with a k-1 base warm-up (ms_thread); matching statistics, record
+    streams and round trips must not depend on the tile length.  Reads of exactly T, T+1, 2T-1, 2T, ...
+    bases, error-free contigs (unique-predecessor runs spanning many tiles) and noisy long reads."""
+    rng = np.random.default_rng(61)
+    for case in small_cases:
+        src = [c for c in case.contigs if len(c) > 0]
+        for T in (256, 260, 1024):
+            case.ctx.set_tile_len(T)
+            reads = helpers.sample_reads(rng, src, 30, lengths=[T - 1, T, T + 1, 2 * T - 1, 2 * T, 2 * T + 1, 3 * T + 5, 5000, 150, 1],
+                                         error_rates=[0, 0.01, 0.05, 0.2], k=case.k)
+            reads += [np.ascontiguousarray(c) for c in src] + [helpers.random_seq(rng, 3 * T + 2)]
+            bases, off = nt.concat_reads(reads)
+            d, s = case.ctx.matching_statistics(bases, off)
+            for i, r in enumerate(reads):
+                od, os_, _ = case.oracle.matching_statistics(r)
+                lo, hi = int(off[i]), int(off[i + 1])
+                assert (d[lo:hi] == od).all() and (s[lo:hi] == os_).all(), (case.k, T, i, len(r))
+            rec, roff = case.ctx.encode_batch(bases, off)
+            orec, oroff = case.oracle.encode_reads(bases, off, fast=True, threads=8)
+            assert (roff == oroff).all() and (rec == orec).all(), (case.k, T)
+            db, doff = case.ctx.decode_batch(rec)
+            assert (doff == off).all() and (db == bases).all()
+        case.ctx.set_tile_len(0)
+        lrec, _ = case.oracle.encode_reads(bases, off, fast=False, threads=8)   # literal restatement on the last batch
+        assert (lrec == rec).all()
+
+
 def test_encode_sequence_triples_and_dictionary(small_cases):
     rng = np.random.default_rng(7)
     for case in small_cases:
