@@ -312,18 +312,42 @@ def main():
     L = _lib.lib()
     n_rec_c, n_bytes_c, n_seqs_c = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
 
+    e2e_split = [0.0, 0.0]
+
     def e2e_step():
+        ta = time.perf_counter()
         _lib.check(L.ntc_encode_batch(ctx._h, h_bases.data_ptr(), h_off.data_ptr(), n_reads, h_rec.data_ptr(), h_rec.numel(), C.byref(n_rec_c), None))
+        tb = time.perf_counter()
         _lib.check(L.ntc_decode_fasta(ctx._h, h_rec.data_ptr(), n_rec_c.value, lo + 1, h_text.data_ptr(), out_cap, C.byref(n_bytes_c), C.byref(n_seqs_c)))
+        e2e_split[0] += tb - ta
+        e2e_split[1] += time.perf_counter() - tb
+
+    def pcie_peak():
+        """pinned-memory copy bandwidth of this box (GB/s), the ceiling of the end-to-end leg"""
+        nb = min(n_bases, 1 << 30)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        best = [0.0, 0.0]
+        for _ in range(3):
+            e0.record()
+            d_out[:nb].copy_(h_text[:nb], non_blocking=True)
+            e1.record()
+            h_text[:nb].copy_(d_out[:nb], non_blocking=True)
+            e2.record()
+            torch.cuda.synchronize()
+            best = [max(best[0], nb / e0.elapsed_time(e1) / 1e6), max(best[1], nb / e1.elapsed_time(e2) / 1e6)]
+        return best
 
     e2e_steps = max(1, min(steps, 3))
     t_e2e = float("nan")
+    pcie = [None, None]
     if not args.no_e2e:
+        pcie = pcie_peak()
         e2e_step()
         first = (b">seq.%d\n" % (lo + 1)) + bytes(h_bases[:read_len].numpy()) + b"\n"
         if n_seqs_c.value != n_reads or bytes(h_text[: len(first)].numpy()) != first:
             raise SystemExit("bench.py: end-to-end FASTA does not start with the first read")
         barrier()
+        e2e_split[0] = e2e_split[1] = 0.0
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             e2e_step()
@@ -386,7 +410,10 @@ def main():
         "encode_mbases_s": total_bases * steps / (t_enc * 1e-3) / 1e6, "decode_mbases_s": total_bases * steps / (t_dec * 1e-3) / 1e6,
         "records_per_read": n_rec / n_reads, "clocks": clocks,
         "e2e": {"value": total_bases * e2e_steps / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e2e_steps, "api": "ntc_encode_batch + ntc_decode_fasta, pinned host buffers"},
+                "steps": e2e_steps, "api": "ntc_encode_batch + ntc_decode_fasta, pinned host buffers",
+                "encode_ms_per_step": 1e3 * e2e_split[0] / e2e_steps, "decode_ms_per_step": 1e3 * e2e_split[1] / e2e_steps,
+                "pcie_h2d_gbs": pcie[0], "pcie_d2h_gbs": pcie[1],
+                "pcie_floor_ms_per_step": (h2d / pcie[0] + d2h / pcie[1]) / 1e6 if pcie[0] else None},
         "gpu_launches": gpu_launches, "roofline": roofline, "cpu_baseline": cpu, "setup_s": t_setup,
         "index_bytes": ctx.index_bytes(),
     }

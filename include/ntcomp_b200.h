@@ -135,6 +135,20 @@ int32_t ntc_block_write_gpu(ntc_ctx* ctx, const uint64_t* records, uint64_t n_re
 int32_t ntc_column_code(const uint64_t* values, uint64_t n, int32_t rice, uint64_t* words, uint64_t cap, uint64_t* n_words,
                         uint64_t* param);
 
+/* ---------------- file-level host pipeline ("next" row f3) ------------------------------------------
+ * The driver loops of `ntcomp encode` (src/main.rs:141-181) and `ntcomp decode` (src/main.rs:183-211) as
+ * overlapped stages: fastX parsing / block framing on a reader thread, the hot path on the GPU, the block
+ * container (column codes + gzip, or gunzip + decode + zip) per 65,536-read block on n_threads host threads
+ * (<= 0: all cores), and an in-order writer.  Paths may be "-" (stdin / stdout); fastX input may be
+ * gzip-compressed.  encoded.dat layout: src/lib.rs:29-92,232-252.
+ * encode stats[6]: reads, bases, records, bytes written, blocks written, blocks dropped (Q4);
+ * decode stats[6]: sequences, FASTA bytes written, records, bytes read, blocks, 0.  stats may be NULL. */
+int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_path, int32_t n_threads, uint64_t* stats);
+int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path, int32_t n_threads, uint64_t* stats);
+/* `ntcomp build` front end (src/main.rs:97-134): every fastX record of every file is one input sequence */
+int32_t ntc_index_build_from_files(const char* const* paths, uint64_t n_paths, uint32_t k, int32_t add_revcomp,
+                                   int32_t n_threads, ntc_index** out);
+
 /* ---------------- device-resident variants (buffers already in HBM, stream-ordered) ----------
  * Same semantics; all pointers are device pointers on ctx's GPU, `stream` is a cudaStream_t (0 =
  * default stream).  Results that are counts stay on the device: d_counts[0] = n_records / n_seqs,

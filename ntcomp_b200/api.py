@@ -76,6 +76,14 @@ class Index:
         return cls(h)
 
     @classmethod
+    def build_from_files(cls, paths, k, add_revcomp=True, n_threads=0):
+        """`ntcomp build` front end (src/main.rs:97-134): every fastX record of every file is one input sequence"""
+        arr = (C.c_char_p * len(paths))(*[str(p).encode() for p in paths])
+        h = C.c_void_p()
+        check(_lib.lib().ntc_index_build_from_files(arr, len(paths), k, int(add_revcomp), n_threads, C.byref(h)))
+        return cls(h)
+
+    @classmethod
     def load(cls, path):
         h = C.c_void_p()
         check(_lib.lib().ntc_index_load(str(path).encode(), C.byref(h)))
@@ -146,6 +154,18 @@ class Context:
     def set_tile_len(self, tile_len=0):
         """matching-statistics tile length (0 = automatic); results do not depend on it"""
         check(_lib.lib().ntc_ctx_set_tile_len(self._h, int(tile_len)))
+
+    def encode_file(self, fastx_path, out_path, n_threads=0):
+        """`ntcomp encode` (src/main.rs:141-181): fastX file -> encoded.dat; returns the stats dict"""
+        st = np.zeros(6, dtype=np.uint64)
+        check(_lib.lib().ntc_encode_file(self._h, str(fastx_path).encode(), str(out_path).encode(), n_threads, _ptr(st)))
+        return dict(zip(["reads", "bases", "records", "bytes", "blocks", "dropped_blocks"], (int(x) for x in st)))
+
+    def decode_file(self, in_path, out_path, n_threads=0):
+        """`ntcomp decode` (src/main.rs:183-211): encoded.dat -> FASTA text; returns the stats dict"""
+        st = np.zeros(6, dtype=np.uint64)
+        check(_lib.lib().ntc_decode_file(self._h, str(in_path).encode(), str(out_path).encode(), n_threads, _ptr(st)))
+        return dict(zip(["sequences", "fasta_bytes", "records", "bytes_read", "blocks"], (int(x) for x in st)))
 
     def set_profiling(self, on=True):
         check(_lib.lib().ntc_ctx_set_profiling(self._h, int(on)))
@@ -269,3 +289,32 @@ def decode_sequence(encoding, sbwt):
     """src/lib.rs:254."""
     bases, off = sbwt.decode_batch(encoding)
     return [bases[int(off[i]): int(off[i + 1])].tobytes() for i in range(len(off) - 1)]
+
+
+def block_write(records, num_reads):
+    """write_block_to (src/lib.rs:232-252) on the host: one block of encoded.dat (four coded + gzipped columns)"""
+    rec = np.ascontiguousarray(records, dtype=np.uint64)
+    cap = int(_lib.lib().ntc_block_bound(len(rec)))
+    out = np.zeros(cap, dtype=np.uint8)
+    nb = C.c_uint64(0)
+    check(_lib.lib().ntc_block_write(_ptr(rec), len(rec), int(num_reads), _ptr(out), cap, C.byref(nb)))
+    return out[: nb.value].tobytes()
+
+
+def block_read(data):
+    """decode_block up to decode_sequence (src/lib.rs:320-363): (records, bytes consumed); consumed == 0 at EOF"""
+    buf = np.frombuffer(data, dtype=np.uint8)
+    n, used = C.c_uint64(0), C.c_uint64(0)
+    cap = 1024
+    if len(buf) >= 32 * 3:   # capacity from the flags column's value count (third sub-block header)
+        pos = 0
+        for q in range(3):
+            if pos + 32 > len(buf):
+                break
+            bs = int(np.frombuffer(buf[pos: pos + 4].tobytes(), dtype=np.uint32)[0])
+            if q == 2:
+                cap = int(np.frombuffer(buf[pos + 8: pos + 12].tobytes(), dtype=np.uint32)[0]) + 16
+            pos += 32 + bs
+    rec = np.zeros(cap, dtype=np.uint64)
+    check(_lib.lib().ntc_block_read(_ptr(buf) if len(buf) else None, len(buf), _ptr(rec), cap, C.byref(n), C.byref(used)))
+    return rec[: n.value].copy(), used.value

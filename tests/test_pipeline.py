@@ -1,0 +1,133 @@
+"""File-level host pipeline and command-line front end: `ntcomp build / encode / decode`
+(src/main.rs:97-211) over the C ABI.  CPU part: fastX parsing and the build subcommand; the encode /
+decode subcommands must fail loudly without a GPU.  GPU part: files round-trip, block streams equal the
+oracle's record stream block by block, FASTA text is the writer loop's."""
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import helpers
+import ntcomp_b200 as nt
+from ntcomp_b200 import _lib
+from oracle import binding as ob
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CLI = os.path.join(ROOT, "ntcomp_b200", "bin", "ntcomp-b200")
+
+
+def _write_fasta(path, seqs, width=70, lower=False, opener=open):
+    with opener(path, "wb") as f:
+        for i, s in enumerate(seqs):
+            f.write(b">contig%d some description\n" % i)
+            b = bytes(s).lower() if lower else bytes(s)
+            for j in range(0, len(b), width):
+                f.write(b[j:j + width] + b"\r\n" if i % 2 else b[j:j + width] + b"\n")
+
+
+def _write_fastq(path, seqs, opener=open):
+    with opener(path, "wb") as f:
+        for i, s in enumerate(seqs):
+            q = b"@" * len(s)                      # quality lines that start with '@' must not confuse the parser
+            f.write(b"@read%d\n%s\n+\n%s\n" % (i, bytes(s), q))
+
+
+@pytest.fixture(scope="module")
+def genome_and_reads():
+    rng = np.random.default_rng(77)
+    contigs = [helpers.random_seq(rng, n) for n in (40000, 2500, 90)]
+    reads = helpers.sample_reads(rng, contigs, 700, lengths=[150, 150, 150, 91, 40, 400, 1000, 3], error_rates=[0, 0.01, 0.05], k=31)
+    return contigs, reads
+
+
+def test_build_from_files_matches_in_memory_build(tmp_path, genome_and_reads):
+    contigs, _ = genome_and_reads
+    fa, fq = tmp_path / "a.fa", tmp_path / "b.fq.gz"
+    _write_fasta(fa, contigs[:2], lower=True)
+    _write_fastq(fq, contigs[2:], opener=gzip.open)
+    a = nt.Index.build_from_files([fa, fq], 31)
+    b = nt.Index.build(contigs, 31)
+    assert a.n_sets == b.n_sets and (a.lcs() == b.lcs()).all()
+    for x, y in zip(a.rows(), b.rows()):
+        assert (x == y).all()
+    with pytest.raises(nt.NtcError) as e:
+        nt.Index.build_from_files([tmp_path / "missing.fa"], 31)
+    assert e.value.code == 7
+    bad = tmp_path / "bad.fq"
+    bad.write_bytes(b"@r1\nACGT\n+\nII\n")          # truncated quality
+    with pytest.raises(nt.NtcError):
+        nt.Index.build_from_files([bad], 31)
+
+
+def test_cli_build_and_no_gpu_failure(tmp_path, genome_and_reads):
+    contigs, reads = genome_and_reads
+    assert os.path.exists(CLI), "ntcomp-b200 is built by make -C ntcomp_b200/csrc"
+    fa = tmp_path / "ref.fa"
+    _write_fasta(fa, contigs)
+    prefix = str(tmp_path / "idx")
+    lst = tmp_path / "list.tsv"
+    lst.write_text("ref\t%s\n" % fa)
+    subprocess.run([CLI, "build", "-k", "31", "-o", prefix, "-l", str(lst), "-t", "2"], check=True, capture_output=True)
+    idx = nt.Index.load(prefix + ".ntcidx")
+    assert idx.k == 31 and idx.n_sets == nt.Index.build(contigs, 31).n_sets
+    assert subprocess.run([CLI], capture_output=True).returncode == 2
+    import torch
+    if not torch.cuda.is_available():                # product path must fail loudly without a GPU
+        fq = tmp_path / "r.fq"
+        _write_fastq(fq, reads[:5])
+        r = subprocess.run([CLI, "encode", "-i", prefix, str(fq)], capture_output=True)
+        assert r.returncode == 1 and b"no CUDA device" in r.stderr and r.stdout == b""
+
+
+@pytest.mark.gpu
+def test_cli_round_trip_and_block_parity(tmp_path, genome_and_reads, monkeypatch):
+    contigs, reads = genome_and_reads
+    # 3 blocks: shrink nothing -- 65,536-read blocks need > 131,072 reads; repeat the read set
+    reads = (reads * 190)[: 2 * 65536 + 777]
+    fa, fq = tmp_path / "ref.fa", tmp_path / "reads.fq.gz"
+    _write_fasta(fa, contigs)
+    _write_fastq(fq, reads, opener=lambda p, m: gzip.open(p, m, compresslevel=1))
+    prefix = str(tmp_path / "idx")
+    subprocess.run([CLI, "build", "-k", "31", "-o", prefix, str(fa)], check=True, capture_output=True)
+    enc, dec = tmp_path / "encoded.dat", tmp_path / "decoded.fasta"
+    with open(enc, "wb") as f:
+        r = subprocess.run([CLI, "encode", "-i", prefix, str(fq)], stdout=f, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr
+    with open(dec, "wb") as f:
+        r = subprocess.run([CLI, "decode", "-i", prefix, str(enc)], stdout=f, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr
+    assert dec.read_bytes() == helpers.fasta_text(reads, 1)                      # README.md:48-53 diff procedure
+    # block stream: 32 zero bytes, then per 65,536 reads the oracle's records (P1) in the reference's container
+    data = enc.read_bytes()
+    assert data[:32] == bytes(32)
+    index = nt.Index.load(prefix + ".ntcidx")
+    oracle = ob.OracleIndex.from_arrays(index.k, index.n_sets, index.rows(), index.lcs())
+    bases, off = nt.concat_reads(reads)
+    orec, oroff = oracle.encode_reads(bases, off, fast=True, threads=8)
+    pos, lo, n_blocks = 32, 0, 0
+    while pos < len(data):
+        rec, used = nt.block_read(data[pos:])
+        assert used > 0
+        hi = min(len(reads), lo + 65536)
+        assert (rec == orec[int(oroff[lo]): int(oroff[hi])]).all()
+        num_records = int(np.frombuffer(data[pos + 4: pos + 8], dtype=np.uint32)[0])
+        assert num_records == hi - lo                                             # src/main.rs:170,176
+        pos += used
+        lo = hi
+        n_blocks += 1
+    assert n_blocks == 3 and lo == len(reads)
+    # same through the Python mirror of the file API
+    ctx = nt.Context(index, 0)
+    st = ctx.encode_file(fq, tmp_path / "e2.dat", n_threads=3)
+    assert st["reads"] == len(reads) and st["blocks"] == 3 and st["dropped_blocks"] == 0 and st["bytes"] == len(data)
+    assert (tmp_path / "e2.dat").read_bytes() == data
+    st = ctx.decode_file(tmp_path / "e2.dat", tmp_path / "d2.fa", n_threads=3)
+    assert st["sequences"] == len(reads) and (tmp_path / "d2.fa").read_bytes() == dec.read_bytes()
+    # a read with an N makes encode fail with NTC_ERR_BAD_BASE instead of the reference's underflow (Q3)
+    bad = tmp_path / "bad.fa"
+    bad.write_bytes(b">x\nACGTNACGT\n")
+    with pytest.raises(nt.NtcError) as e:
+        ctx.encode_file(bad, tmp_path / "bad.dat")
+    assert e.value.code == 5

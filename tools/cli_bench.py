@@ -1,0 +1,76 @@
+#!/usr/bin/env python
+"""File-to-file throughput of the command-line front end (row f3): synthetic reads of a BASELINE config
+written as FASTA, `ntcomp-b200 build / encode / decode`, wall-clock Mbases/s and the compression ratio.
+    python tools/cli_bench.py [--config C2] [--reads N] [--threads T]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from ntcomp_b200 import synth  # noqa: E402
+
+CLI = os.path.join(ROOT, "ntcomp_b200", "bin", "ntcomp-b200")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", default="C2")
+    ap.add_argument("--reads", type=int, default=None)
+    ap.add_argument("--threads", type=int, default=0)
+    args = ap.parse_args()
+    cfg = dict(synth.CONFIGS[args.config])
+    if args.reads:
+        cfg["n_reads"] = args.reads
+    tmp = tempfile.mkdtemp(prefix="ntc_cli_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    g = synth.genome(cfg["genome"])
+    with open(os.path.join(tmp, "ref.fa"), "wb") as f:
+        f.write(b">genome\n" + bytes(g) + b"\n")
+    bases, off = synth.reads(g, cfg["seed"], 0, cfg["n_reads"], cfg["read_len"], cfg["err_ppm"])
+    L = cfg["read_len"]
+    import numpy as np
+    rows = np.empty((cfg["n_reads"], L + 1), dtype=np.uint8)
+    rows[:, :L] = bases.reshape(-1, L)
+    rows[:, L] = 10
+    with open(os.path.join(tmp, "reads.fa"), "wb") as f:      # FASTA with constant headers (header text is not stored)
+        hdr = np.frombuffer(b">r\n", dtype=np.uint8)
+        out = np.empty((cfg["n_reads"], 3 + L + 1), dtype=np.uint8)
+        out[:, :3] = hdr
+        out[:, 3:] = rows
+        f.write(out.tobytes())
+    prefix = os.path.join(tmp, "idx")
+    thr = ["-t", str(args.threads)] if args.threads else []
+    t0 = time.time()
+    subprocess.run([CLI, "build", "-k", str(cfg["k"]), "-o", prefix, os.path.join(tmp, "ref.fa")] + thr, check=True, capture_output=True)
+    t1 = time.time()
+    with open(os.path.join(tmp, "encoded.dat"), "wb") as f:
+        r = subprocess.run([CLI, "encode", "-i", prefix, os.path.join(tmp, "reads.fa")] + thr, stdout=f, stderr=subprocess.PIPE, check=True)
+    enc_log = r.stderr.decode().strip().splitlines()[-1]
+    t2 = time.time()
+    with open(os.path.join(tmp, "decoded.fa"), "wb") as f:
+        r = subprocess.run([CLI, "decode", "-i", prefix, os.path.join(tmp, "encoded.dat")] + thr, stdout=f, stderr=subprocess.PIPE, check=True)
+    dec_log = r.stderr.decode().strip().splitlines()[-1]
+    t3 = time.time()
+    want = b"".join(b">seq.%d\n%s\n" % (i + 1, bytes(bases[i * L:(i + 1) * L])) for i in range(min(cfg["n_reads"], 1000)))
+    got = open(os.path.join(tmp, "decoded.fa"), "rb").read()
+    n_bases = cfg["n_reads"] * L
+    ok = got.startswith(want) and got.endswith(bytes(bases[-L:]) + b"\n") and got.count(b"\n") == 2 * cfg["n_reads"]
+    line = {"config": args.config, "reads": cfg["n_reads"], "bases": n_bases, "round_trip_ok": ok,
+            "build_s": t1 - t0, "encode_wall_s": t2 - t1, "decode_wall_s": t3 - t2,
+            "encode_log": enc_log, "decode_log": dec_log,
+            "encoded_bytes": os.path.getsize(os.path.join(tmp, "encoded.dat")),
+            "bits_per_base": 8.0 * os.path.getsize(os.path.join(tmp, "encoded.dat")) / n_bases,
+            "host_threads": args.threads or os.cpu_count()}
+    print(json.dumps(line))
+    for fn in os.listdir(tmp):
+        os.remove(os.path.join(tmp, fn))
+    os.rmdir(tmp)
+
+
+if __name__ == "__main__":
+    main()
