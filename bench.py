@@ -212,6 +212,8 @@ def main():
     cfg = config_of(args.config, args.reads)
     if cfg["name"] == "C5" and args.reads is None:
         cfg["n_reads"] = 250_000  # C5 is an 8-GPU config: 2 M reads / 8
+    if cfg["name"] == "C4" and args.reads is None:
+        cfg["n_reads"] = 191 * 65536  # C4 is 100 M reads over up to 8 GPUs: 12.5 M per GPU, on a 65,536-read boundary
     n_reads, read_len = cfg["n_reads"], cfg["read_len"]
     n_bases = n_reads * read_len
 

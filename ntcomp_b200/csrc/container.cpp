@@ -44,20 +44,42 @@ struct BitPacker {
     void finish() { if (fill) { words.push_back(__builtin_bswap64(acc)); acc = 0; fill = 0; } }
 };
 
+// MSB-first reader over big-endian u64 words: a 64-bit window refilled word-wise, unary runs by clz
 struct BitCursor {
     const uint64_t* words; uint64_t n_words; uint64_t bit = 0;
-    inline int next() {
-        uint64_t w = bit >> 6;
-        if (w >= n_words) return -1;
-        int b = (int)((__builtin_bswap64(words[w]) >> (63 - (bit & 63))) & 1);
-        bit++;
-        return b;
+    inline uint64_t word(uint64_t w) const { return w < n_words ? __builtin_bswap64(words[w]) : 0; }
+    // the next 64 bits of the stream, left-aligned (zero-padded past the end)
+    inline uint64_t window() const {
+        const uint64_t w = bit >> 6;
+        const unsigned sh = (unsigned)(bit & 63);
+        uint64_t hi = word(w);
+        return sh ? (hi << sh) | (word(w + 1) >> (64 - sh)) : hi;
     }
-    bool take(unsigned nbits, uint64_t* v) {
-        uint64_t r = 0;
-        for (unsigned i = 0; i < nbits; i++) { int b = next(); if (b < 0) return false; r = (r << 1) | (uint64_t)b; }
-        *v = r;
+    inline bool take(unsigned nbits, uint64_t* v) {                    // nbits <= 64
+        if (nbits == 0) { *v = 0; return true; }
+        if (bit + nbits > n_words * 64) return false;
+        *v = window() >> (64 - nbits);
+        bit += nbits;
         return true;
+    }
+    inline bool unary(uint64_t* q) {                                   // zeros up to and including the terminating one
+        uint64_t zeros = 0;
+        for (;;) {
+            if (bit >= n_words * 64) return false;
+            uint64_t win = window();
+            if (win) {
+                unsigned z = (unsigned)__builtin_clzll(win);
+                if (bit + z >= n_words * 64) return false;
+                zeros += z;
+                bit += z + 1;
+                *q = zeros;
+                return true;
+            }
+            uint64_t room = n_words * 64 - bit;
+            uint64_t step = room < 64 ? room : 64;
+            zeros += step;
+            bit += step;
+        }
     }
 };
 }  // namespace
@@ -112,7 +134,7 @@ bool decode_column_host(const uint64_t* words, uint64_t n_words, uint64_t n, int
     if (rice) {
         for (uint64_t i = 0; i < n; i++) {
             uint64_t q = 0, rem = 0;
-            for (;;) { int b = cur.next(); if (b < 0) return false; if (b) break; q++; }
+            if (!cur.unary(&q)) return false;
             if (param && !cur.take((unsigned)param, &rem)) return false;
             out->push_back((q << param) | rem);
         }
@@ -123,7 +145,7 @@ bool decode_column_host(const uint64_t* words, uint64_t n_words, uint64_t n, int
         for (uint64_t i = 0; i < n; i++) {
             uint64_t x = 0;
             if (l && !cur.take(l, &x)) return false;
-            if (x >= limit) { int b = cur.next(); if (b < 0) return false; x = ((x << 1) | (uint64_t)b) - limit; }
+            if (x >= limit) { uint64_t b; if (!cur.take(1, &b)) return false; x = ((x << 1) | b) - limit; }
             out->push_back(x - 1);                                                 // src/decode.rs:74
         }
     }

@@ -32,7 +32,7 @@ using ntc::set_error;
 namespace {
 
 constexpr uint64_t kBlockReads = 65536;            // src/main.rs:152
-constexpr uint64_t kBatchBlocks = 16;              // blocks handed to the GPU per call
+constexpr uint64_t kBatchBlocks = 8;               // blocks handed to the GPU per call (stage overlap granularity)
 constexpr uint64_t kBatchBases = 768ull << 20;     // ... or this many bases, whichever comes first
 
 // ---- bounded single-producer / single-consumer queue -------------------------------------------
@@ -101,41 +101,42 @@ struct Sink {
 };
 
 // ---- fastX reader (plain or gzip; FASTA with wrapped lines, FASTQ with 4-line or wrapped records) ----
+// Reads the stream in 4 MB pieces and walks lines with memchr; sequence bytes are copied line by line
+// and normalised in place (needletail normalize(true) for the bytes that can reach the encoder:
+// upper-case, U -> T, white space dropped; everything else passes through and is rejected by the encoder
+// unless it is A, C, G or T).
 class FastxReader {
 public:
     bool open(const char* path) {
         f_ = (strcmp(path, "-") == 0) ? gzdopen(0, "rb") : gzopen(path, "rb");
         if (!f_) return false;
         gzbuffer(f_, 1 << 20);
+        buf_.resize(4 << 20);
         return true;
     }
     ~FastxReader() { if (f_) gzclose(f_); }
     // appends the next record's normalised sequence to *bases; 1 = got one, 0 = end of file, -1 = malformed
     int next(std::vector<uint8_t>* bases) {
-        std::string& ln = line_;
-        if (!have_line_ && !read_line()) return 0;
-        while (ln.empty()) { if (!read_line()) return 0; }             // blank lines between records
-        have_line_ = false;
-        raw_len_ = 0;
+        const uint8_t* ln;
+        size_t n;
+        do { if (!line(&ln, &n)) return 0; } while (n == 0);            // blank lines between records
         if (ln[0] == '>') {
-            for (;;) {
-                if (!read_line()) break;
-                if (!ln.empty() && ln[0] == '>') { have_line_ = true; break; }
-                append_normalised(ln, bases);
+            while (peek() >= 0 && peek() != '>') {
+                if (!line(&ln, &n)) break;
+                append_normalised(ln, n, bases);
             }
             return 1;
         }
         if (ln[0] == '@') {
+            size_t want = 0, got = 0;                                  // quality has one byte per sequence byte
             for (;;) {                                                 // sequence lines up to the '+' separator
-                if (!read_line()) return -1;
-                if (!ln.empty() && ln[0] == '+') break;
-                append_normalised(ln, bases);
+                if (!line(&ln, &n)) return -1;
+                if (n && ln[0] == '+') break;
+                want += append_normalised(ln, n, bases);
             }
-            const size_t want = raw_len_;                              // quality has one byte per sequence byte
-            size_t got = 0;
             while (got < want) {
-                if (!read_line()) return -1;
-                got += ln.size();
+                if (!line(&ln, &n)) return -1;
+                got += n;
             }
             return got == want ? 1 : -1;
         }
@@ -144,32 +145,60 @@ public:
 
 private:
     gzFile f_ = nullptr;
-    std::string line_;
-    bool have_line_ = false;
-    size_t raw_len_ = 0;
-    std::vector<char> buf_ = std::vector<char>(1 << 16);
+    std::vector<uint8_t> buf_;
+    size_t lo_ = 0, hi_ = 0;      // unread bytes are buf_[lo_, hi_)
+    bool eof_ = false;
 
-    bool read_line() {                                                 // strips the trailing "\n" / "\r\n"
-        line_.clear();
-        for (;;) {
-            if (!gzgets(f_, buf_.data(), (int)buf_.size())) return !line_.empty();
-            size_t n = strlen(buf_.data());
-            line_.append(buf_.data(), n);
-            if (n && buf_[n - 1] == '\n') break;
-        }
-        while (!line_.empty() && (line_.back() == '\n' || line_.back() == '\r')) line_.pop_back();
+    bool fill() {                 // keeps the unread tail, appends more input; false when nothing was added
+        if (eof_) return false;
+        if (lo_ > 0) { memmove(buf_.data(), buf_.data() + lo_, hi_ - lo_); hi_ -= lo_; lo_ = 0; }
+        if (hi_ == buf_.size()) buf_.resize(buf_.size() * 2);         // a single line longer than the buffer
+        int got = gzread(f_, buf_.data() + hi_, (unsigned)std::min<size_t>(buf_.size() - hi_, 1u << 30));
+        if (got <= 0) { eof_ = true; return false; }
+        hi_ += (size_t)got;
         return true;
     }
-    // needletail normalize(true) for the bytes that can reach the encoder: upper-case, U -> T, white space
-    // dropped; everything else passes through and is rejected by the encoder unless it is A, C, G or T
-    void append_normalised(const std::string& s, std::vector<uint8_t>* out) {
-        for (unsigned char ch : s) {
-            if (ch == ' ' || ch == '\t') continue;
-            raw_len_++;
-            if (ch >= 'a' && ch <= 'z') ch = (unsigned char)(ch - 32);
-            if (ch == 'U') ch = 'T';
-            out->push_back(ch);
+    int peek() {                  // first byte of the next line, -1 at end of input
+        if (lo_ == hi_ && !fill()) return -1;
+        return buf_[lo_];
+    }
+    bool line(const uint8_t** p, size_t* n) {                          // next line without its "\n" / "\r\n"
+        for (;;) {
+            const uint8_t* nl = hi_ > lo_ ? (const uint8_t*)memchr(buf_.data() + lo_, '\n', hi_ - lo_) : nullptr;
+            if (nl) {
+                *p = buf_.data() + lo_;
+                *n = (size_t)(nl - *p);
+                lo_ += *n + 1;
+                break;
+            }
+            if (!fill()) {                                             // last line without a newline
+                if (lo_ == hi_) return false;
+                *p = buf_.data() + lo_;
+                *n = hi_ - lo_;
+                lo_ = hi_;
+                break;
+            }
         }
+        while (*n && ((*p)[*n - 1] == '\r')) (*n)--;
+        return true;
+    }
+    size_t append_normalised(const uint8_t* s, size_t n, std::vector<uint8_t>* out) {
+        const size_t at = out->size();
+        out->resize(at + n);
+        uint8_t* d = out->data() + at;
+        bool blank = false;
+        for (size_t i = 0; i < n; i++) {                               // branch-free: vectorises
+            uint8_t ch = s[i];
+            ch = (uint8_t)(ch - (((ch >= 'a') & (ch <= 'z')) << 5));
+            ch = ch == 'U' ? (uint8_t)'T' : ch;
+            blank |= (ch == ' ') | (ch == '\t');
+            d[i] = ch;
+        }
+        if (!blank) return n;
+        size_t w = 0;
+        for (size_t i = 0; i < n; i++) if (d[i] != ' ' && d[i] != '\t') d[w++] = d[i];
+        out->resize(at + w);
+        return w;
     }
 };
 
