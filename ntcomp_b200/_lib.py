@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libntcomp_b200.so")
+LIB_PATH = os.environ.get("NTC_LIB_PATH") or os.path.join(_HERE, "libntcomp_b200.so")   # override: kernel-variant experiments
 
 NTC_OK = 0
 ERROR_NAMES = {

@@ -25,7 +25,6 @@ struct CountLoad {
 };
 
 inline unsigned blocks_for(uint64_t n, unsigned per) { return (unsigned)((n + per - 1) / per); }
-constexpr uint64_t kMaxDecodeChunks = 256;
 
 // Brackets the launches of one kernel class with CUDA events on the launching stream when
 // profiling is on; always counts launches.
@@ -169,39 +168,53 @@ int32_t encode_pipeline(ntc_ctx* ctx, Lane& lane, int mode, const uint8_t* d_bas
 }
 
 // ------------------------------------------------------------------------------------------
-// decode on device buffers: scans + sequence bookkeeping, then the walk over records [i0, i1)
+// decode on device buffers with the workspaces of `lane`: scans + per-sequence layout (prepare), then
+// FASTA headers + the walk over all records.  Counts land in d_counts ([0] sequences, [1] bytes).
+// off_carry is added to every entry of d_seq_offsets (chunked host path).
 // ------------------------------------------------------------------------------------------
-int32_t decode_prepare(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint64_t cap,
-                       uint64_t* d_seq_offsets, uint64_t cap_seqs, uint64_t* d_counts, cudaStream_t st) {
-    NTC_CUDA_TRY(ensure(&ctx->base_off, (n_rec + 1) * 8));
-    NTC_CUDA_TRY(ensure(&ctx->seq_idx, (n_rec + 1) * 8));
-    NTC_CUDA_TRY(ensure(&ctx->seq_first, (n_rec + 1) * 8));
-    NTC_CUDA_TRY(ensure(&ctx->dec_tiles, scan_num_tiles(n_rec) * sizeof(Pair64)));
-    uint64_t* base_off = (uint64_t*)ctx->base_off.p;
-    uint64_t* seq_idx = (uint64_t*)ctx->seq_idx.p;
-    uint64_t* seq_first = (uint64_t*)ctx->seq_first.p;
-    uint64_t* totals = ctx->d_totals + 6;
+int32_t decode_prepare(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint64_t cap,
+                       uint64_t* d_seq_offsets, uint64_t cap_seqs, uint64_t off_carry, uint64_t* d_counts, cudaStream_t st) {
+    NTC_CUDA_TRY(ensure(&lane.base_off, (n_rec + 1) * 8));
+    NTC_CUDA_TRY(ensure(&lane.seq_idx, (n_rec + 1) * 8));
+    NTC_CUDA_TRY(ensure(&lane.seq_first, (n_rec + 1) * 8));
+    NTC_CUDA_TRY(ensure(&lane.seq_endkey, (n_rec + 1) * 8));
+    NTC_CUDA_TRY(ensure(&lane.dec_tiles, scan_num_tiles(n_rec) * sizeof(Pair64)));
+    NTC_CUDA_TRY(ensure(&lane.dec_small, 64));
+    uint64_t* base_off = (uint64_t*)lane.base_off.p;
+    uint64_t* seq_idx = (uint64_t*)lane.seq_idx.p;
+    uint64_t* seq_first = (uint64_t*)lane.seq_first.p;
+    uint64_t* totals = (uint64_t*)lane.dec_small.p;
     {
         Timed t(ctx, KC_DSCAN, st, 3);
-        exclusive_scan_pairs(RecordLoad{d_records}, n_rec, (Pair64*)ctx->dec_tiles.p, nullptr, totals, base_off, seq_idx, st);
+        exclusive_scan_pairs(RecordLoad{d_records}, n_rec, (Pair64*)lane.dec_tiles.p, nullptr, totals, base_off, seq_idx, st);
     }
     {
         Timed t(ctx, KC_SEQ, st, 2);
         seq_starts_kernel<<<blocks_for(n_rec, 256), 256, 0, st>>>(d_records, n_rec, seq_idx, seq_first);
-        seq_offsets_kernel<<<blocks_for(n_rec + 1, 256), 256, 0, st>>>(base_off, seq_first, totals, n_rec, d_seq_offsets, cap_seqs, first_no,
-                                                                       fasta, cap, d_counts, ctx->d_status);
+        seq_layout_kernel<<<blocks_for(n_rec + 1, 256), 256, 0, st>>>(base_off, seq_first, totals, n_rec, (uint64_t*)lane.seq_endkey.p,
+                                                                      d_seq_offsets, cap_seqs, off_carry, first_no, fasta, cap, d_counts,
+                                                                      ctx->d_status);
     }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
 }
 
-int32_t decode_walk(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* d_out, uint64_t cap,
-                    const uint64_t* d_counts, uint64_t i0, uint64_t i1, cudaStream_t st) {
-    if (i1 <= i0) return NTC_OK;
-    Timed t(ctx, KC_WALK, st);
-    walk_kernel<<<blocks_for(i1 - i0, 128), 128, 0, st>>>(ctx->dix, d_records, n_rec, (const uint64_t*)ctx->base_off.p,
-                                                          (const uint64_t*)ctx->seq_idx.p, (const uint64_t*)ctx->seq_first.p,
-                                                          ctx->d_totals + 6, first_no, fasta, d_out, cap, d_counts, ctx->d_status, i0, i1);
+// n_seqs_bound: an upper bound of the number of sequences (the header kernel's grid); n_rec when unknown
+int32_t decode_walk(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* d_out,
+                    uint64_t cap, const uint64_t* d_counts, uint64_t n_seqs_bound, cudaStream_t st) {
+    if (n_rec == 0) return NTC_OK;
+    if (fasta && n_seqs_bound) {
+        Timed t(ctx, KC_SEQ, st);
+        fasta_header_kernel<<<blocks_for(n_seqs_bound, 256), 256, 0, st>>>((const uint64_t*)lane.base_off.p, (const uint64_t*)lane.seq_first.p,
+                                                                           (const uint64_t*)lane.dec_small.p, n_rec,
+                                                                           (const uint64_t*)lane.seq_endkey.p, first_no, d_out, cap, d_counts);
+    }
+    {
+        Timed t(ctx, KC_WALK, st);
+        walk_kernel<<<blocks_for(n_rec, 128), 128, 0, st>>>(ctx->dix, d_records, n_rec, (const uint64_t*)lane.base_off.p,
+                                                            (const uint64_t*)lane.seq_idx.p, (const uint64_t*)lane.seq_endkey.p, d_out, cap,
+                                                            d_counts, ctx->d_status);
+    }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
 }
@@ -213,9 +226,10 @@ int32_t decode_pipeline(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec,
         if (d_seq_offsets) NTC_CUDA_TRY(cudaMemsetAsync(d_seq_offsets, 0, 8, st));
         return NTC_OK;
     }
-    int32_t rc = decode_prepare(ctx, d_records, n_rec, first_no, fasta, cap, d_seq_offsets, cap_seqs, d_counts, st);
+    Lane& lane = ctx->lanes[0];
+    int32_t rc = decode_prepare(ctx, lane, d_records, n_rec, first_no, fasta, cap, d_seq_offsets, cap_seqs, 0, d_counts, st);
     if (rc) return rc;
-    return decode_walk(ctx, d_records, n_rec, first_no, fasta, d_out, cap, d_counts, 0, n_rec, st);
+    return decode_walk(ctx, lane, d_records, n_rec, first_no, fasta, d_out, cap, d_counts, n_rec, st);
 }
 
 int32_t read_status(ntc_ctx* ctx, cudaStream_t st) {
@@ -249,7 +263,11 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     ctx->n = idx->n;
     if (const char* env = getenv("NTC_MAX_CHUNK_BASES")) {
         unsigned long long v = strtoull(env, nullptr, 10);
-        if (v >= 1024) { ctx->max_chunk_bases = v; ctx->max_chunk_bytes = v; }
+        if (v >= 1024) ctx->max_chunk_bases = v;
+    }
+    if (const char* env = getenv("NTC_MAX_CHUNK_RECORDS")) {
+        unsigned long long v = strtoull(env, nullptr, 10);
+        if (v >= 16) ctx->max_chunk_records = v;
     }
     int threads = (int)std::max(1u, std::thread::hardware_concurrency());
     std::vector<uint32_t> rank;
@@ -274,10 +292,8 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     if ((e = cudaMemcpy(ctx->d_jump, jump.data(), ctx->index_bytes[2], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload jump", e);
     if ((e = cudaMalloc((void**)&ctx->d_status, 16)) != cudaSuccess) return fail("cudaMalloc status", e);
     if ((e = cudaMalloc((void**)&ctx->d_totals, 64)) != cudaSuccess) return fail("cudaMalloc totals", e);
-    if ((e = cudaMalloc((void**)&ctx->d_counts, 32)) != cudaSuccess) return fail("cudaMalloc counts", e);
     cudaMemset(ctx->d_status, 0, 16);
     cudaMemset(ctx->d_totals, 0, 64);
-    cudaMemset(ctx->d_counts, 0, 32);
     for (Lane& ln : ctx->lanes) {
         if ((e = cudaStreamCreateWithFlags(&ln.stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
         if ((e = cudaEventCreateWithFlags(&ln.ev_scan, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
@@ -285,8 +301,6 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
         if ((e = cudaHostAlloc((void**)&ln.h_land, 64, cudaHostAllocDefault)) != cudaSuccess) return fail("cudaHostAlloc", e);
     }
     ctx->stream = ctx->lanes[0].stream;
-    if ((e = cudaEventCreateWithFlags(&ctx->ev_walk, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
-    if ((e = cudaHostAlloc((void**)&ctx->h_bounds, 2 * 8 * (kMaxDecodeChunks + 2), cudaHostAllocDefault)) != cudaSuccess) return fail("cudaHostAlloc", e);
     ctx->dix.rank = (const uint4*)ctx->d_rank;
     ctx->dix.lcsx = (const uint32_t*)ctx->d_lcs;
     ctx->dix.jump = (const uint64_t*)ctx->d_jump;
@@ -309,18 +323,14 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
         if (ln.ev_scan) cudaEventDestroy(ln.ev_scan);
         if (ln.ev_done) cudaEventDestroy(ln.ev_done);
         if (ln.h_land) cudaFreeHost(ln.h_land);
-        DevBuf* lb[] = {&ln.packed, &ln.scratch, &ln.counts, &ln.tiles, &ln.rec_off, &ln.tile_off, &ln.desc, &ln.st_in, &ln.st_off, &ln.st_out, &ln.st_out2};
+        DevBuf* lb[] = {&ln.packed, &ln.scratch, &ln.counts, &ln.tiles, &ln.rec_off, &ln.tile_off, &ln.desc, &ln.base_off, &ln.seq_idx, &ln.seq_first, &ln.seq_endkey, &ln.dec_tiles, &ln.dec_small, &ln.st_in, &ln.st_off, &ln.st_out, &ln.st_out2};
         for (DevBuf* b : lb) release(b);
     }
     free_column_work(ctx);
-    if (ctx->ev_walk) cudaEventDestroy(ctx->ev_walk);
-    if (ctx->h_bounds) cudaFreeHost(ctx->h_bounds);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
     for (auto ev : ctx->event_pool) cudaEventDestroy(ev);
     cudaFree(ctx->d_rank); cudaFree(ctx->d_lcs); cudaFree(ctx->d_jump);
-    cudaFree(ctx->d_status); cudaFree(ctx->d_totals); cudaFree(ctx->d_counts);
-    DevBuf* bufs[] = {&ctx->base_off, &ctx->seq_idx, &ctx->seq_first, &ctx->dec_tiles, &ctx->bounds};
-    for (DevBuf* b : bufs) release(b);
+    cudaFree(ctx->d_status); cudaFree(ctx->d_totals);
     delete ctx;
 }
 

@@ -27,6 +27,9 @@ struct Lane {
     DevBuf packed, scratch, counts, tiles, rec_off;   // encode workspaces
     DevBuf tile_off, desc;                            // tiles per read (scanned) and work-item descriptors of ms_kernel
     DevBuf st_in, st_off, st_out, st_out2;            // staging for host buffers
+    // decode workspaces: base offsets / sequence ids per record, first record and layout word per sequence,
+    // scan tiles, and dec_small = [0..1] scan totals (bases, sequences), [2..3] counts (sequences, bytes)
+    DevBuf base_off, seq_idx, seq_first, seq_endkey, dec_tiles, dec_small;
     cudaEvent_t ev_scan = nullptr, ev_done = nullptr;
     uint64_t* h_land = nullptr;                       // pinned landing zone: [0..1] totals, [2] status
 };
@@ -44,18 +47,13 @@ struct ntc_ctx {
 
     uint32_t* d_status = nullptr;   // [4]
     uint64_t* d_totals = nullptr;   // [8]: ring of 3 encode scan totals (Pair64 each) + decode totals at [6]
-    uint64_t* d_counts = nullptr;   // [4]: internal counts for the host-buffer API
     uint64_t launches = 0;
     uint64_t max_chunk_bases = 96ull << 20;   // host-buffer API chunk (overlap granularity); NTC_MAX_CHUNK_BASES overrides
     uint32_t tile_len = 0;                    // matching-statistics tile length; 0 = chosen per batch (ntc_ctx_set_tile_len)
-    uint64_t max_chunk_bytes = 128ull << 20;  // decode output chunk for D2H overlap
 
     ntc::Lane lanes[2];             // lanes[0] also serves the device-resident API (on the caller's stream)
-    // decode workspaces
-    ntc::DevBuf base_off, seq_idx, seq_first, dec_tiles, bounds;
-    uint64_t* h_bounds = nullptr;   // pinned, decode chunk bounds
+    uint64_t max_chunk_records = 4ull << 20;  // host-buffer decode: records per chunk (NTC_MAX_CHUNK_RECORDS overrides)
     cudaStream_t stream = nullptr;  // == lanes[0].stream
-    cudaEvent_t ev_walk = nullptr;
     void* colwork = nullptr;        // workspaces of the GPU column codec (api_columns.inc)
 
     // optional per-kernel-class timing with CUDA events on the launching stream (bench.py roofline)

@@ -67,13 +67,21 @@ __global__ void __launch_bounds__(256) seq_starts_kernel(const uint64_t* __restr
     seq_starts_thread(rec, n_rec, seq_idx, seq_first, (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
-// seq_offsets[j] = bases before sequence j (relative to the first sequence), j in [0, n_seqs]
-NTC_HD void seq_offsets_thread(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
-                               const uint64_t* __restrict__ totals /* [bases, n_seqs] */, uint64_t n_rec,
-                               uint64_t* __restrict__ seq_offsets, uint64_t cap_seqs, uint64_t first_no, int fasta, uint64_t cap_bytes,
-                               uint64_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t j) {
-    uint64_t n_seqs = totals[1];
-    uint64_t base0 = n_seqs ? base_off[seq_first[0]] : 0;
+// ---- per-sequence layout ---------------------------------------------------------------------
+// One thread per sequence j (plus one for the end marker): everything the walk needs about a sequence
+// collapses into ONE word, seq_endkey[j] = (output position of the sequence's first base) + B_j, where
+// [A_j, B_j) are the sequence's bases in record order coordinates (base_off); the segment of record i
+// then ends at seq_endkey[sid] - base_off[i].  FASTA header digits are counted here, per sequence, not
+// per record (ncu r1: digit arithmetic per record was ~1/3 of walk_kernel's instructions).
+// counts[0] = n_seqs, counts[1] = output bytes; seq_offsets (optional) = bases before sequence j + carry.
+NTC_HD void seq_layout_thread(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
+                              const uint64_t* __restrict__ totals /* [bases, n_seqs] */, uint64_t n_rec,
+                              uint64_t* __restrict__ seq_endkey, uint64_t* __restrict__ seq_offsets, uint64_t cap_seqs, uint64_t off_carry,
+                              uint64_t first_no, int fasta, uint64_t cap_bytes, uint64_t* __restrict__ counts,
+                              uint32_t* __restrict__ status, uint64_t j) {
+    const uint64_t n_seqs = totals[1];
+    if (j > n_seqs) return;
+    const uint64_t base0 = n_seqs ? base_off[seq_first[0]] : 0;
     if (j == 0) {
         uint64_t n_bases = n_seqs ? base_off[n_rec] - base0 : 0;
         uint64_t bytes = fasta ? (n_seqs ? n_bases + fasta_overhead(first_no, n_seqs - 1) + 1 : 0) : n_bases;
@@ -81,16 +89,47 @@ NTC_HD void seq_offsets_thread(const uint64_t* __restrict__ base_off, const uint
         counts[1] = bytes;
         if (bytes > cap_bytes || (seq_offsets && n_seqs > cap_seqs)) NTC_ATOMIC_OR(status, (uint32_t)ST_CAPACITY);
     }
-    if (!seq_offsets || j > n_seqs || j > cap_seqs) return;
-    seq_offsets[j] = (j < n_seqs ? base_off[seq_first[j]] : base_off[n_rec]) - base0;
+    const uint64_t A = j < n_seqs ? base_off[seq_first[j]] : base_off[n_rec];
+    if (seq_offsets && j <= cap_seqs) seq_offsets[j] = A - base0 + off_carry;
+    if (j == n_seqs) return;
+    const uint64_t B = j + 1 < n_seqs ? base_off[seq_first[j + 1]] : base_off[n_rec];
+    const uint64_t lo = A - base0 + (fasta ? fasta_overhead(first_no, j) : 0);
+    seq_endkey[j] = lo + B;
 }
-__global__ void __launch_bounds__(256) seq_offsets_kernel(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
-                                                          const uint64_t* __restrict__ totals, uint64_t n_rec,
-                                                          uint64_t* __restrict__ seq_offsets, uint64_t cap_seqs,
-                                                          uint64_t first_no, int fasta, uint64_t cap_bytes, uint64_t* __restrict__ counts,
-                                                          uint32_t* __restrict__ status) {
-    seq_offsets_thread(base_off, seq_first, totals, n_rec, seq_offsets, cap_seqs, first_no, fasta, cap_bytes, counts, status,
-                       (uint64_t)blockIdx.x * 256 + threadIdx.x);
+__global__ void __launch_bounds__(256) seq_layout_kernel(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
+                                                         const uint64_t* __restrict__ totals, uint64_t n_rec,
+                                                         uint64_t* __restrict__ seq_endkey, uint64_t* __restrict__ seq_offsets,
+                                                         uint64_t cap_seqs, uint64_t off_carry, uint64_t first_no, int fasta,
+                                                         uint64_t cap_bytes, uint64_t* __restrict__ counts, uint32_t* __restrict__ status) {
+    seq_layout_thread(base_off, seq_first, totals, n_rec, seq_endkey, seq_offsets, cap_seqs, off_carry, first_no, fasta, cap_bytes, counts,
+                      status, (uint64_t)blockIdx.x * 256 + threadIdx.x);
+}
+
+// ">seq.N\n" before and "\n" after every sequence (src/main.rs:204-206), one thread per sequence
+NTC_HD void fasta_header_thread(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
+                                const uint64_t* __restrict__ totals, uint64_t n_rec, const uint64_t* __restrict__ seq_endkey,
+                                uint64_t first_no, uint8_t* __restrict__ out, uint64_t cap_bytes, const uint64_t* __restrict__ counts,
+                                uint64_t j) {
+    const uint64_t n_seqs = totals[1];
+    if (j >= n_seqs || counts[1] > cap_bytes) return;
+    const uint64_t A = base_off[seq_first[j]];
+    const uint64_t B = j + 1 < n_seqs ? base_off[seq_first[j + 1]] : base_off[n_rec];
+    const uint64_t lo = seq_endkey[j] - B;
+    uint64_t no = first_no + j;
+    const uint32_t dg = dec_digits(no);
+    uint8_t* h = out + lo - (6 + dg);
+    h[0] = '>'; h[1] = 's'; h[2] = 'e'; h[3] = 'q'; h[4] = '.';
+    for (uint32_t q = 0; q < dg; q++) { h[5 + dg - 1 - q] = (uint8_t)('0' + no % 10); no /= 10; }
+    h[5 + dg] = '\n';
+    out[lo + (B - A)] = '\n';
+}
+__global__ void __launch_bounds__(256) fasta_header_kernel(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
+                                                           const uint64_t* __restrict__ totals, uint64_t n_rec,
+                                                           const uint64_t* __restrict__ seq_endkey, uint64_t first_no,
+                                                           uint8_t* __restrict__ out, uint64_t cap_bytes,
+                                                           const uint64_t* __restrict__ counts) {
+    fasta_header_thread(base_off, seq_first, totals, n_rec, seq_endkey, first_no, out, cap_bytes, counts,
+                        (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
 // ---- leftward write combiner ---------------------------------------------------------------
@@ -165,43 +204,25 @@ NTC_HD void emit_codes(LeftWriter& w, uint32_t codes, uint32_t t, bool last) {
     else w.push_last(hi, t);
 }
 
-// one thread per record: walk / unpack and store ASCII bases (and FASTA header + newline on the
-// record that opens a sequence)
+// one thread per record: walk / unpack and store ASCII bases
 NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, uint64_t n_rec, const uint64_t* __restrict__ base_off,
-                        const uint64_t* __restrict__ seq_idx, const uint64_t* __restrict__ seq_first, const uint64_t* __restrict__ totals,
-                        uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes, const uint64_t* __restrict__ counts,
-                        uint32_t* __restrict__ status, uint64_t i) {
+                        const uint64_t* __restrict__ seq_idx, const uint64_t* __restrict__ seq_endkey, uint8_t* __restrict__ out,
+                        uint64_t cap_bytes, const uint64_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t i) {
     if (i >= n_rec) return;
     if (counts[1] > cap_bytes) return;  // capacity error already flagged
     const uint64_t w = NTC_LDG(rec + i);
     const uint32_t flag = (uint32_t)(w >> 56);
-    const uint64_t n_seqs = totals[1];
-    uint64_t incl = seq_idx[i] + (flag & 1u);  // sequences opened up to and including this record
-    if (incl == 0) return;                      // records before the first `first` flag are dropped (src/lib.rs:308-317)
-    const uint64_t sid = incl - 1;
-    const uint64_t base0 = base_off[seq_first[0]];
-    const uint64_t A = base_off[seq_first[sid]];
-    const uint64_t B = sid + 1 < n_seqs ? base_off[seq_first[sid + 1]] : base_off[n_rec];
-    uint32_t L = (uint32_t)(base_off[i + 1] - base_off[i]);
-    // segment [A + B - E[i+1], A + B - E[i]) of the base stream
-    uint64_t seg_end = A + B - base_off[i] - base0;
-    uint64_t shift = fasta ? fasta_overhead(first_no, sid) : 0;
-
-    if (fasta && (flag & 1u)) {  // header before the sequence, newline after it
-        uint64_t seq_lo = A - base0 + shift, seq_hi = B - base0 + shift;
-        uint64_t no = first_no + sid;
-        uint32_t dg = dec_digits(no);
-        uint8_t* h = out + seq_lo - (6 + dg);
-        h[0] = '>'; h[1] = 's'; h[2] = 'e'; h[3] = 'q'; h[4] = '.';
-        for (uint32_t q = 0; q < dg; q++) { h[5 + dg - 1 - q] = (uint8_t)('0' + no % 10); no /= 10; }
-        h[5 + dg] = '\n';
-        out[seq_hi] = '\n';
-    }
+    const uint64_t incl = seq_idx[i] + (flag & 1u);  // sequences opened up to and including this record
+    if (incl == 0) return;                            // records before the first `first` flag are dropped (src/lib.rs:308-317)
+    const uint64_t bo = base_off[i];
+    const uint32_t L = (uint32_t)(base_off[i + 1] - bo);
+    // records of a sequence run from its END to its START: this one ends at (sequence end) - (bases before it)
+    const uint64_t seg_end = seq_endkey[incl - 1] - bo;
     if (L == 0) return;
     // the output buffer may be misaligned by the caller: fold the misalignment into the position
     const uint64_t mis = (uint64_t)((uintptr_t)out & 7u);
     LeftWriter lw;
-    lw.init(out - mis, seg_end + shift + mis);
+    lw.init(out - mis, seg_end + mis);
 
     if (flag & 2u) {  // literal record (<= 32 bases), src/lib.rs:295-306
         uint64_t bits = w & ((1ull << (2 * L)) - 1ull);  // L <= 32 here; L == 32 keeps all 56 bits + zeros
@@ -230,37 +251,9 @@ NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, ui
 }
 __global__ void __launch_bounds__(128) walk_kernel(DevIndex ix, const uint64_t* __restrict__ rec, uint64_t n_rec,
                                                    const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_idx,
-                                                   const uint64_t* __restrict__ seq_first, const uint64_t* __restrict__ totals,
-                                                   uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes,
-                                                   const uint64_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t i0,
-                                                   uint64_t i1) {
-    // records [i0, i1): the host-buffer API walks the stream in chunks so D2H overlaps the next chunk
-    uint64_t i = i0 + (uint64_t)blockIdx.x * 128 + threadIdx.x;
-    if (i >= i1) return;
-    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_first, totals, first_no, fasta, out, cap_bytes, counts, status, i);
-}
-
-// chunk plan for the host-buffer API: chunk j covers sequences [j*S, (j+1)*S); writes the first record
-// and the first output byte of every chunk (entry n_chunks = end)
-NTC_HD void chunk_bounds_thread(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
-                                const uint64_t* __restrict__ totals, const uint64_t* __restrict__ counts, uint64_t n_rec,
-                                uint64_t first_no, int fasta, uint64_t seqs_per_chunk, uint64_t n_chunks, uint64_t* __restrict__ bounds,
-                                uint64_t j) {
-    if (j > n_chunks) return;
-    const uint64_t n_seqs = totals[1];
-    uint64_t sj = j * seqs_per_chunk;
-    if (sj >= n_seqs || j == n_chunks) { bounds[2 * j] = n_rec; bounds[2 * j + 1] = counts[1]; return; }
-    const uint64_t base0 = base_off[seq_first[0]];
-    uint64_t byte = base_off[seq_first[sj]] - base0;
-    if (fasta) byte += fasta_overhead(first_no, sj) - (6 + dec_digits(first_no + sj));   // start of the header line
-    bounds[2 * j] = seq_first[sj];
-    bounds[2 * j + 1] = byte;
-}
-__global__ void chunk_bounds_kernel(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
-                                    const uint64_t* __restrict__ totals, const uint64_t* __restrict__ counts, uint64_t n_rec,
-                                    uint64_t first_no, int fasta, uint64_t seqs_per_chunk, uint64_t n_chunks, uint64_t* __restrict__ bounds) {
-    chunk_bounds_thread(base_off, seq_first, totals, counts, n_rec, first_no, fasta, seqs_per_chunk, n_chunks, bounds,
-                        (uint64_t)blockIdx.x * blockDim.x + threadIdx.x);
+                                                   const uint64_t* __restrict__ seq_endkey, uint8_t* __restrict__ out, uint64_t cap_bytes,
+                                                   const uint64_t* __restrict__ counts, uint32_t* __restrict__ status) {
+    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_endkey, out, cap_bytes, counts, status, (uint64_t)blockIdx.x * 128 + threadIdx.x);
 }
 
 }  // namespace ntc

@@ -95,7 +95,10 @@ NTC_HD CachePolicy make_policies() {
     return p;
 }
 NTC_HD uint4 ld16_keep(const uint4* ptr, uint64_t pol) {
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__) && defined(NTC_NO_HINTS)
+    (void)pol;
+    return __ldg(ptr);
+#elif defined(__CUDA_ARCH__)
     uint4 v;
     asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr), "l"(pol));
     return v;
@@ -105,7 +108,10 @@ NTC_HD uint4 ld16_keep(const uint4* ptr, uint64_t pol) {
 #endif
 }
 NTC_HD uint32_t ld4_keep(const uint32_t* ptr, uint64_t pol) {
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__) && defined(NTC_NO_HINTS)
+    (void)pol;
+    return __ldg(ptr);
+#elif defined(__CUDA_ARCH__)
     uint32_t v;
     asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(ptr), "l"(pol));
     return v;

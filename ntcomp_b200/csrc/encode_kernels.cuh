@@ -191,7 +191,10 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
     uint64_t word = packed[(a + j) >> 5];
     uint32_t c = (uint32_t)(word >> (((a + j) & 31) * 2)) & 3u;
     while (j < p1) {
-        const uint32_t bs = s / 48u, be = e / 48u;
+        // a singleton interval [s, s+1) -- the common case once the match is longer than ~log4(n) -- needs one
+        // entry only, also when s is the last node of its block: rank(s+1) = rank(s) + row bit of s
+        const bool single = e == s + 1u;
+        const uint32_t bs = s / 48u, be = single ? bs : e / 48u;
         const uint32_t os = s - bs * 48u, oe = e - be * 48u;
         const uint4 va = ld16_keep(ix.rank + (size_t)bs * 4 + c, pol.keep);
         // LCS words of the interval ends: loaded speculatively only while d is in the window where
@@ -199,7 +202,6 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         // (ncu r1 v3: unconditional speculation doubled the sector traffic; v5: d < 20 still spent 39% of
         // all load sectors on it)
         const bool spec = force || (d - ix.spec_lo < ix.spec_span);   // unsigned: spec_lo <= d < spec_lo + spec_span
-        const bool single = e == s + 1u;
         uint32_t xs = 0, xe = 0;
         if (spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = single ? xs : ld4_keep(ix.lcsx + (e - 1u), pol.keep); }
         const uint4 vb = (be != bs) ? ld16_keep(ix.rank + (size_t)be * 4 + c, pol.keep) : va;
@@ -324,7 +326,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 
 constexpr uint32_t kMsStageWords = 1024;  // 8 KB of packed reads per block (128 reads x up to 256 bases); longer reads load from global
 
-__global__ void __launch_bounds__(kMsThreads, 10) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
+#ifndef NTC_MS_MIN_BLOCKS
+#define NTC_MS_MIN_BLOCKS 10
+#endif
+__global__ void __launch_bounds__(kMsThreads, NTC_MS_MIN_BLOCKS) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
                                                         const uint64_t* __restrict__ offsets, const uint64_t* __restrict__ desc,
                                                         const uint64_t* __restrict__ n_items, uint32_t T,
                                                         uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts,

@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <functional>
@@ -32,8 +33,16 @@ using ntc::set_error;
 namespace {
 
 constexpr uint64_t kBlockReads = 65536;            // src/main.rs:152
-constexpr uint64_t kBatchBlocks = 8;               // blocks handed to the GPU per call (stage overlap granularity)
+constexpr uint64_t kBatchBlocksDefault = 8;        // blocks handed to the GPU per call (stage overlap granularity)
 constexpr uint64_t kBatchBases = 768ull << 20;     // ... or this many bases, whichever comes first
+
+uint64_t batch_blocks() {                          // NTC_PIPELINE_BATCH_BLOCKS overrides (tests: several groups from small files)
+    if (const char* env = getenv("NTC_PIPELINE_BATCH_BLOCKS")) {
+        unsigned long long v = strtoull(env, nullptr, 10);
+        if (v >= 1 && v <= 4096) return v;
+    }
+    return kBatchBlocksDefault;
+}
 
 // ---- bounded single-producer / single-consumer queue -------------------------------------------
 template <typename T>
@@ -233,6 +242,7 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
     if (!sink.write(file_header, 32)) { set_error("write failed"); return NTC_ERR_IO; }
     st[3] = 32;
 
+    const uint64_t kBatchBlocks = batch_blocks();
     Channel<ReadBatch> parsed(2);
     Channel<BytesBatch> coded(2);
     // stage 1: parse
@@ -334,6 +344,7 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
     if (fread(file_header, 1, 32, in) != 32) { if (in != stdin) fclose(in); set_error("truncated file header"); return NTC_ERR_IO; }
     st[3] = 32;
 
+    const uint64_t kBatchBlocks = batch_blocks();
     struct RecBatch { std::vector<uint64_t> records; uint64_t n_blocks = 0; int32_t rc = NTC_OK; std::string msg; };
     Channel<RecBatch> unpacked(2);
     Channel<BytesBatch> texts(2);

@@ -115,10 +115,15 @@ uint32_t emul_decode(void* ep, const uint64_t* rec, uint64_t n_rec, uint64_t fir
     base_off[n_rec] = a; seq_idx[n_rec] = b;
     uint64_t totals[2] = {a, b};
     for (uint64_t i = 0; i < n_rec; i++) seq_starts_thread(rec, n_rec, seq_idx.data(), seq_first.data(), i);
+    std::vector<uint64_t> seq_endkey(n_rec + 1, 0);
     for (uint64_t j = 0; j <= n_rec; j++)
-        seq_offsets_thread(base_off.data(), seq_first.data(), totals, n_rec, seq_offsets, cap_seqs, first_no, fasta, cap, counts, &status, j);
+        seq_layout_thread(base_off.data(), seq_first.data(), totals, n_rec, seq_endkey.data(), seq_offsets, cap_seqs, 0, first_no, fasta, cap,
+                          counts, &status, j);
+    if (fasta)
+        for (uint64_t j = 0; j < n_rec; j++)
+            fasta_header_thread(base_off.data(), seq_first.data(), totals, n_rec, seq_endkey.data(), first_no, out, cap, counts, j);
     for (uint64_t i = 0; i < n_rec; i++)
-        walk_thread(e->dix, rec, n_rec, base_off.data(), seq_idx.data(), seq_first.data(), totals, first_no, fasta, out, cap, counts, &status, i);
+        walk_thread(e->dix, rec, n_rec, base_off.data(), seq_idx.data(), seq_endkey.data(), out, cap, counts, &status, i);
     return status;
 }
 

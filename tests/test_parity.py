@@ -252,6 +252,18 @@ def test_index_with_missing_base_flags_absent_base(backend):
     assert oe.value.code == -3
 
 
+def _decode_with_cap(ctx, rec, cap):
+    import ctypes as C
+    from ntcomp_b200 import _lib
+    rec = np.ascontiguousarray(rec, dtype=np.uint64)
+    out = np.zeros(cap + 64, dtype=np.uint8)
+    soff = np.zeros(len(rec) + 1, dtype=np.uint64)
+    n = C.c_uint64(0)
+    _lib.check(_lib.lib().ntc_decode_batch(ctx._h, rec.ctypes.data_as(C.c_void_p), len(rec), out.ctypes.data_as(C.c_void_p), cap,
+                                           soff.ctypes.data_as(C.c_void_p), len(rec), C.byref(n)))
+    return out, soff, n.value
+
+
 @pytest.mark.gpu
 def test_chunked_host_path_matches_unchunked(monkeypatch, small_cases):
     if small_cases[0].backend != "gpu":
@@ -262,17 +274,27 @@ def test_chunked_host_path_matches_unchunked(monkeypatch, small_cases):
     bases, off = nt.concat_reads(reads)
     rec, roff = case0.ctx.encode_batch(bases, off)
     monkeypatch.setenv("NTC_MAX_CHUNK_BASES", "4096")
+    monkeypatch.setenv("NTC_MAX_CHUNK_RECORDS", "64")           # decode: many chunks, alternating lanes
     ctx2 = nt.Context(case0.index, 0)
     rec2, roff2 = ctx2.encode_batch(bases, off)
     assert (rec == rec2).all() and (roff == roff2).all()
     tri, _ = case0.ctx.encode_sequence_batch(bases, off)
     tri2, _ = ctx2.encode_sequence_batch(bases, off)
     assert (tri == tri2).all()
-    # chunked decode (walk per chunk of sequences, D2H overlapped) == one-shot decode == input
+    # chunked decode (chunks start on records that open a sequence; numbering / offsets carried across) == input
     db, doff = ctx2.decode_batch(rec2)
     assert (db == bases).all() and (doff == off).all()
-    text, n = ctx2.decode_fasta(rec2, 12345)
-    assert text == helpers.fasta_text(reads, 12345) and n == len(reads)
+    for first in (1, 9995, 12345):                               # digit-count changes inside a chunk and across chunks
+        text, n = ctx2.decode_fasta(rec2, first)
+        assert text == helpers.fasta_text(reads, first) and n == len(reads)
+    # leading records without a `first` flag are dropped (src/lib.rs:308-317), also when they fill whole chunks
+    tail = rec[int(roff[len(reads) - 3]) + 1:]                   # starts inside the last contig-sized read: > 64 orphan records
+    db2, doff2 = ctx2.decode_batch(tail)
+    db3, doff3 = case0.ctx.decode_batch(tail)
+    assert (db2 == db3).all() and (doff2 == doff3).all()
+    with pytest.raises(nt.NtcError) as e:                        # capacity error in a later chunk
+        _decode_with_cap(ctx2, rec2, len(bases) - 5)
+    assert e.value.code == 3
     with pytest.raises(nt.NtcError) as e:                        # an error in a middle chunk drains both lanes cleanly
         ctx2.encode_batch(*nt.concat_reads(reads[:200] + [b"ACGTNNNN"] + reads[200:]))
     assert e.value.code == 5

@@ -125,6 +125,13 @@ def test_cli_round_trip_and_block_parity(tmp_path, genome_and_reads, monkeypatch
     assert (tmp_path / "e2.dat").read_bytes() == data
     st = ctx.decode_file(tmp_path / "e2.dat", tmp_path / "d2.fa", n_threads=3)
     assert st["sequences"] == len(reads) and (tmp_path / "d2.fa").read_bytes() == dec.read_bytes()
+    # several GPU batches per file (one block per batch): same bytes, same text
+    monkeypatch.setenv("NTC_PIPELINE_BATCH_BLOCKS", "1")
+    ctx.encode_file(fq, tmp_path / "e3.dat", n_threads=2)
+    assert (tmp_path / "e3.dat").read_bytes() == data
+    ctx.decode_file(tmp_path / "e3.dat", tmp_path / "d3.fa", n_threads=2)
+    assert (tmp_path / "d3.fa").read_bytes() == dec.read_bytes()
+    monkeypatch.delenv("NTC_PIPELINE_BATCH_BLOCKS")
     # a read with an N makes encode fail with NTC_ERR_BAD_BASE instead of the reference's underflow (Q3)
     bad = tmp_path / "bad.fa"
     bad.write_bytes(b">x\nACGTNACGT\n")

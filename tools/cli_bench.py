@@ -23,11 +23,12 @@ def main():
     ap.add_argument("--config", default="C2")
     ap.add_argument("--reads", type=int, default=None)
     ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--tmp", default=None, help="scratch directory (default: the system temp dir)")
     args = ap.parse_args()
     cfg = dict(synth.CONFIGS[args.config])
     if args.reads:
         cfg["n_reads"] = args.reads
-    tmp = tempfile.mkdtemp(prefix="ntc_cli_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    tmp = tempfile.mkdtemp(prefix="ntc_cli_", dir=args.tmp)
     g = synth.genome(cfg["genome"])
     with open(os.path.join(tmp, "ref.fa"), "wb") as f:
         f.write(b">genome\n" + bytes(g) + b"\n")
@@ -49,11 +50,15 @@ def main():
     subprocess.run([CLI, "build", "-k", str(cfg["k"]), "-o", prefix, os.path.join(tmp, "ref.fa")] + thr, check=True, capture_output=True)
     t1 = time.time()
     with open(os.path.join(tmp, "encoded.dat"), "wb") as f:
-        r = subprocess.run([CLI, "encode", "-i", prefix, os.path.join(tmp, "reads.fa")] + thr, stdout=f, stderr=subprocess.PIPE, check=True)
+        r = subprocess.run([CLI, "encode", "-i", prefix, os.path.join(tmp, "reads.fa")] + thr, stdout=f, stderr=subprocess.PIPE)
+    if r.returncode:
+        raise SystemExit("encode failed: " + r.stderr.decode())
     enc_log = r.stderr.decode().strip().splitlines()[-1]
     t2 = time.time()
     with open(os.path.join(tmp, "decoded.fa"), "wb") as f:
-        r = subprocess.run([CLI, "decode", "-i", prefix, os.path.join(tmp, "encoded.dat")] + thr, stdout=f, stderr=subprocess.PIPE, check=True)
+        r = subprocess.run([CLI, "decode", "-i", prefix, os.path.join(tmp, "encoded.dat")] + thr, stdout=f, stderr=subprocess.PIPE)
+    if r.returncode:
+        raise SystemExit("decode failed: " + r.stderr.decode())
     dec_log = r.stderr.decode().strip().splitlines()[-1]
     t3 = time.time()
     want = b"".join(b">seq.%d\n%s\n" % (i + 1, bytes(bases[i * L:(i + 1) * L])) for i in range(min(cfg["n_reads"], 1000)))
