@@ -389,6 +389,7 @@ def main():
                       "peak_source": "ntc_l2_random_bench: independent 16 B loads, 48 MB buffer, %.1f G sectors/s (16 MB: %.1f, dependent chain: %.1f)" % (
                           l2_gsect, l2_gsect_small, l2_dep)},
         "kernel_ms_per_launch": {k: (v[0] / v[1] if v[1] else 0.0) for k, v in ktimes.items()},
+        "kernel_ms_per_step": {k: v[0] / steps for k, v in ktimes.items()},
         "kernel_share_of_step": {k: v[0] / (t_total if t_total else 1) for k, v in ktimes.items()},
         "dominant": top[0],
         "decode_walk": {"algorithmic_bytes_per_base": 32, "achieved": n_bases * 32.0 / ((walk_ms / max(walk_launches, 1)) * 1e-3) / 1e9,

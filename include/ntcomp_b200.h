@@ -127,6 +127,14 @@ int32_t ntc_block_write(const uint64_t* records, uint64_t n_records, uint64_t nu
                         uint64_t* n_bytes);
 int32_t ntc_block_read(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records,
                        uint64_t* consumed);
+/* ntc_block_read with options.  NTC_BLOCK_FULL_LAST_LITERAL_WORD: a block whose literal bases are a non-zero
+ * multiple of 31 ends in a full literal word; the reference's zip_block_contents takes that word to hold
+ * `bitnuc_len % 31` = 0 bases and panics at src/decode.rs:138, so ntc_block_read reports
+ * NTC_ERR_IO for such a block.  With the flag the word is read as the 31 bases the encoder put there --
+ * the file pipeline uses it, so every file the encoder writes can be decoded. */
+#define NTC_BLOCK_FULL_LAST_LITERAL_WORD 1
+int32_t ntc_block_read_ex(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records,
+                          uint64_t* consumed, int32_t flags);
 /* write_block_to with the column split and the Rice / minimal-binary bit packing on the GPU (prefix sum
  * of code lengths + atomic OR into the MSB-first stream); gzip on the host.  Same bytes as ntc_block_write. */
 int32_t ntc_block_write_gpu(ntc_ctx* ctx, const uint64_t* records, uint64_t n_records, uint64_t num_reads, uint8_t* out,

@@ -301,8 +301,9 @@ def block_write(records, num_reads):
     return out[: nb.value].tobytes()
 
 
-def block_read(data):
-    """decode_block up to decode_sequence (src/lib.rs:320-363): (records, bytes consumed); consumed == 0 at EOF"""
+def block_read(data, full_last_literal_word=False):
+    """decode_block up to decode_sequence (src/lib.rs:320-363): (records, bytes consumed); consumed == 0 at EOF.
+    full_last_literal_word: decode blocks the reference panics on (literal bases a multiple of 31)"""
     buf = np.frombuffer(data, dtype=np.uint8)
     n, used = C.c_uint64(0), C.c_uint64(0)
     cap = 1024
@@ -316,5 +317,6 @@ def block_read(data):
                 cap = int(np.frombuffer(buf[pos + 8: pos + 12].tobytes(), dtype=np.uint32)[0]) + 16
             pos += 32 + bs
     rec = np.zeros(cap, dtype=np.uint64)
-    check(_lib.lib().ntc_block_read(_ptr(buf) if len(buf) else None, len(buf), _ptr(rec), cap, C.byref(n), C.byref(used)))
+    check(_lib.lib().ntc_block_read_ex(_ptr(buf) if len(buf) else None, len(buf), _ptr(rec), cap, C.byref(n), C.byref(used),
+                                       1 if full_last_literal_word else 0))
     return rec[: n.value].copy(), used.value

@@ -45,6 +45,16 @@ struct Timed {
     }
 };
 
+// Results the host waits for (scan totals, status word) are written straight into the lane's pinned landing
+// zone (UVA: cudaHostAlloc memory is device-accessible) instead of going through a cudaMemcpyAsync: a small
+// D2H copy queues behind the other lane's bulk D2H on the copy engine and would serialise the two lanes.
+__global__ void publish_kernel(const uint64_t* __restrict__ pair, const uint32_t* __restrict__ status, volatile uint64_t* land) {
+    land[0] = pair[0];
+    land[1] = pair[1];
+    land[2] = *status;
+    __threadfence_system();
+}
+
 __global__ void copy_totals_kernel(const uint64_t* totals, uint64_t* counts) {
     counts[0] = totals[0];
     counts[1] = totals[0] * 8;
@@ -199,21 +209,15 @@ int32_t decode_prepare(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint
     return NTC_OK;
 }
 
-// n_seqs_bound: an upper bound of the number of sequences (the header kernel's grid); n_rec when unknown
 int32_t decode_walk(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* d_out,
-                    uint64_t cap, const uint64_t* d_counts, uint64_t n_seqs_bound, cudaStream_t st) {
+                    uint64_t cap, const uint64_t* d_counts, cudaStream_t st) {
     if (n_rec == 0) return NTC_OK;
-    if (fasta && n_seqs_bound) {
-        Timed t(ctx, KC_SEQ, st);
-        fasta_header_kernel<<<blocks_for(n_seqs_bound, 256), 256, 0, st>>>((const uint64_t*)lane.base_off.p, (const uint64_t*)lane.seq_first.p,
-                                                                           (const uint64_t*)lane.dec_small.p, n_rec,
-                                                                           (const uint64_t*)lane.seq_endkey.p, first_no, d_out, cap, d_counts);
-    }
     {
         Timed t(ctx, KC_WALK, st);
         walk_kernel<<<blocks_for(n_rec, 128), 128, 0, st>>>(ctx->dix, d_records, n_rec, (const uint64_t*)lane.base_off.p,
-                                                            (const uint64_t*)lane.seq_idx.p, (const uint64_t*)lane.seq_endkey.p, d_out, cap,
-                                                            d_counts, ctx->d_status);
+                                                            (const uint64_t*)lane.seq_idx.p, (const uint64_t*)lane.seq_endkey.p,
+                                                            (const uint64_t*)lane.dec_small.p, first_no, fasta, d_out, cap, d_counts,
+                                                            ctx->d_status);
     }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
@@ -229,7 +233,7 @@ int32_t decode_pipeline(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec,
     Lane& lane = ctx->lanes[0];
     int32_t rc = decode_prepare(ctx, lane, d_records, n_rec, first_no, fasta, cap, d_seq_offsets, cap_seqs, 0, d_counts, st);
     if (rc) return rc;
-    return decode_walk(ctx, lane, d_records, n_rec, first_no, fasta, d_out, cap, d_counts, n_rec, st);
+    return decode_walk(ctx, lane, d_records, n_rec, first_no, fasta, d_out, cap, d_counts, st);
 }
 
 int32_t read_status(ntc_ctx* ctx, cudaStream_t st) {
@@ -298,7 +302,7 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
         if ((e = cudaStreamCreateWithFlags(&ln.stream, cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
         if ((e = cudaEventCreateWithFlags(&ln.ev_scan, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
         if ((e = cudaEventCreateWithFlags(&ln.ev_done, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
-        if ((e = cudaHostAlloc((void**)&ln.h_land, 64, cudaHostAllocDefault)) != cudaSuccess) return fail("cudaHostAlloc", e);
+        if ((e = cudaHostAlloc((void**)&ln.h_land, 64, cudaHostAllocMapped)) != cudaSuccess) return fail("cudaHostAlloc", e);
     }
     ctx->stream = ctx->lanes[0].stream;
     ctx->dix.rank = (const uint4*)ctx->d_rank;

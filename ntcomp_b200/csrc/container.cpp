@@ -176,7 +176,7 @@ void split_records(const uint64_t* rec, uint64_t n, BlockColumns* c) {
     if (held) c->literals.push_back(cur);
 }
 
-int zip_columns(const BlockColumns& c, std::vector<uint64_t>* rec) {
+int zip_columns(const BlockColumns& c, std::vector<uint64_t>* rec, bool full_last_word) {
     if (c.colex.size() != c.len.size()) return -1;                                // src/decode.rs:108
     uint64_t lit_bases = 0;
     for (uint64_t f : c.flags) lit_bases += (f & 0xFC) >> 2;
@@ -184,6 +184,9 @@ int zip_columns(const BlockColumns& c, std::vector<uint64_t>* rec) {
     auto base_at = [&](uint64_t pos, bool* ok) -> uint64_t {
         uint64_t wi = pos / 31, off = pos % 31;
         uint64_t in_word = wi + 1 == c.literals.size() ? lit_bases % 31 : 31;
+        // full_last_word: a block whose literal bases are a non-zero multiple of 31 has a full last word; the
+        // reference reads it as empty and panics at src/decode.rs:138 (Q5) -- the file pipeline decodes it
+        if (full_last_word && in_word == 0) in_word = 31;
         if (wi >= c.literals.size() || off >= in_word) { *ok = false; return 0; }
         return (c.literals[wi] >> (2 * off)) & 3ull;
     };
@@ -331,7 +334,8 @@ int32_t ntc_block_write(const uint64_t* records, uint64_t n_records, uint64_t nu
     return NTC_OK;
 }
 
-int32_t ntc_block_read(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records, uint64_t* consumed) {
+static int32_t block_read_impl(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records, uint64_t* consumed,
+                               bool full_last_word) {
     if (!n_records || !consumed || (size && !data)) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
     *n_records = 0;
     *consumed = 0;
@@ -346,13 +350,22 @@ int32_t ntc_block_read(const uint8_t* data, uint64_t size, uint64_t* records, ui
         pos += (uint64_t)used;
     }
     std::vector<uint64_t> rec;
-    int z = zip_columns(c, &rec);
+    int z = zip_columns(c, &rec, full_last_word);
     if (z < 0) { set_error("columns do not zip (code " + std::to_string(z) + "; src/decode.rs:108,138)"); return NTC_ERR_IO; }
     if (rec.size() > cap) { set_error("records buffer too small"); return NTC_ERR_CAPACITY; }
     if (!rec.empty()) memcpy(records, rec.data(), rec.size() * 8);
     *n_records = rec.size();
     *consumed = pos;
     return NTC_OK;
+}
+
+int32_t ntc_block_read(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records, uint64_t* consumed) {
+    return block_read_impl(data, size, records, cap, n_records, consumed, false);
+}
+
+int32_t ntc_block_read_ex(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records, uint64_t* consumed,
+                          int32_t flags) {
+    return block_read_impl(data, size, records, cap, n_records, consumed, (flags & NTC_BLOCK_FULL_LAST_LITERAL_WORD) != 0);
 }
 
 }  // extern "C"

@@ -19,7 +19,7 @@ void minimal_binary_shape(uint64_t upper, unsigned* l, uint64_t* limit);
 bool code_column_host(const uint64_t* v, uint64_t n, int rice, std::vector<uint64_t>* words, uint64_t* param);
 bool decode_column_host(const uint64_t* words, uint64_t n_words, uint64_t n, int rice, uint64_t param, std::vector<uint64_t>* out);
 void split_records(const uint64_t* rec, uint64_t n, BlockColumns* c);
-int zip_columns(const BlockColumns& c, std::vector<uint64_t>* rec);
+int zip_columns(const BlockColumns& c, std::vector<uint64_t>* rec, bool full_last_word = false);
 void put_sub_block(const CodedColumn& col, uint64_t num_records, std::vector<uint8_t>* sink, bool* ok);
 int64_t read_sub_block(const uint8_t* data, uint64_t size, int rice, std::vector<uint64_t>* values);
 

@@ -105,33 +105,6 @@ __global__ void __launch_bounds__(256) seq_layout_kernel(const uint64_t* __restr
                       status, (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
-// ">seq.N\n" before and "\n" after every sequence (src/main.rs:204-206), one thread per sequence
-NTC_HD void fasta_header_thread(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
-                                const uint64_t* __restrict__ totals, uint64_t n_rec, const uint64_t* __restrict__ seq_endkey,
-                                uint64_t first_no, uint8_t* __restrict__ out, uint64_t cap_bytes, const uint64_t* __restrict__ counts,
-                                uint64_t j) {
-    const uint64_t n_seqs = totals[1];
-    if (j >= n_seqs || counts[1] > cap_bytes) return;
-    const uint64_t A = base_off[seq_first[j]];
-    const uint64_t B = j + 1 < n_seqs ? base_off[seq_first[j + 1]] : base_off[n_rec];
-    const uint64_t lo = seq_endkey[j] - B;
-    uint64_t no = first_no + j;
-    const uint32_t dg = dec_digits(no);
-    uint8_t* h = out + lo - (6 + dg);
-    h[0] = '>'; h[1] = 's'; h[2] = 'e'; h[3] = 'q'; h[4] = '.';
-    for (uint32_t q = 0; q < dg; q++) { h[5 + dg - 1 - q] = (uint8_t)('0' + no % 10); no /= 10; }
-    h[5 + dg] = '\n';
-    out[lo + (B - A)] = '\n';
-}
-__global__ void __launch_bounds__(256) fasta_header_kernel(const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_first,
-                                                           const uint64_t* __restrict__ totals, uint64_t n_rec,
-                                                           const uint64_t* __restrict__ seq_endkey, uint64_t first_no,
-                                                           uint8_t* __restrict__ out, uint64_t cap_bytes,
-                                                           const uint64_t* __restrict__ counts) {
-    fasta_header_thread(base_off, seq_first, totals, n_rec, seq_endkey, first_no, out, cap_bytes, counts,
-                        (uint64_t)blockIdx.x * 256 + threadIdx.x);
-}
-
 // ---- leftward write combiner ---------------------------------------------------------------
 // A record's bases come out right-to-left, 16 per jump-table load.  Bytes are merged into aligned
 // 8-byte words so the interior of a segment is written with full u64 stores; only the two edges
@@ -167,6 +140,25 @@ struct LeftWriter {
         }
         p -= 8;
     }
+    // x holds n < 8 bytes for positions [p-n, p) in its UPPER lanes (lower lanes are ignored); more may follow
+    NTC_HD void push_n(uint64_t x, uint32_t n) {
+        if (n == 0) return;
+        x &= ~0ull << (8 * (8 - n));
+        const uint32_t q = (uint32_t)(p & 7);
+        if (q == 0) { acc = x; top = 8; p -= n; return; }             // opens a new word: lanes [8-n, 8) pending
+        const uint32_t sh = 8 * q;
+        const uint64_t w = acc | (x >> (64 - sh));
+        if (n < q) { acc = w; p -= n; return; }                        // lanes [q-n, top) pending
+        store_lanes(out + (p & ~7ull), w, 0, top);                     // the word holding p is complete
+        acc = x << sh;                                                 // the other n-q bytes open the next word
+        top = 8;
+        p -= n;
+    }
+    // writes what is pending; the writer's bytes end at p
+    NTC_HD void finish() {
+        const uint32_t q = (uint32_t)(p & 7);
+        if (q) store_lanes(out + (p & ~7ull), acc, q, top);
+    }
     // x holds n < 8 bytes for positions [p-n, p) in its UPPER lanes; ends the segment
     NTC_HD void push_last(uint64_t x, uint32_t n) {
         uint32_t q = (uint32_t)(p & 7);
@@ -196,64 +188,93 @@ NTC_HD uint64_t ascii8(uint32_t codes16) {  // eight 2-bit codes in the low 16 b
     return (uint64_t)ascii4(codes16 & 0xFFu) | ((uint64_t)ascii4((codes16 >> 8) & 0xFFu) << 32);
 }
 
-// emits the last `t` (<= 16) bases of `codes` (base i of the 16-base window at bits 2i..2i+1)
-NTC_HD void emit_codes(LeftWriter& w, uint32_t codes, uint32_t t, bool last) {
+// emits the last `t` (<= 16) bases of `codes` (base i of the 16-base window at bits 2i..2i+1); the caller
+// ends the segment with finish()
+NTC_HD void emit_codes(LeftWriter& w, uint32_t codes, uint32_t t) {
     uint64_t hi = ascii8(codes >> 16), lo = ascii8(codes & 0xFFFFu);
-    if (t == 16) { w.push8(hi); w.push8(lo); if (last) w.push_last(0, 0); return; }
-    if (t >= 8) { w.push8(hi); w.push_last(lo, t - 8); }
-    else w.push_last(hi, t);
+    if (t == 16) { w.push8(hi); w.push8(lo); return; }
+    if (t >= 8) { w.push8(hi); w.push_n(lo, t - 8); }
+    else w.push_n(hi, t);
 }
 
-// one thread per record: walk / unpack and store ASCII bases
+// FASTA framing (src/main.rs:204-206): the text between the bases of sequence j-1 and those of sequence j,
+// "\n>seq.N\n" (no leading newline for j = 0), lies immediately left of sequence j's START segment, so the
+// thread of that segment -- the last record of the sequence -- keeps writing leftwards: digits come out least
+// significant first, and the bytes merge into the same aligned word stores as the bases.
+// (Earlier versions: byte stores from the END segment's thread, then a kernel of its own with one thread per
+// sequence -- 0.76 ms per 10 M sequences, most of it partial-sector writes.)
+NTC_HD void emit_header(LeftWriter& lw, uint64_t no, bool leading_newline) {
+    uint64_t acc = 0;
+    uint32_t n = 0;
+    auto put = [&](uint32_t b) {
+        acc |= (uint64_t)b << (8 * (7 - n));
+        if (++n == 8) { lw.push8(acc); acc = 0; n = 0; }
+    };
+    put('\n');
+    if (no <= 0xFFFFFFFFull) { uint32_t x = (uint32_t)no; do { put('0' + x % 10u); x /= 10u; } while (x); }
+    else do { put('0' + (uint32_t)(no % 10)); no /= 10; } while (no);
+    put('.'); put('q'); put('e'); put('s'); put('>');
+    if (leading_newline) put('\n');
+    lw.push_n(acc, n);
+}
+
+// one thread per record: walk / unpack and store ASCII bases (+ the FASTA framing left of a START segment)
 NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, uint64_t n_rec, const uint64_t* __restrict__ base_off,
-                        const uint64_t* __restrict__ seq_idx, const uint64_t* __restrict__ seq_endkey, uint8_t* __restrict__ out,
-                        uint64_t cap_bytes, const uint64_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t i) {
+                        const uint64_t* __restrict__ seq_idx, const uint64_t* __restrict__ seq_endkey, const uint64_t* __restrict__ totals,
+                        uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes, const uint64_t* __restrict__ counts,
+                        uint32_t* __restrict__ status, uint64_t i) {
     if (i >= n_rec) return;
     if (counts[1] > cap_bytes) return;  // capacity error already flagged
     const uint64_t w = NTC_LDG(rec + i);
     const uint32_t flag = (uint32_t)(w >> 56);
     const uint64_t incl = seq_idx[i] + (flag & 1u);  // sequences opened up to and including this record
     if (incl == 0) return;                            // records before the first `first` flag are dropped (src/lib.rs:308-317)
+    const uint64_t sid = incl - 1;
     const uint64_t bo = base_off[i];
     const uint32_t L = (uint32_t)(base_off[i + 1] - bo);
     // records of a sequence run from its END to its START: this one ends at (sequence end) - (bases before it)
-    const uint64_t seg_end = seq_endkey[incl - 1] - bo;
-    if (L == 0) return;
+    const uint64_t seg_end = seq_endkey[sid] - bo;
+    // START segment of its sequence = last record before the next `first` flag
+    const bool closes = fasta && (i + 1 == n_rec || record_first(NTC_LDG(rec + i + 1)));
+    if (fasta && (flag & 1u) && sid + 1 == totals[1]) out[counts[1] - 1] = '\n';   // the stream's final newline
+    if (L == 0 && !closes) return;
     // the output buffer may be misaligned by the caller: fold the misalignment into the position
     const uint64_t mis = (uint64_t)((uintptr_t)out & 7u);
     LeftWriter lw;
     lw.init(out - mis, seg_end + mis);
 
     if (flag & 2u) {  // literal record (<= 32 bases), src/lib.rs:295-306
-        uint64_t bits = w & ((1ull << (2 * L)) - 1ull);  // L <= 32 here; L == 32 keeps all 56 bits + zeros
-        if (L == 32) bits = w & 0x00FFFFFFFFFFFFFFull;
+        uint64_t bits = L >= 32 ? (w & 0x00FFFFFFFFFFFFFFull) : (w & ((1ull << (2 * L)) - 1ull));   // 56 payload bits + zeros
         if (L > 16) {
-            uint32_t top_codes = (uint32_t)(bits >> (2 * (L - 16)));           // last 16 bases
-            emit_codes(lw, top_codes, 16, false);
-            uint32_t rest = L - 16;                                             // first `rest` bases, to the upper lanes of a window
-            emit_codes(lw, (uint32_t)(bits << (2 * (16 - rest))), rest, true);
-        } else {
-            emit_codes(lw, (uint32_t)(bits << (2 * (16 - L))), L, true);
+            emit_codes(lw, (uint32_t)(bits >> (2 * (L - 16))), 16);           // last 16 bases
+            uint32_t rest = L - 16;                                           // first `rest` bases, to the upper lanes of a window
+            emit_codes(lw, (uint32_t)(bits << (2 * (16 - rest))), rest);
+        } else if (L) {
+            emit_codes(lw, (uint32_t)(bits << (2 * (16 - L))), L);
         }
-        return;
+    } else {
+        uint32_t v = (uint32_t)w;
+        if (v >= ix.n) { NTC_ATOMIC_OR(status, (uint32_t)ST_BAD_RECORD); return; }
+        const uint64_t keep = make_policies().keep;   // the jump table must survive the output stream in L2
+        uint32_t remaining = L;
+        while (remaining > 0) {
+            uint64_t ent = ld8_keep(ix.jump + v, keep);
+            uint32_t t = tmin(remaining, 16u);
+            remaining -= t;
+            emit_codes(lw, (uint32_t)(ent >> 32), t);
+            v = (uint32_t)ent;
+        }
     }
-    uint32_t v = (uint32_t)w;
-    if (v >= ix.n) { NTC_ATOMIC_OR(status, (uint32_t)ST_BAD_RECORD); return; }
-    const uint64_t keep = make_policies().keep;   // the jump table must survive the output stream in L2
-    uint32_t remaining = L;
-    while (remaining > 0) {
-        uint64_t ent = ld8_keep(ix.jump + v, keep);
-        uint32_t t = tmin(remaining, 16u);
-        remaining -= t;
-        emit_codes(lw, (uint32_t)(ent >> 32), t, remaining == 0);
-        v = (uint32_t)ent;
-    }
+    if (closes) emit_header(lw, first_no + sid, sid != 0);
+    lw.finish();
 }
 __global__ void __launch_bounds__(128) walk_kernel(DevIndex ix, const uint64_t* __restrict__ rec, uint64_t n_rec,
                                                    const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_idx,
-                                                   const uint64_t* __restrict__ seq_endkey, uint8_t* __restrict__ out, uint64_t cap_bytes,
+                                                   const uint64_t* __restrict__ seq_endkey, const uint64_t* __restrict__ totals,
+                                                   uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes,
                                                    const uint64_t* __restrict__ counts, uint32_t* __restrict__ status) {
-    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_endkey, out, cap_bytes, counts, status, (uint64_t)blockIdx.x * 128 + threadIdx.x);
+    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_endkey, totals, first_no, fasta, out, cap_bytes, counts, status,
+                (uint64_t)blockIdx.x * 128 + threadIdx.x);
 }
 
 }  // namespace ntc

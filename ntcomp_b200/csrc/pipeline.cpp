@@ -390,7 +390,8 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
                 }
                 recs[j].resize(std::max<uint64_t>(cap, 1));
                 uint64_t n_rec = 0, used = 0;
-                brc[j] = ntc_block_read(raw[j].data(), raw[j].size(), recs[j].data(), recs[j].size(), &n_rec, &used);
+                brc[j] = ntc_block_read_ex(raw[j].data(), raw[j].size(), recs[j].data(), recs[j].size(), &n_rec, &used,
+                                           NTC_BLOCK_FULL_LAST_LITERAL_WORD);   // Q5: the reference panics on 1 block in 31
                 if (brc[j] != NTC_OK) bmsg[j] = ntc_last_error();
                 recs[j].resize(brc[j] == NTC_OK ? n_rec : 0);
             });

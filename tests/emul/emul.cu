@@ -119,11 +119,8 @@ uint32_t emul_decode(void* ep, const uint64_t* rec, uint64_t n_rec, uint64_t fir
     for (uint64_t j = 0; j <= n_rec; j++)
         seq_layout_thread(base_off.data(), seq_first.data(), totals, n_rec, seq_endkey.data(), seq_offsets, cap_seqs, 0, first_no, fasta, cap,
                           counts, &status, j);
-    if (fasta)
-        for (uint64_t j = 0; j < n_rec; j++)
-            fasta_header_thread(base_off.data(), seq_first.data(), totals, n_rec, seq_endkey.data(), first_no, out, cap, counts, j);
     for (uint64_t i = 0; i < n_rec; i++)
-        walk_thread(e->dix, rec, n_rec, base_off.data(), seq_idx.data(), seq_endkey.data(), out, cap, counts, &status, i);
+        walk_thread(e->dix, rec, n_rec, base_off.data(), seq_idx.data(), seq_endkey.data(), totals, first_no, fasta, out, cap, counts, &status, i);
     return status;
 }
 

@@ -88,6 +88,30 @@ def test_block_write_read_matches_oracle():
     assert rc == 7
 
 
+def test_q5_block_is_refused_like_the_reference_and_decoded_with_the_flag():
+    """literal bases a non-zero multiple of 31: the reference's zip_block_contents reads the last literal word
+    as empty and panics (src/decode.rs:114-118,138); ntc_block_read mirrors that, ntc_block_read_ex with
+    NTC_BLOCK_FULL_LAST_LITERAL_WORD returns what the encoder wrote (the file pipeline uses it)."""
+    import ntcomp_b200 as nt
+    rng = np.random.default_rng(31)
+    for n_lit_records, L in [(31, 1), (31, 2), (31, 11), (62, 3)]:
+        recs = [7 | (40 << 32) | (1 << 56)]                                            # one reference record
+        for i in range(n_lit_records):
+            bits = int(rng.integers(0, 1 << (2 * L)))
+            recs.append(bits | (((i % 2) + 2) | (L << 2)) << 56)
+        rec = np.array(recs, dtype=np.uint64)
+        rc, blob = block_write(rec, 5)
+        assert rc == 0 and blob == ob.write_block(rec, 5)
+        rc, _, _ = block_read(blob)
+        assert rc == 7
+        rec2, used = nt.block_read(blob, full_last_literal_word=True)
+        assert used == len(blob) and (rec2 == rec).all()
+    # the flag changes nothing for blocks the reference can read
+    rec = np.array([7 | (40 << 32) | (1 << 56), 0b1101 | ((0 + 2) | (2 << 2)) << 56], dtype=np.uint64)
+    rc, blob = block_write(rec, 1)
+    assert (nt.block_read(blob, True)[0] == rec).all() and (nt.block_read(blob, False)[0] == rec).all()
+
+
 def test_q4_blocks_are_refused_like_the_reference():
     rec = np.array([5 | (20 << 32) | (1 << 56), 9 | (30 << 32)], dtype=np.uint64)     # reference records only
     assert block_write(rec, 1)[0] == 10
