@@ -167,7 +167,7 @@ def run_reference(args, rank):
             "encode_mbases_s": tb / sum(r["t_enc"] for r in results) / 1e6, "decode_mbases_s": tb / sum(r["t_dec"] for r in results) / 1e6,
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def workload_config(cfg, n_gpus):
@@ -179,7 +179,26 @@ def workload_config(cfg, n_gpus):
             "l2_policy": "inputs larger than L2 (%.0f MB of reads per step per GPU)" % (cfg["n_reads"] * cfg["read_len"] / 1e6)}
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """the ONE JSON line, on the process's original stdout"""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    # libraries print to fd 1 behind Python's back (NCCL's version banner when NCCL_DEBUG is set): route fd 1 to
+    # stderr for the run and keep the original for the result line
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -204,6 +223,7 @@ def main():
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    cpus = sharding.bind_to_gpu_numa(local_rank) if world > 1 else None
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -417,10 +437,11 @@ def main():
                 "encode_ms_per_step": 1e3 * e2e_split[0] / e2e_steps, "decode_ms_per_step": 1e3 * e2e_split[1] / e2e_steps,
                 "pcie_h2d_gbs": pcie[0], "pcie_d2h_gbs": pcie[1],
                 "pcie_floor_ms_per_step": (h2d / pcie[0] + d2h / pcie[1]) / 1e6 if pcie[0] else None},
+        "host_binding": ("NUMA-local CPUs of each GPU (%d CPUs on rank 0)" % len(cpus)) if cpus else "none",
         "gpu_launches": gpu_launches, "roofline": roofline, "cpu_baseline": cpu, "setup_s": t_setup,
         "index_bytes": ctx.index_bytes(),
     }
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 

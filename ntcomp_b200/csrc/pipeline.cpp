@@ -11,6 +11,7 @@
 #include <zlib.h>
 
 #include <algorithm>
+#include <chrono>
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
@@ -75,6 +76,8 @@ private:
     size_t depth_;
     bool done_ = false, closed_ = false;
 };
+
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 // runs fn(i) for i in [0, n) on up to n_threads threads
 void parallel_for(uint64_t n, int n_threads, const std::function<void(uint64_t)>& fn) {
@@ -245,11 +248,16 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
     const uint64_t kBatchBlocks = batch_blocks();
     Channel<ReadBatch> parsed(2);
     Channel<BytesBatch> coded(2);
+    double t_stage[4] = {0, 0, 0, 0};                                  // busy seconds: parse, GPU, block container, write
     // stage 1: parse
     std::thread t_read([&] {
         bool eof = false;
+        size_t reserve_bases = 0;
         while (!eof) {
+            const double t0 = now_s();
             ReadBatch b;
+            b.bases.reserve(reserve_bases);
+            b.offsets.reserve(kBatchBlocks * kBlockReads + 1);
             b.offsets.push_back(0);
             while (b.offsets.size() - 1 < kBatchBlocks * kBlockReads && b.bases.size() < kBatchBases) {
                 int r = reader->next(&b.bases);
@@ -265,6 +273,8 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
                 if (r < 0) { b.err = 1; eof = true; break; }
                 b.offsets.push_back(b.bases.size());
             }
+            reserve_bases = b.bases.size() + b.bases.size() / 16;
+            t_stage[0] += now_s() - t0;
             if (b.offsets.size() > 1 || b.err) { if (!parsed.push(std::move(b))) return; }
         }
         parsed.finish();
@@ -276,52 +286,74 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
         BytesBatch bb;
         while (coded.pop(&bb)) {
             if (bb.rc != NTC_OK) { w_rc = bb.rc; w_msg = bb.msg; coded.close(); return; }
+            const double t0 = now_s();
             for (auto& p : bb.parts) {
                 if (!sink.write(p.data(), p.size())) { w_rc = NTC_ERR_IO; w_msg = "write failed"; coded.close(); return; }
                 st[3] += p.size();
             }
+            t_stage[3] += now_s() - t0;
         }
     });
-    // stage 2 (this thread): GPU encode, then the block container on the pool
+    // stage 3: the block container per 65,536-read block on the pool (its own thread, so the GPU works on the
+    // next batch meanwhile)
+    struct RecordBatch { std::vector<uint64_t> records, rec_off; uint64_t n_reads = 0; };
+    Channel<RecordBatch> encoded(2);
+    std::thread t_code([&] {
+        RecordBatch rb;
+        while (encoded.pop(&rb)) {
+            const uint64_t n = rb.n_reads, n_blocks = (n + kBlockReads - 1) / kBlockReads;
+            BytesBatch out;
+            out.parts.resize(n_blocks);
+            std::vector<int32_t> brc(n_blocks, NTC_OK);
+            const double t0 = now_s();
+            parallel_for(n_blocks, n_threads, [&](uint64_t j) {
+                const uint64_t lo = j * kBlockReads, hi = std::min(n, lo + kBlockReads);
+                const uint64_t r0 = rb.rec_off[lo], r1 = rb.rec_off[hi];
+                std::vector<uint8_t>& buf = out.parts[j];
+                buf.resize(ntc_block_bound(r1 - r0));
+                uint64_t nb = 0;
+                // src/main.rs:170,176: num_records = the block size argument (65,536, or the tail count)
+                brc[j] = ntc_block_write(rb.records.data() + r0, r1 - r0, hi - lo, buf.data(), buf.size(), &nb);
+                buf.resize(brc[j] == NTC_OK ? nb : 0);
+            });
+            t_stage[2] += now_s() - t0;
+            for (uint64_t j = 0; j < n_blocks; j++) {
+                if (brc[j] == NTC_OK) st[4]++;
+                else if (brc[j] == NTC_ERR_EMPTY_COLUMN) st[5]++;       // dropped, as the reference does (Q4)
+                else { out.rc = brc[j]; out.msg = "block container failed"; }
+            }
+            if (!coded.push(std::move(out))) { encoded.close(); return; }
+        }
+        coded.finish();
+    });
+    // stage 2 (this thread): the hot path on the GPU
     int32_t rc = NTC_OK;
     std::string msg;
-    std::vector<uint64_t> records, rec_off;
     ReadBatch b;
     while (parsed.pop(&b)) {
         if (b.err) { rc = NTC_ERR_IO; msg = "malformed fastX record near read " + std::to_string(st[0] + b.offsets.size()); break; }
         const uint64_t n = b.offsets.size() - 1;
-        records.resize(std::max<uint64_t>(b.bases.size(), 1));
-        rec_off.resize(n + 1);
+        RecordBatch rb;
+        rb.n_reads = n;
+        rb.records.resize(std::max<uint64_t>(b.bases.size(), 1));
+        rb.rec_off.resize(n + 1);
         uint64_t n_rec = 0;
-        rc = ntc_encode_batch(ctx, b.bases.data(), b.offsets.data(), n, records.data(), records.size(), &n_rec, rec_off.data());
+        const double t0 = now_s();
+        rc = ntc_encode_batch(ctx, b.bases.data(), b.offsets.data(), n, rb.records.data(), rb.records.size(), &n_rec, rb.rec_off.data());
+        t_stage[1] += now_s() - t0;
         if (rc != NTC_OK) { msg = ntc_last_error(); break; }
         st[0] += n; st[1] += b.bases.size(); st[2] += n_rec;
-        const uint64_t n_blocks = (n + kBlockReads - 1) / kBlockReads;
-        BytesBatch out;
-        out.parts.resize(n_blocks);
-        std::vector<int32_t> brc(n_blocks, NTC_OK);
-        parallel_for(n_blocks, n_threads, [&](uint64_t j) {
-            const uint64_t lo = j * kBlockReads, hi = std::min(n, lo + kBlockReads);
-            const uint64_t r0 = rec_off[lo], r1 = rec_off[hi];
-            std::vector<uint8_t>& buf = out.parts[j];
-            buf.resize(ntc_block_bound(r1 - r0));
-            uint64_t nb = 0;
-            // src/main.rs:170,176: num_records = the block size argument (65,536, or the tail count)
-            brc[j] = ntc_block_write(records.data() + r0, r1 - r0, hi - lo, buf.data(), buf.size(), &nb);
-            buf.resize(brc[j] == NTC_OK ? nb : 0);
-        });
-        for (uint64_t j = 0; j < n_blocks; j++) {
-            if (brc[j] == NTC_OK) st[4]++;
-            else if (brc[j] == NTC_ERR_EMPTY_COLUMN) st[5]++;           // dropped, as the reference does (Q4)
-            else { out.rc = brc[j]; out.msg = "block container failed"; }
-        }
-        if (!coded.push(std::move(out))) break;
+        if (!encoded.push(std::move(rb))) break;
     }
     parsed.close();
-    coded.finish();
+    encoded.finish();
     t_read.join();
+    t_code.join();
     t_write.join();
     sink.close();
+    if (getenv("NTC_TRACE"))
+        fprintf(stderr, "[ntc trace] encode_file busy seconds: parse %.3f, gpu %.3f, block container %.3f, write %.3f\n", t_stage[0], t_stage[1],
+                t_stage[2], t_stage[3]);
     if (stats) memcpy(stats, st, sizeof(st));
     if (rc != NTC_OK) { set_error(msg); return rc; }
     if (w_rc != NTC_OK) { set_error(w_msg); return w_rc; }

@@ -30,3 +30,26 @@ def concat_in_rank_order(parts):
     import numpy as np
     parts = [p for p in parts if len(p)]
     return np.concatenate(parts) if parts else np.zeros(0, dtype=np.uint64)
+
+
+def bind_to_gpu_numa(device):
+    """Pin this process to the CPUs closest to `device` (NVML's ideal CPU affinity) before it allocates pinned
+    host buffers, so that every rank's staging memory and copy-issuing thread sit on the NUMA node its GPU hangs
+    off.  With 8 ranks on one box this is what keeps the host-buffer (end-to-end) path off the inter-socket
+    link.  Returns the CPU list it bound to, or None when NVML / sched_setaffinity is unavailable."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cpus = [64 * w + b for w, mask in enumerate(words) for b in range(64) if (mask >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
