@@ -139,6 +139,12 @@ int32_t ntc_block_read_ex(const uint8_t* data, uint64_t size, uint64_t* records,
  * of code lengths + atomic OR into the MSB-first stream); gzip on the host.  Same bytes as ntc_block_write. */
 int32_t ntc_block_write_gpu(ntc_ctx* ctx, const uint64_t* records, uint64_t n_records, uint64_t num_reads, uint8_t* out,
                             uint64_t cap, uint64_t* n_bytes);
+/* decode_block up to decode_sequence (src/lib.rs:320-363) with the Rice / minimal-binary decoders (src/decode.rs:51-77)
+ * and zip_block_contents (src/decode.rs:102-149) on the GPU: chunked speculative decoding of the code streams
+ * (entry-state tables per chunk, composed by one warp per stream); gunzip on the host.  Same records, same
+ * errors as ntc_block_read_ex. */
+int32_t ntc_block_read_gpu(ntc_ctx* ctx, const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap,
+                           uint64_t* n_records, uint64_t* consumed, int32_t flags);
 /* one column through rice_encode / minimal_binary_encode (src/encode.rs:59-94): rice != 0 selects Rice */
 int32_t ntc_column_code(const uint64_t* values, uint64_t n, int32_t rice, uint64_t* words, uint64_t cap, uint64_t* n_words,
                         uint64_t* param);

@@ -46,6 +46,7 @@ SIGNATURES = {
     "ntc_block_write": (_i32, [_vp, _u64, _u64, _vp, _u64, _vp]),
     "ntc_block_read": (_i32, [_vp, _u64, _vp, _u64, _vp, _vp]),
     "ntc_block_read_ex": (_i32, [_vp, _u64, _vp, _u64, _vp, _vp, _i32]),
+    "ntc_block_read_gpu": (_i32, [_vp, _vp, _u64, _vp, _u64, _vp, _vp, _i32]),
     "ntc_block_write_gpu": (_i32, [_vp, _vp, _u64, _u64, _vp, _u64, _vp]),
     "ntc_column_code": (_i32, [_vp, _u64, _i32, _vp, _u64, _vp, _vp]),
     "ntc_encode_device": (_i32, [_vp, _vp, _vp, _u64, _u64, _vp, _u64, _vp, _vp, _vp]),

@@ -270,6 +270,24 @@ void put_sub_block(const CodedColumn& col, uint64_t num_records, std::vector<uin
     sink->insert(sink->end(), gz.begin(), gz.end());
 }
 
+// header fields + gunzip of one sub-block, without decoding the integer codes (the GPU column decoder's input)
+int64_t inflate_sub_block(const uint8_t* data, uint64_t size, std::vector<uint64_t>* words, uint64_t* n_values, uint64_t* param) {
+    if (size < 32) return -1;
+    uint32_t block_size, num_u64, encoded_size;
+    memcpy(&block_size, data, 4);
+    memcpy(&num_u64, data + 8, 4);
+    memcpy(&encoded_size, data + 12, 4);
+    memcpy(param, data + 16, 8);
+    if (32ull + block_size > size) return -2;
+    std::vector<uint8_t> raw;
+    if (!gunzip_member(data + 32, block_size, &raw)) return -3;
+    if (raw.size() % 8 || raw.size() / 8 != encoded_size) return -5;              // src/decode.rs:90
+    words->resize(raw.size() / 8);
+    if (!raw.empty()) memcpy(words->data(), raw.data(), raw.size());
+    *n_values = num_u64;
+    return 32 + (int64_t)block_size;
+}
+
 int64_t read_sub_block(const uint8_t* data, uint64_t size, int rice, std::vector<uint64_t>* values) {
     if (size < 32) return -1;
     uint32_t block_size, num_u64, encoded_size;

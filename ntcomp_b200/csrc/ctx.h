@@ -55,6 +55,7 @@ struct ntc_ctx {
     uint64_t max_chunk_records = 4ull << 20;  // host-buffer decode: records per chunk (NTC_MAX_CHUNK_RECORDS overrides)
     cudaStream_t stream = nullptr;  // == lanes[0].stream
     void* colwork = nullptr;        // workspaces of the GPU column codec (api_columns.inc)
+    void* coldecwork = nullptr;     // ... and of its inverse
 
     // optional per-kernel-class timing with CUDA events on the launching stream (bench.py roofline)
     bool profiling = false;

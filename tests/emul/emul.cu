@@ -5,6 +5,7 @@
 #include <cstring>
 #include <vector>
 
+#include "../../ntcomp_b200/csrc/column_decode_kernels.cuh"
 #include "../../ntcomp_b200/csrc/column_kernels.cuh"
 #include "../../ntcomp_b200/csrc/container.h"
 #include "../../ntcomp_b200/csrc/decode_kernels.cuh"
@@ -158,6 +159,41 @@ int emul_block_columns(const uint64_t* rec, uint64_t n, uint64_t* words, uint64_
         pos += n_words[q];
     }
     return 0;
+}
+
+
+// GPU column decoder bodies (column_decode_kernels.cuh) on the CPU: words as stored (big-endian u64), n values
+// expected; returns the number of codes found (values beyond n are not stored).  -1: bad parameter.
+int64_t emul_column_decode(const uint64_t* words_be, uint64_t n_words, uint64_t n, int rice, uint64_t param, uint64_t* out) {
+    CodeParams p;
+    if (rice) { if (param > 63) return -1; p = CodeParams{1, (uint32_t)param, 0, 0}; }
+    else { if (param < 2) return -1; unsigned l; uint64_t limit; minimal_binary_shape(param, &l, &limit); p = CodeParams{0, 0, l, limit}; }
+    if (n_words == 0) return 0;
+    std::vector<uint64_t> w(n_words);
+    for (uint64_t i = 0; i < n_words; i++) w[i] = __builtin_bswap64(words_be[i]);      // bswap_kernel
+    const uint64_t n_chunks = (n_words * 64 + kCwChunkBits - 1) / kCwChunkBits;
+    const uint32_t ns = cw_num_states(p);
+    std::vector<uint32_t> table(n_chunks * ns), entry(n_chunks);
+    std::vector<uint64_t> first(n_chunks);
+    for (uint64_t i = n_chunks * ns; i-- > 0;) cw_table_thread(p, w.data(), n_words, n_chunks, table.data(), i);
+    uint64_t total = 0;
+    cw_resolve_serial(table.data(), ns, n_chunks, entry.data(), first.data(), &total);
+    for (uint64_t c = n_chunks; c-- > 0;) cw_extract_thread(p, w.data(), n_words, n_chunks, entry.data(), first.data(), out, n, c);
+    return (int64_t)total;
+}
+
+// zip_thread over a block's four columns; returns the error bits (0 = ok)
+uint32_t emul_zip(const uint64_t* colex, const uint64_t* len, uint64_t n_ref, const uint64_t* flags, uint64_t n, const uint64_t* lits,
+                  uint64_t n_lit_words, int full_last_word, uint64_t* rec) {
+    std::vector<uint64_t> ref_idx(n + 1), lit_off(n + 1);
+    FlagLoad load{flags};
+    uint64_t a = 0, b = 0;
+    for (uint64_t i = 0; i < n; i++) { ref_idx[i] = a; lit_off[i] = b; Pair64 pr = load(i); a += pr.a; b += pr.b; }
+    uint64_t totals[2] = {a, b};
+    uint32_t err = 0;
+    for (uint64_t i = 0; i < n; i++)
+        zip_thread(colex, len, n_ref, flags, n, lits, n_lit_words, ref_idx.data(), lit_off.data(), totals, full_last_word, rec, &err, i);
+    return err;
 }
 
 }  // extern "C"

@@ -132,6 +132,14 @@ def test_cli_round_trip_and_block_parity(tmp_path, genome_and_reads, monkeypatch
     ctx.decode_file(tmp_path / "e3.dat", tmp_path / "d3.fa", n_threads=2)
     assert (tmp_path / "d3.fa").read_bytes() == dec.read_bytes()
     monkeypatch.delenv("NTC_PIPELINE_BATCH_BLOCKS")
+    # one record per base (reads of 1-3 bases): the pipeline's first record buffer is too small and it retries with the bound
+    tiny = [helpers.random_seq(np.random.default_rng(5), n) for n in ([1, 2, 3, 1] * 700)]
+    _write_fasta(tmp_path / "tiny.fa", tiny)
+    st = ctx.encode_file(tmp_path / "tiny.fa", tmp_path / "tiny.dat")
+    assert st["reads"] == len(tiny) and st["records"] >= len(tiny)
+    if st["dropped_blocks"] == 0:
+        ctx.decode_file(tmp_path / "tiny.dat", tmp_path / "tiny.out")
+        assert (tmp_path / "tiny.out").read_bytes() == helpers.fasta_text(tiny, 1)
     # a read with an N makes encode fail with NTC_ERR_BAD_BASE instead of the reference's underflow (Q3)
     bad = tmp_path / "bad.fa"
     bad.write_bytes(b">x\nACGTNACGT\n")

@@ -53,12 +53,14 @@ def main():
         r = subprocess.run([CLI, "encode", "-i", prefix, os.path.join(tmp, "reads.fa")] + thr, stdout=f, stderr=subprocess.PIPE)
     if r.returncode:
         raise SystemExit("encode failed: " + r.stderr.decode())
+    sys.stderr.write(r.stderr.decode())
     enc_log = r.stderr.decode().strip().splitlines()[-1]
     t2 = time.time()
     with open(os.path.join(tmp, "decoded.fa"), "wb") as f:
         r = subprocess.run([CLI, "decode", "-i", prefix, os.path.join(tmp, "encoded.dat")] + thr, stdout=f, stderr=subprocess.PIPE)
     if r.returncode:
         raise SystemExit("decode failed: " + r.stderr.decode())
+    sys.stderr.write(r.stderr.decode())
     dec_log = r.stderr.decode().strip().splitlines()[-1]
     t3 = time.time()
     want = b"".join(b">seq.%d\n%s\n" % (i + 1, bytes(bases[i * L:(i + 1) * L])) for i in range(min(cfg["n_reads"], 1000)))
