@@ -33,6 +33,20 @@ NTC_HD uint32_t ascii_code(uint32_t b, uint32_t* bad) {
     return code;
 }
 
+// four ASCII bases in one 32-bit word -> four 2-bit codes in the low byte; *bad |= any byte that is not A, C, G or T
+// (first version: byte by byte, ~8 instructions per base -- pack2bit_kernel was instruction bound at 36% of HBM)
+NTC_HD uint32_t ascii4_codes(uint32_t w, uint32_t* bad) {
+    const uint32_t x = (w >> 1) & 0x03030303u;                       // A->0 C->1 G->3 T->2 in every byte
+    const uint32_t c = x ^ ((x >> 1) & 0x01010101u);                 // A0 C1 G2 T3
+#if defined(__CUDA_ARCH__)
+    const uint32_t sel = (c & 0x3u) | ((c >> 4) & 0x30u) | ((c >> 8) & 0x300u) | ((c >> 12) & 0x3000u);
+    *bad |= (__byte_perm(0x54474341u, 0u, sel) != w);                // the letters these codes stand for
+#else
+    for (int j = 0; j < 4; j++) *bad |= (((0x54474341u >> (8 * ((c >> (8 * j)) & 3u))) & 0xFFu) != ((w >> (8 * j)) & 0xFFu));
+#endif
+    return (c | (c >> 6) | (c >> 12) | (c >> 18)) & 0xFFu;
+}
+
 NTC_HD void pack2bit_thread(const uint8_t* __restrict__ bases, const uint64_t* __restrict__ offsets, uint64_t n_bases,
                             uint64_t* __restrict__ packed, uint32_t* __restrict__ status, uint64_t w) {
     const uint8_t* __restrict__ src = bases + NTC_LDG(offsets);
@@ -45,13 +59,7 @@ NTC_HD void pack2bit_thread(const uint8_t* __restrict__ bases, const uint64_t* _
         uint4 v0 = NTC_LDG((const uint4*)s), v1 = NTC_LDG((const uint4*)s + 1);
         uint32_t q[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                uint32_t code = ascii_code((q[i] >> (8 * j)) & 0xFFu, &bad);
-                out |= (uint64_t)code << (2 * (4 * i + j));
-            }
-        }
+        for (int i = 0; i < 8; i++) out |= (uint64_t)ascii4_codes(q[i], &bad) << (8 * i);
     } else {
         uint32_t m = (uint32_t)tmin<uint64_t>(32, n_bases - p0);
         for (uint32_t j = 0; j < m; j++) out |= (uint64_t)ascii_code(s[j], &bad) << (2 * j);

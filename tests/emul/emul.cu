@@ -2,6 +2,7 @@
 // (ntcomp_b200/csrc/*_kernels.cuh, NTC_HD functions) on the CPU, one loop iteration per CUDA thread,
 // so kernel LOGIC is checked against the oracle in the "not gpu" suite before GPU time is spent.
 // Not part of the product: libntcomp_b200.so never links or calls this file.
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
