@@ -363,7 +363,12 @@ def main():
     t_e2e = float("nan")
     pcie = [None, None]
     if not args.no_e2e:
+        barrier()                                   # all ranks copy at the same time: the host side is shared
         pcie = pcie_peak()
+        if world > 1:
+            tp = torch.tensor(pcie, dtype=torch.float64, device=dev)
+            dist.all_reduce(tp, op=dist.ReduceOp.MIN)
+            pcie = [float(x) for x in tp.tolist()]
         e2e_step()
         first = (b">seq.%d\n" % (lo + 1)) + bytes(h_bases[:read_len].numpy()) + b"\n"
         if n_seqs_c.value != n_reads or bytes(h_text[: len(first)].numpy()) != first:
@@ -435,7 +440,7 @@ def main():
         "e2e": {"value": total_bases * e2e_steps / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e2e_steps, "api": "ntc_encode_batch + ntc_decode_fasta, pinned host buffers",
                 "encode_ms_per_step": 1e3 * e2e_split[0] / e2e_steps, "decode_ms_per_step": 1e3 * e2e_split[1] / e2e_steps,
-                "pcie_h2d_gbs": pcie[0], "pcie_d2h_gbs": pcie[1],
+                "pcie_h2d_gbs": pcie[0], "pcie_d2h_gbs": pcie[1],   # per GPU, all ranks copying at once (min over ranks)
                 "pcie_floor_ms_per_step": (h2d / pcie[0] + d2h / pcie[1]) / 1e6 if pcie[0] else None},
         "host_binding": ("NUMA-local CPUs of each GPU (%d CPUs on rank 0)" % len(cpus)) if cpus else "none",
         "gpu_launches": gpu_launches, "roofline": roofline, "cpu_baseline": cpu, "setup_s": t_setup,
