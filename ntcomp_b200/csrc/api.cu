@@ -2,6 +2,7 @@
 // device pipelines, and the host-buffer entry points a Rust/cgo/ctypes caller binds.
 // There is no CPU fallback here: without a GPU every compute entry point returns NTC_ERR_CUDA.
 #include <algorithm>
+#include <cstdio>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -56,6 +57,11 @@ __global__ void publish_kernel(const uint64_t* __restrict__ pair, const uint32_t
     __threadfence_system();
 }
 
+__global__ void policy_kernel(uint64_t* out) {
+    const CachePolicy p = make_policies();
+    out[0] = p.keep;
+    out[1] = p.stream;
+}
 __global__ void copy_totals_kernel(const uint64_t* totals, uint64_t* counts) {
     counts[0] = totals[0];
     counts[1] = totals[0] * 8;
@@ -315,9 +321,29 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     ctx->dix.n = (uint32_t)idx->n;
     ctx->dix.k = idx->k;
     spec_window(idx->n, &ctx->dix.spec_lo, &ctx->dix.spec_span);
-    if (const char* env = getenv("NTC_TILE_LEN")) ntc_ctx_set_tile_len(ctx, (uint32_t)strtoul(env, nullptr, 10));
-    if (const char* env = getenv("NTC_SPEC_LO")) ctx->dix.spec_lo = (uint32_t)strtoul(env, nullptr, 10);      // tuning knobs
-    if (const char* env = getenv("NTC_SPEC_SPAN")) ctx->dix.spec_span = (uint32_t)strtoul(env, nullptr, 10);
+    {
+        // L2 cache-hint descriptors, made once on the device and handed to every kernel as (uniform) parameters
+        policy_kernel<<<1, 1>>>((uint64_t*)ctx->d_totals);
+        uint64_t pol[2] = {0, 0};
+        if ((e = cudaMemcpy(pol, ctx->d_totals, 16, cudaMemcpyDeviceToHost)) != cudaSuccess) return fail("policy_kernel", e);
+        cudaMemset(ctx->d_totals, 0, 64);
+        ctx->dix.pol_keep = pol[0];
+        ctx->dix.pol_stream = pol[1];
+        // A persisting carve-out (cudaLimitPersistingL2CacheSize) is NOT set by default: measured on B200 (C3,
+        // profiles/r1/ab_l2_persist.txt) a 64 / 79 MB set-aside slows ms_kernel from 15.3 to 20.1 / 26.4 ms, 32 MB changes
+        // nothing -- the carve-out shrinks the L2 left for everything else, while the evict_last / evict_first hints
+        // alone already keep the index resident (without them: see profiles).  NTC_L2_PERSIST_MB sets one for experiments.
+        if (const char* env = getenv("NTC_L2_PERSIST_MB")) {
+            cudaDeviceProp prop;
+            if (cudaGetDeviceProperties(&prop, device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
+                size_t want = std::min<size_t>((size_t)strtoull(env, nullptr, 10) << 20, (size_t)prop.persistingL2CacheMaxSize);
+                cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+                if (getenv("NTC_VERBOSE"))
+                    fprintf(stderr, "ntcomp_b200: L2 %d MB, persisting max %d MB, set-aside %zu MB\n", prop.l2CacheSize >> 20,
+                            prop.persistingL2CacheMaxSize >> 20, want >> 20);
+            }
+        }
+    }
     *out = ctx;
     return NTC_OK;
 }

@@ -191,45 +191,51 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
     const bool multi = len > T;                                       // counted by count_kernel once every tile is done
     const uint32_t p0 = tile * T;                                     // first stored position
     const uint32_t p1 = multi ? tmin(len, p0 + T) : len;              // end of the tile
-    const CachePolicy pol = make_policies();
+    const uint64_t keep = ix.pol_keep;
     uint64_t* __restrict__ sc = scratch + scratch_base(a, r);
-    uint32_t s = 0, e = n, d = 0, urun = 0, prev_s = 0, prev_d = 0;
+    uint32_t s = 0, e = n, d = 0, urun = 0;
     uint32_t j = tile ? p0 - (k - 1u) : 0u;                           // warm-up start
-    bool fresh = true, absent = false, force = false;
-    // the read's bases leave `word` two bits at a time; `left` bases remain in it (no 64-bit position arithmetic or
-    // variable shift per base: ncu r1 v10 had 10% of the loop's instructions in the base fetch)
-    const uint64_t* __restrict__ wp = packed + ((a + j) >> 5);
-    uint32_t left = 32u - (uint32_t)((a + j) & 31);
-    uint64_t word = *wp >> (((a + j) & 31) * 2);
-    uint32_t c = (uint32_t)word & 3u;
+    bool fresh = true, force = false;
+    uint32_t dmin = 1;                                                // 0 once a base was absent from the index
+    // the read's bases leave `word` two bits at a time, 16 per 32-bit word (ncu r1 v10: 10% of the loop's instructions
+    // were 64-bit position arithmetic and variable shifts in the base fetch; v11 used a 64-bit shift register)
+    const uint32_t* __restrict__ wp = (const uint32_t*)packed + ((a + j) >> 4);
+    uint32_t left = 16u - (uint32_t)((a + j) & 15);
+    uint32_t word = *wp >> (((uint32_t)(a + j) & 15u) * 2u);
+    uint32_t c = word & 3u;
     while (j < p1) {
         // a singleton interval [s, s+1) -- the common case once the match is longer than ~log4(n) -- needs one
         // entry only, also when s is the last node of its block: rank(s+1) = rank(s) + row bit of s
         const bool single = e == s + 1u;
-        const uint32_t bs = s / 48u, be = single ? bs : e / 48u;
-        const uint32_t os = s - bs * 48u, oe = e - be * 48u;
-        const uint4 va = ld16_keep(ix.rank + (size_t)bs * 4 + c, pol.keep);
+        const uint32_t bs = rank_block(s), os = rank_offset(s, bs);
+        const uint32_t be = rank_block(e), oe = rank_offset(e, be);
+        const bool other = !single && be != bs;                       // the interval end lies in another block
         // LCS words of the interval ends: loaded speculatively only while d is in the window where
         // extensions of chance matches fail (around log4(n_sets), set by the host), on demand otherwise
         // (ncu r1 v3: unconditional speculation doubled the sector traffic; v5: d < 20 still spent 39% of
         // all load sectors on it)
         const bool spec = force || (d - ix.spec_lo < ix.spec_span);   // unsigned: spec_lo <= d < spec_lo + spec_span
-        uint32_t xs = 0, xe = 0;
-        if (spec) { xs = ld4_keep(ix.lcsx + s, pol.keep); xe = single ? xs : ld4_keep(ix.lcsx + (e - 1u), pol.keep); }
-        const uint4 vb = (be != bs) ? ld16_keep(ix.rank + (size_t)be * 4 + c, pol.keep) : va;
+        // all loads of the iteration issue back to back, before any of their results is used
+        const uint4 va = ld16_keep(ix.rank + (bs * 4u + c), keep);             // 32-bit entry index: n / 8 < 2^29
+        const RankPart vb = ld_rank_part_if(ix.rank + (be * 4u + c), keep, other);
+        const uint32_t xs = ld4_keep_if(ix.lcsx + s, keep, spec);
+        uint32_t xe = ld4_keep_if(ix.lcsx + (e - 1u), keep, spec && !single);
+        xe = single ? xs : xe;
+        const uint32_t s2 = entry_rank(va, os);
+        const uint32_t e2 = single ? s2 + entry_bit(va, os) : entry_rank_sel(va, vb, other, oe);
         if (fresh) {
-            // the block of the previous interval start also holds its Q bit: finish entry j-1
+            // the block of the interval start (unchanged since the last successful step) also holds its Q bit:
+            // finish entry j-1, whose (start, d) are still in s and d
             if (j > p0) {
-                urun = (prev_d == k && entry_qbit(va, os)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
-                uint32_t slot = (j - 1) & 3u;
-                stage[slot * stride] = make_entry(prev_s, prev_d, urun);
+                urun = (d == k && entry_qbit(va, os)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
+                const uint32_t slot = (j - 1u) & 3u;
+                stage[slot * stride] = make_entry(s, d, urun);
                 if (slot == 3u) {                                     // one full 32-byte sector
-                    st32_stream(sc + (j - 4), stage[0], stage[stride], stage[2 * stride], stage[3 * stride], pol.stream);
+                    st32_stream(sc + (j - 4u), stage[0], stage[stride], stage[2 * stride], stage[3 * stride], ix.pol_stream);
                 }
             }
             fresh = false;
         }
-        const uint32_t s2 = entry_rank(va, os), e2 = entry_rank(vb, oe);
         if (s2 >= e2 && !(s == 0 && e == n)) {
             // contract_left (sbwt LcsArray): the interval is maximal for its level d, so both boundary
             // LCS values are < d and the reference's loop -- which re-probes the same empty interval for
@@ -257,26 +263,30 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
             d = (uint32_t)t;
             continue;
         }
-        if (s2 < e2) { s = s2; e = e2; d = tmin(d + 1u, k); }         // extend_right succeeded
-        else { d = 0; absent = true; }                                // base absent from the index
-        prev_s = s; prev_d = d; fresh = true;
+        const bool ok = s2 < e2;                                      // extend_right succeeded; else the base is absent from the index
+        s = ok ? s2 : s;
+        e = ok ? e2 : e;
+        d = ok ? tmin(d + 1u, k) : 0u;
+        dmin = tmin(dmin, d);
+        fresh = true;
         j++;
         word >>= 2;
-        if (--left == 0) { word = j < p1 ? *++wp : 0; left = 32; }
-        c = (uint32_t)word & 3u;
+        if (--left == 0) { word = j < p1 ? *++wp : 0; left = 16; }
+        c = word & 3u;
     }
-    // tail: entries of the last, partial group of four + the tile's final position
+    // tail: entries of the last, partial group of four + the tile's final position (whose start and d are in s, d)
     {
         uint32_t first_unflushed = (p1 - 1) & ~3u;                     // entries [first_unflushed, p1-1) are staged (>= p0: p0 % 4 == 0)
         for (uint32_t q = first_unflushed; q + 1 < p1; q++) sc[q] = stage[(q & 3u) * stride];
         uint32_t last_run = 0;                                         // urun of a read's last position is never read (ext looks at i-2)
         if (p1 < len) {                                                // ... but the next tile's runs may continue this one
-            const uint4 vq = ld16_keep(ix.rank + (size_t)(prev_s / 48u) * 4, pol.keep);
-            last_run = (prev_d == k && entry_qbit(vq, prev_s % 48u)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
+            const uint32_t bq = rank_block(s);
+            const uint4 vq = ld16_keep(ix.rank + (size_t)bq * 4, keep);
+            last_run = (d == k && entry_qbit(vq, rank_offset(s, bq))) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
         }
-        sc[p1 - 1] = make_entry(prev_s, prev_d, last_run);
+        sc[p1 - 1] = make_entry(s, d, last_run);
     }
-    if (absent) {                                                     // lib.rs:207 would underflow (Q3)
+    if (dmin == 0) {                                                  // lib.rs:207 would underflow (Q3)
         if (counts && !multi) counts[r] = 0;
         NTC_ATOMIC_OR(status, (uint32_t)ST_BAD_BASE);
         return;

@@ -4,6 +4,7 @@
 #include <cstdint>
 #include <string>
 #include <vector>
+#include "layout.h"
 
 struct ntc_index {
     uint32_t k = 0;
@@ -18,7 +19,7 @@ namespace ntc {
 constexpr uint32_t kMinK = 12;   // len <= 11 literals index kmer[k-len..k) (src/encode.rs:152): needs k >= 11;
                                  // the decode jump table packs 16 bases, the bucketed builder uses 8
 constexpr uint32_t kMaxK = 255;  // d and LCS are stored in one byte
-constexpr uint32_t kBlockNodes = 48;  // nodes per 64-byte rank block
+constexpr uint32_t kBlockNodes = NTC_RANK_NODES;  // nodes per 64-byte rank block (layout.h)
 
 void set_error(const std::string& msg);
 
@@ -30,8 +31,8 @@ int32_t build_index(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n
 
 // ---- derived device layouts (built on the host, uploaded by ntc_ctx_create) ----
 
-// Rank blocks: 64 bytes per 48 nodes = 4 x 16-byte entries (A,C,G,T), entry =
-//   u32 ones of this row before the block | 48 row bits | 48 Q bits
+// Rank blocks: 64 bytes per kBlockNodes nodes = 4 x 16-byte entries (A,C,G,T), entry =
+//   u32 C[c] + ones of this row before the block | row bits | Q bits   (32 + 32 (+ 32 spare) or 48 + 48 bits)
 // Q[v] = node v is alone in its (k-1)-suffix group  <=>  LCS[v] < k-1 and (v+1 == n or LCS[v+1] < k-1).
 // One rank probe = one aligned 16-byte load = one 32-byte L2 sector.
 void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out /* 16 u32 per block */, int n_threads);
