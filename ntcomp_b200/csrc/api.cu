@@ -331,8 +331,9 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
         ctx->dix.pol_stream = pol[1];
         // A persisting carve-out (cudaLimitPersistingL2CacheSize) is NOT set by default: measured on B200 (C3,
         // profiles/r1/ab_l2_persist.txt) a 64 / 79 MB set-aside slows ms_kernel from 15.3 to 20.1 / 26.4 ms, 32 MB changes
-        // nothing -- the carve-out shrinks the L2 left for everything else, while the evict_last / evict_first hints
-        // alone already keep the index resident (without them: see profiles).  NTC_L2_PERSIST_MB sets one for experiments.
+        // nothing -- the carve-out shrinks the L2 left for everything else.  (The evict_last / evict_first hints by
+        // themselves measure neutral on v12: 12.01 ms without them, profiles/r1/ab_v12_variants.txt.)
+        // NTC_L2_PERSIST_MB sets a carve-out for experiments.
         if (const char* env = getenv("NTC_L2_PERSIST_MB")) {
             cudaDeviceProp prop;
             if (cudaGetDeviceProperties(&prop, device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
@@ -344,6 +345,9 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
             }
         }
     }
+    if (const char* env = getenv("NTC_TILE_LEN")) ntc_ctx_set_tile_len(ctx, (uint32_t)strtoul(env, nullptr, 10));
+    if (const char* env = getenv("NTC_SPEC_LO")) ctx->dix.spec_lo = (uint32_t)strtoul(env, nullptr, 10);      // tuning knobs
+    if (const char* env = getenv("NTC_SPEC_SPAN")) ctx->dix.spec_span = (uint32_t)strtoul(env, nullptr, 10);
     *out = ctx;
     return NTC_OK;
 }

@@ -133,9 +133,12 @@ void build_lcs_words(const ntc_index& idx, std::vector<uint32_t>* out) {
 // window of match lengths in which extensions of chance matches keep failing: around log4(n_sets)
 void spec_window(uint64_t n_sets, uint32_t* lo, uint32_t* span) {
     double l4 = std::log((double)std::max<uint64_t>(n_sets, 4)) / std::log(4.0);
-    int a = (int)std::floor(l4) - 1;   // swept on B200 (tools/sweep_spec.py, C3 shape): [10,16) best at n = 10^7
+    // swept on B200 (tools/sweep_spec.py, C3 shape, n = 10^7, log4 n = 11.6; profiles/r1/sweep_spec_v12.txt): with all
+    // loads of an iteration issued together (v12) the window hardly matters any more -- [11,14) 4.77 ms, [10,16) 4.91,
+    // no speculation at all 4.91, always 7.62 -- so it is kept narrow
+    int a = (int)std::floor(l4);
     *lo = (uint32_t)std::max(1, a);
-    *span = 6;
+    *span = 3;
 }
 
 void build_jump_table(const ntc_index& idx, std::vector<uint64_t>* out, int n_threads) {

@@ -14,7 +14,7 @@ d_rec = torch.empty(nb // 6, dtype=torch.int64, device=dev); d_roff = torch.empt
 d_cnt = torch.zeros(4, dtype=torch.int64, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 first = True
-for lo, span, od in [(10, 6, 0), (0, 0, 0), (0, 20, 0), (9, 7, 0), (10, 4, 0), (11, 5, 0), (0, 255, 0)]:
+for lo, span, od in [(10, 6, 0), (0, 0, 0), (11, 3, 0), (10, 3, 0), (11, 2, 0), (10, 4, 0), (11, 5, 0), (9, 7, 0), (12, 3, 0), (0, 255, 0)]:
     os.environ["NTC_SPEC_LO"] = str(lo); os.environ["NTC_SPEC_SPAN"] = str(span); os.environ["NTC_SPEC_ONDEMAND"] = str(od)
     ctx = nt.Context(idx, 0)
     if first:
