@@ -48,7 +48,7 @@ struct ntc_ctx {
     uint32_t* d_status = nullptr;   // [4]
     uint64_t* d_totals = nullptr;   // [8]: ring of 3 encode scan totals (Pair64 each) + decode totals at [6]
     uint64_t launches = 0;
-    uint64_t max_chunk_bases = 96ull << 20;   // host-buffer API chunk (overlap granularity); NTC_MAX_CHUNK_BASES overrides
+    uint64_t max_chunk_bases = 48ull << 20;   // host-buffer API chunk (overlap granularity; 16 M .. 192 M swept on B200, profiles/r1/sweep_chunks_v12.txt); NTC_MAX_CHUNK_BASES overrides
     uint32_t tile_len = 0;                    // matching-statistics tile length; 0 = chosen per batch (ntc_ctx_set_tile_len)
 
     ntc::Lane lanes[2];             // lanes[0] also serves the device-resident API (on the caller's stream)
