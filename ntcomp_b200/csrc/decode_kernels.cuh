@@ -255,7 +255,7 @@ NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, ui
     } else {
         uint32_t v = (uint32_t)w;
         if (v >= ix.n) { NTC_ATOMIC_OR(status, (uint32_t)ST_BAD_RECORD); return; }
-        const uint64_t keep = make_policies().keep;   // the jump table must survive the output stream in L2
+        const uint64_t keep = ix.pol_keep;            // the jump table must survive the output stream in L2
         uint32_t remaining = L;
         while (remaining > 0) {
             uint64_t ent = ld8_keep(ix.jump + v, keep);

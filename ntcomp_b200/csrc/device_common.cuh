@@ -35,9 +35,8 @@ enum : uint32_t {
 // Index as the kernels see it.  All arrays are L2-resident at the BASELINE configs
 // (5 Mbp / k=91: rank 13.4 MB, LCS 10 MB, jump 80 MB).
 struct DevIndex {
-    const uint4* rank;     // [(n/NTC_RANK_NODES+1) * 4] entries, c = entry index & 3.  32 nodes: {C[c] + ones before
-                           //   block, row bits, Q bits, 0}; 48 nodes: {count, row bits 0-31, row bits 32-47 | Q bits
-                           //   0-15 << 16, Q bits 16-47}
+    const uint4* rank;     // [(n/32+1) * 4] entries, c = entry index & 3: {C[c] + ones of row c before the block,
+                           //   row bits, Q bits, 0}
     const uint32_t* lcsx;  // [n + 1] LCS[i] | dist to previous smaller << 8 | LCS[i+1] << 16 | dist to next smaller of i+1 << 24
     const uint64_t* jump;  // [n] pred^16 | chars16 << 32
     uint32_t n;
@@ -63,7 +62,6 @@ NTC_HD uint32_t entry_urun(uint64_t e) { return (uint32_t)(e >> 40); }
 #else
 #define NTC_POPC(x) __builtin_popcount(x)
 #endif
-#if NTC_RANK_NODES == 32
 NTC_HD uint32_t rank_block(uint32_t v) { return v >> 5; }
 NTC_HD uint32_t rank_offset(uint32_t v, uint32_t) { return v & 31u; }
 NTC_HD uint32_t entry_rank(const uint4& e, uint32_t off) {            // off in [0, 32)
@@ -71,24 +69,6 @@ NTC_HD uint32_t entry_rank(const uint4& e, uint32_t off) {            // off in 
 }
 NTC_HD uint32_t entry_bit(const uint4& e, uint32_t off) { return (e.y >> off) & 1u; }
 NTC_HD uint32_t entry_qbit(const uint4& e, uint32_t off) { return (e.z >> off) & 1u; }
-#else
-NTC_HD uint32_t rank_block(uint32_t v) { return v / 48u; }
-NTC_HD uint32_t rank_offset(uint32_t v, uint32_t b) { return v - b * 48u; }
-NTC_HD uint32_t entry_rank(const uint4& e, uint32_t off) {            // off in [0, 48)
-    uint64_t bits = (uint64_t)e.y | ((uint64_t)(e.z & 0xFFFFu) << 32);
-    return e.x + (uint32_t)NTC_POPCLL(bits & ((1ull << off) - 1ull));
-}
-NTC_HD uint32_t entry_bit(const uint4& e, uint32_t off) {
-    uint64_t bits = (uint64_t)e.y | ((uint64_t)(e.z & 0xFFFFu) << 32);
-    return (uint32_t)(bits >> off) & 1u;
-}
-NTC_HD uint32_t entry_qbit(const uint4& e, uint32_t off) {
-    uint64_t q = (uint64_t)(e.z >> 16) | ((uint64_t)e.w << 16);
-    return (uint32_t)(q >> off) & 1u;
-}
-#endif
-
-NTC_HD uint4 ldg_entry(const uint4* p) { return NTC_LDG(p); }
 
 // 2-bit base at chunk-relative position p of a packed stream (32 bases per u64, LSB first)
 NTC_HD uint32_t packed_base(const uint64_t* __restrict__ packed, uint64_t p) {
@@ -107,7 +87,10 @@ NTC_HD uint64_t packed_slice(const uint64_t* __restrict__ packed, uint64_t p, ui
 // The index (rank blocks, LCS words, jump table) is re-read at random and must stay in the 126 MB L2;
 // scratch / record / FASTA streams pass through once.  ncu r1 v4 showed 14.5 GB of DRAM reads in
 // ms_kernel -- index lines evicted by the 12 GB scratch stream -- so index loads carry an evict_last
-// policy and streaming stores an evict_first one (createpolicy + .L2::cache_hint).
+// policy and streaming stores an evict_first one (createpolicy + .L2::cache_hint).  Measured again on v12 the
+// hints are neutral (12.01 vs 12.00 ms) and most of those DRAM reads turned out to be the record-count pass
+// re-reading scratch entries; a persisting-L2 carve-out on top is harmful (api.cu, ntc_ctx_create).
+// The descriptors are made once (policy_kernel) and travel as kernel parameters in DevIndex.
 struct CachePolicy {
     uint64_t keep, stream;
 };
@@ -120,10 +103,7 @@ NTC_HD CachePolicy make_policies() {
     return p;
 }
 NTC_HD uint4 ld16_keep(const uint4* ptr, uint64_t pol) {
-#if defined(__CUDA_ARCH__) && defined(NTC_NO_HINTS)
-    (void)pol;
-    return __ldg(ptr);
-#elif defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__)
     uint4 v;
     asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr), "l"(pol));
     return v;
@@ -133,10 +113,7 @@ NTC_HD uint4 ld16_keep(const uint4* ptr, uint64_t pol) {
 #endif
 }
 NTC_HD uint32_t ld4_keep(const uint32_t* ptr, uint64_t pol) {
-#if defined(__CUDA_ARCH__) && defined(NTC_NO_HINTS)
-    (void)pol;
-    return __ldg(ptr);
-#elif defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__)
     uint32_t v;
     asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(ptr), "l"(pol));
     return v;
@@ -174,37 +151,14 @@ NTC_HD uint2 ld8x2_keep_if(const uint4* ptr, uint64_t pol, bool on) {   // first
     return on ? uint2{ptr->x, ptr->y} : uint2{0u, 0u};
 #endif
 }
-NTC_HD uint4 ld16_keep_if(const uint4* ptr, uint64_t pol, bool on) {
-#if defined(__CUDA_ARCH__)
-    uint4 v;
-    asm volatile(
-        "{\n .reg .pred p;\n setp.ne.u32 p, %6, 0;\n mov.u32 %0, 0;\n mov.u32 %1, 0;\n mov.u32 %2, 0;\n mov.u32 %3, 0;\n"
-        " @p ld.global.nc.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;\n}"
-        : "=&r"(v.x), "=&r"(v.y), "=&r"(v.z), "=&r"(v.w) : "l"(ptr), "l"(pol), "r"((uint32_t)on));
-    return v;
-#else
-    (void)pol;
-    return on ? *ptr : uint4{0u, 0u, 0u, 0u};
-#endif
-}
 // the part of a rank entry that a rank needs (count + row bits), loaded only when `on`; and the rank of offset `off`
 // in that entry when `on`, else in `va`
-#if NTC_RANK_NODES == 32
 typedef uint2 RankPart;
 NTC_HD RankPart ld_rank_part_if(const uint4* ptr, uint64_t pol, bool on) { return ld8x2_keep_if(ptr, pol, on); }
 NTC_HD uint32_t entry_rank_sel(const uint4& va, const RankPart& vb, bool on, uint32_t off) {
     const uint32_t cnt = on ? vb.x : va.x, bits = on ? vb.y : va.y;
     return cnt + (uint32_t)NTC_POPC(bits & ((1u << off) - 1u));
 }
-#else
-typedef uint4 RankPart;
-NTC_HD RankPart ld_rank_part_if(const uint4* ptr, uint64_t pol, bool on) { return ld16_keep_if(ptr, pol, on); }
-NTC_HD uint32_t entry_rank_sel(const uint4& va, const RankPart& vb, bool on, uint32_t off) {
-    uint4 v;
-    v.x = on ? vb.x : va.x; v.y = on ? vb.y : va.y; v.z = on ? vb.z : va.z; v.w = 0;
-    return entry_rank(v, off);
-}
-#endif
 NTC_HD uint64_t ld8_keep(const uint64_t* ptr, uint64_t pol) {
 #if defined(__CUDA_ARCH__)
     uint64_t v;

@@ -93,13 +93,8 @@ void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out, int n_t
                 uint32_t* e = out->data() + b * 16 + c * 4;
                 e[0] = (uint32_t)idx.C[c] + rank(c, base);  // C[c] folded in: extend_right is entry count + popcount
                 e[1] = (uint32_t)bits;
-#if NTC_RANK_NODES == 32
                 e[2] = (uint32_t)q;
                 e[3] = 0;
-#else
-                e[2] = (uint32_t)((bits >> 32) & 0xFFFF) | (uint32_t)((q & 0xFFFF) << 16);
-                e[3] = (uint32_t)(q >> 16);
-#endif
             }
         }
     });

@@ -32,7 +32,7 @@ int32_t build_index(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n
 // ---- derived device layouts (built on the host, uploaded by ntc_ctx_create) ----
 
 // Rank blocks: 64 bytes per kBlockNodes nodes = 4 x 16-byte entries (A,C,G,T), entry =
-//   u32 C[c] + ones of this row before the block | row bits | Q bits   (32 + 32 (+ 32 spare) or 48 + 48 bits)
+//   u32 C[c] + ones of this row before the block | 32 row bits | 32 Q bits | spare word
 // Q[v] = node v is alone in its (k-1)-suffix group  <=>  LCS[v] < k-1 and (v+1 == n or LCS[v+1] < k-1).
 // One rank probe = one aligned 16-byte load = one 32-byte L2 sector.
 void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out /* 16 u32 per block */, int n_threads);
