@@ -401,3 +401,27 @@ def test_config_c2_full_size_round_trip_and_sampled_parity():
         r, _ = ctx.encode_batch(bases[int(off[lo]): int(off[hi])], off[lo: hi + 1] - off[lo])
         parts.append(r)
     assert (sharding.concat_in_rank_order(parts) == rec).all()
+
+
+def test_record_length_limit_2_pow_24(backend):
+    """Maximum sizes: a read that is one unbroken unique match.  Self-encoding a contig of n bases gives a first record
+    of hops * k + 1 bases (src/lib.rs:186-203); at >= 2^24 the reference asserts (src/lib.rs:226) -> NTC_ERR_LEN24, just
+    below it the record is legal and must survive the round trip.  Also the longest chain of matching-statistics tiles
+    the default tile length produces (unique-predecessor runs continuing across every tile border)."""
+    rng = np.random.default_rng(2024)
+    k = 31
+    contig = helpers.random_seq(rng, (1 << 24) + 4 * k)
+    index = nt.Index.build([contig], k, False)
+    ctx = make_ctx(backend, index)
+    with pytest.raises(nt.NtcError) as e:
+        ctx.encode_batch(*nt.concat_reads([contig]))
+    assert e.value.code == 6                                          # NTC_ERR_LEN24
+    n_ok = ((1 << 24) - 2) // k * k - k + 5                           # first record well below the limit
+    read = np.ascontiguousarray(contig[100: 100 + n_ok])
+    bases, off = nt.concat_reads([read, contig[:500], read[: 3 * k]])
+    rec, roff = ctx.encode_batch(bases, off)
+    lens = np.where((rec >> np.uint64(57)) & np.uint64(1), rec >> np.uint64(58), (rec >> np.uint64(32)) & np.uint64(0xFFFFFF))
+    assert int(lens.max()) > (1 << 23) and int(lens.max()) < (1 << 24)
+    assert int(lens[int(roff[0]): int(roff[1])].sum()) == n_ok        # src/lib.rs:227
+    db, doff = ctx.decode_batch(rec)
+    assert (doff == off).all() and (db == bases).all()
