@@ -223,7 +223,7 @@ int32_t decode_walk(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint64_
         // (a two-pass variant -- walk to 2-bit slots per record, then one thread per sequence formatting header + bases
         // left to right -- measured slower on B200: 3.31 vs 2.56 ms on C3, 9.6 vs 6.0 ms on C5; r1 A/B, profiles/r1)
         Timed t(ctx, KC_WALK, st);
-        walk_kernel<<<blocks_for(n_rec, 128), 128, 0, st>>>(ctx->dix, d_records, n_rec, (const uint64_t*)lane.base_off.p,
+        walk_kernel<<<blocks_for(n_rec, kWalkThreads), kWalkThreads, 0, st>>>(ctx->dix, d_records, n_rec, (const uint64_t*)lane.base_off.p,
                                                             (const uint64_t*)lane.seq_idx.p, (const uint64_t*)lane.seq_endkey.p,
                                                             (const uint64_t*)lane.dec_small.p, first_no, fasta, d_out, cap, d_counts,
                                                             ctx->d_status);

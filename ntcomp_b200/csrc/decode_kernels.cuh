@@ -268,13 +268,53 @@ NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, ui
     if (closes) emit_header(lw, first_no + sid, sid != 0);
     lw.finish();
 }
-__global__ void __launch_bounds__(128) walk_kernel(DevIndex ix, const uint64_t* __restrict__ rec, uint64_t n_rec,
+// Work assignment inside a block.  A record costs one dependent jump-table load + two word pushes per 16 bases, and the
+// lengths of neighbouring records differ by an order of magnitude (150 bp reads at 1 %: 92, 58, a 1-base literal, ...), so
+// with record i on thread i every warp ran as long as its longest record (ncu r1 v12: 8.9 active threads per
+// instruction, issue bound).  The block's records are therefore counting-sorted by their number of 16-base steps
+// (descending, 16 buckets, shared-memory histogram) and handed to the threads in that order: warps get records of
+// (nearly) equal cost, the heaviest warps start first.  Each record is still written by one thread, so the
+// output bytes do not depend on the order.
+#ifndef NTC_WALK_THREADS
+#define NTC_WALK_THREADS 256
+#endif
+#ifndef NTC_WALK_SORT
+#define NTC_WALK_SORT 1
+#endif
+constexpr int kWalkThreads = NTC_WALK_THREADS;
+constexpr uint32_t kWalkBuckets = 16;
+
+NTC_HD uint32_t walk_cost_key(uint64_t w) {   // 0 for literal records, else min(ceil(L / 16), 15)
+    if ((w >> 56) & 2u) return 0;
+    const uint32_t L = (uint32_t)(w >> 32) & 0xFFFFFFu;
+    return tmin((L + 15u) >> 4, kWalkBuckets - 1u);
+}
+
+__global__ void __launch_bounds__(kWalkThreads) walk_kernel(DevIndex ix, const uint64_t* __restrict__ rec, uint64_t n_rec,
                                                    const uint64_t* __restrict__ base_off, const uint64_t* __restrict__ seq_idx,
                                                    const uint64_t* __restrict__ seq_endkey, const uint64_t* __restrict__ totals,
                                                    uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes,
                                                    const uint64_t* __restrict__ counts, uint32_t* __restrict__ status) {
-    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_endkey, totals, first_no, fasta, out, cap_bytes, counts, status,
-                (uint64_t)blockIdx.x * 128 + threadIdx.x);
+    const uint64_t i0 = (uint64_t)blockIdx.x * kWalkThreads;
+#if NTC_WALK_SORT
+    __shared__ uint32_t s_hist[kWalkBuckets];
+    __shared__ uint16_t s_perm[kWalkThreads];
+    const uint32_t tid = threadIdx.x;
+    if (tid < kWalkBuckets) s_hist[tid] = 0;
+    __syncthreads();
+    const uint64_t mine = i0 + tid;
+    const uint32_t bucket = kWalkBuckets - 1u - (mine < n_rec ? walk_cost_key(NTC_LDG(rec + mine)) : 0u);   // heaviest first
+    const uint32_t pos = atomicAdd(&s_hist[bucket], 1u);
+    __syncthreads();
+    uint32_t start = 0;
+    for (uint32_t b = 0; b < bucket; b++) start += s_hist[b];
+    s_perm[start + pos] = (uint16_t)tid;
+    __syncthreads();
+    const uint64_t i = i0 + s_perm[tid];
+#else
+    const uint64_t i = i0 + threadIdx.x;
+#endif
+    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_endkey, totals, first_no, fasta, out, cap_bytes, counts, status, i);
 }
 
 }  // namespace ntc

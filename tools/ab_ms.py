@@ -62,6 +62,9 @@ for _ in range(reps):
 ctx.status(st)
 t = ctx.kernel_times()
 chk = int((d_rec[:n_rec] * 0x9E3779B97F4A7C15).sum().item()) & 0xFFFFFFFFFFFF
+nbytes = int(d_cnt[1].item()) // 8 * 8
+wv = d_out[:nbytes].view(torch.int64)
+ochk = int((wv * (torch.arange(wv.numel(), device=dev) % 1021 + 1)).sum().item()) & 0xFFFFFFFFFFFF
 parts = " ".join("%s=%.3f" % (n, v[0] / reps) for n, v in t.items() if v[1])
 tot = sum(v[0] for v in t.values()) / reps
-print("%-14s reads=%d L=%d err=%d records=%d chk=%012x  total=%.3f ms  %s" % (label, n_reads, L, err, n_rec, chk, tot, parts), flush=True)
+print("%-14s reads=%d L=%d err=%d records=%d chk=%012x out=%012x  total=%.3f ms  %s" % (label, n_reads, L, err, n_rec, chk, ochk, tot, parts), flush=True)
