@@ -109,9 +109,9 @@ int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint
     uint64_t* tile_off = (uint64_t*)lane.tile_off.p;
     uint64_t* tile_tot = tile_off + n_reads + 2;                      // 2 x u64 scan totals
     {
-        Timed t(ctx, KC_SCAN, st, 4);
-        exclusive_scan_pairs(TileLoad{d_offsets, T}, n_reads, (Pair64*)lane.tiles.p, nullptr, tile_tot, tile_off, nullptr, st);
-        tile_desc_kernel<<<blocks_for(n_reads, 256), 256, 0, st>>>(d_offsets, n_reads, tile_off, T, (uint64_t*)lane.desc.p);
+        Timed t(ctx, KC_SCAN, st, 3);
+        exclusive_scan_pairs(TileLoad{d_offsets, T}, n_reads, (Pair64*)lane.tiles.p, nullptr, tile_tot, tile_off, nullptr, st,
+                             TileDescPost{(uint64_t*)lane.desc.p});
     }
     {
         Timed t(ctx, KC_MS, st);
@@ -203,11 +203,11 @@ int32_t decode_prepare(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint
     uint64_t* totals = (uint64_t*)lane.dec_small.p;
     {
         Timed t(ctx, KC_DSCAN, st, 3);
-        exclusive_scan_pairs(RecordLoad{d_records}, n_rec, (Pair64*)lane.dec_tiles.p, nullptr, totals, base_off, seq_idx, st);
+        exclusive_scan_pairs(RecordLoad{d_records}, n_rec, (Pair64*)lane.dec_tiles.p, nullptr, totals, base_off, seq_idx, st,
+                             SeqFirstPost{seq_first});
     }
     {
-        Timed t(ctx, KC_SEQ, st, 2);
-        seq_starts_kernel<<<blocks_for(n_rec, 256), 256, 0, st>>>(d_records, n_rec, seq_idx, seq_first);
+        Timed t(ctx, KC_SEQ, st, 1);
         seq_layout_kernel<<<blocks_for(n_rec + 1, 256), 256, 0, st>>>(base_off, seq_first, totals, n_rec, (uint64_t*)lane.seq_endkey.p,
                                                                       d_seq_offsets, cap_seqs, off_carry, first_no, fasta, cap, d_counts,
                                                                       ctx->d_status);

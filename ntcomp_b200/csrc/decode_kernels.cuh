@@ -55,17 +55,14 @@ NTC_HD uint64_t fasta_overhead(uint64_t first_no, uint64_t sid) {
     return (sid + 1) * 6 + digits + sid;
 }
 
-// seq_first[j] = index of the record that opens sequence j; E_first gives its base offset
-NTC_HD void seq_starts_thread(const uint64_t* __restrict__ rec, uint64_t n_rec, const uint64_t* __restrict__ seq_idx,
-                              uint64_t* __restrict__ seq_first, uint64_t i) {
-    if (i >= n_rec) return;
-    if (record_first(NTC_LDG(rec + i))) seq_first[seq_idx[i]] = i;
-}
-__global__ void __launch_bounds__(256) seq_starts_kernel(const uint64_t* __restrict__ rec, uint64_t n_rec,
-                                                         const uint64_t* __restrict__ seq_idx /* exclusive count of firsts */,
-                                                         uint64_t* __restrict__ seq_first) {
-    seq_starts_thread(rec, n_rec, seq_idx, seq_first, (uint64_t)blockIdx.x * 256 + threadIdx.x);
-}
+// seq_first[j] = index of the record that opens sequence j: noted by the record scan's last pass (scan_down_kernel's
+// post hook; a kernel of its own until r1 v12 -- 0.18 ms per 39 M records for re-reading the records and their prefixes)
+struct SeqFirstPost {
+    uint64_t* seq_first;
+    NTC_HD void operator()(uint64_t i, const Pair64& prefix, const Pair64& v) const {
+        if (v.b) seq_first[prefix.b] = i;
+    }
+};
 
 // ---- per-sequence layout ---------------------------------------------------------------------
 // One thread per sequence j (plus one for the end marker): everything the walk needs about a sequence

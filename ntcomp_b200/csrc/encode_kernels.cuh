@@ -164,13 +164,14 @@ struct TileLoad {
     NTC_HD Pair64 operator()(uint64_t r) const { return Pair64{tiles_of((uint32_t)(offsets[r + 1] - offsets[r]), T), 0}; }
 };
 
-NTC_HD void tile_desc_thread(const uint64_t* __restrict__ offsets, uint64_t n_reads, const uint64_t* __restrict__ tile_off, uint32_t T,
-                             uint64_t* __restrict__ desc, uint64_t r) {
-    if (r >= n_reads) return;
-    const uint32_t nt = tiles_of((uint32_t)(offsets[r + 1] - offsets[r]), T);
-    uint64_t* d = desc + tile_off[r];
-    for (uint32_t t = 0; t < nt; t++) d[t] = (r << kDescTileBits) | t;
-}
+// work-item descriptors, written by the tile scan's last pass (scan_down_kernel's post hook): read r's tiles are items
+// [prefix.a, prefix.a + tiles)
+struct TileDescPost {
+    uint64_t* desc;
+    NTC_HD void operator()(uint64_t r, const Pair64& prefix, const Pair64& v) const {
+        for (uint64_t t = 0; t < v.a; t++) desc[prefix.a + t] = (r << kDescTileBits) | t;
+    }
+};
 
 // `stage` = 4 x blockDim u64 staging slots of this thread's block (shared memory on the GPU),
 // indexed [slot * stride + lane]
@@ -384,11 +385,6 @@ __global__ void __launch_bounds__(kMsThreads, NTC_MS_MIN_BLOCKS) ms_kernel(DevIn
     const uint64_t i = i0 + threadIdx.x;
     if (i >= i1) return;
     ms_thread(ix, pk, offsets, desc[i], T, scratch, counts, status, s_stage + threadIdx.x, kMsThreads);
-}
-
-__global__ void __launch_bounds__(256) tile_desc_kernel(const uint64_t* __restrict__ offsets, uint64_t n_reads,
-                                                        const uint64_t* __restrict__ tile_off, uint32_t T, uint64_t* __restrict__ desc) {
-    tile_desc_thread(offsets, n_reads, tile_off, T, desc, (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
 __global__ void __launch_bounds__(256) count_kernel(DevIndex ix, const uint64_t* __restrict__ offsets, uint64_t n_reads, uint32_t T,

@@ -56,7 +56,8 @@ static void run_ms(const EmulIndex* e, const uint8_t* bases, const uint64_t* off
     TileLoad tl{offsets, T};
     for (uint64_t r = 0; r < n_reads; r++) tile_off[r + 1] = tile_off[r] + tl(r).a;
     std::vector<uint64_t> desc(tile_off[n_reads] + 1, ~0ull);
-    for (uint64_t r = 0; r < n_reads; r++) tile_desc_thread(offsets, n_reads, tile_off.data(), T, desc.data(), r);
+    TileDescPost tpost{desc.data()};
+    for (uint64_t r = 0; r < n_reads; r++) tpost(r, Pair64{tile_off[r], 0}, tl(r));
     uint64_t stage[4];
     // items in reverse order: tiles of a read must not depend on the order in which they run
     for (uint64_t i = tile_off[n_reads]; i-- > 0;) ms_thread(e->dix, packed->data(), offsets, desc[i], T, sc, counts, status, stage, 1);
@@ -113,10 +114,10 @@ uint32_t emul_decode(void* ep, const uint64_t* rec, uint64_t n_rec, uint64_t fir
     std::vector<uint64_t> base_off(n_rec + 1), seq_idx(n_rec + 1), seq_first(n_rec + 1, 0);
     RecordLoad load{rec};
     uint64_t a = 0, b = 0;
-    for (uint64_t i = 0; i < n_rec; i++) { base_off[i] = a; seq_idx[i] = b; Pair64 p = load(i); a += p.a; b += p.b; }
+    SeqFirstPost post{seq_first.data()};
+    for (uint64_t i = 0; i < n_rec; i++) { base_off[i] = a; seq_idx[i] = b; Pair64 p = load(i); post(i, Pair64{a, b}, p); a += p.a; b += p.b; }
     base_off[n_rec] = a; seq_idx[n_rec] = b;
     uint64_t totals[2] = {a, b};
-    for (uint64_t i = 0; i < n_rec; i++) seq_starts_thread(rec, n_rec, seq_idx.data(), seq_first.data(), i);
     std::vector<uint64_t> seq_endkey(n_rec + 1, 0);
     for (uint64_t j = 0; j <= n_rec; j++)
         seq_layout_thread(base_off.data(), seq_first.data(), totals, n_rec, seq_endkey.data(), seq_offsets, cap_seqs, 0, first_no, fasta, cap,
