@@ -101,7 +101,7 @@ uint32_t tile_len_for(const ntc_ctx* ctx, uint64_t n_bases) {
 // matching statistics of a packed batch: tiles per read -> scan -> item descriptors -> ms_kernel over
 // the items -> record counts of multi-tile reads.  counts may be null (diagnostic entry point).
 int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint64_t* d_offsets, uint64_t n_reads, uint64_t n_bases,
-                    uint32_t T, uint64_t* scratch, uint32_t* counts, uint32_t* status, cudaStream_t st) {
+                    uint32_t T, uint64_t* scratch, uint32_t* counts, uint32_t* status, cudaStream_t st, bool keep_records = false) {
     const uint64_t max_items = n_reads + n_bases / T;                 // sum over reads of max(1, ceil(len / T)) is at most this
     NTC_CUDA_TRY(ensure(&lane.tile_off, (n_reads + 2) * 8 + 16));
     NTC_CUDA_TRY(ensure(&lane.desc, (max_items + 1) * 8));
@@ -116,11 +116,12 @@ int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint
     {
         Timed t(ctx, KC_MS, st);
         ms_kernel<<<blocks_for(max_items, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, (const uint64_t*)lane.desc.p,
-                                                                            tile_off + n_reads, T, scratch, counts, status);
+                                                                            tile_off + n_reads, T, scratch, counts, status, keep_records ? 1 : 0);
     }
     if (counts && n_bases > (uint64_t)T) {                            // no read can exceed T otherwise
         Timed t(ctx, KC_SCAN, st);
-        count_kernel<<<blocks_for(n_reads, 256), 256, 0, st>>>(ctx->dix, d_offsets, n_reads, T, scratch, counts, status);
+        count_kernel<<<blocks_for(n_reads, 256), 256, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, T, scratch, counts, status,
+                                                               keep_records ? 1 : 0);
     }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
@@ -163,7 +164,7 @@ int32_t encode_pipeline(ntc_ctx* ctx, Lane& lane, int mode, const uint8_t* d_bas
                                                                                                 ctx->d_status);
     }
     const uint32_t T = tile_len_for(ctx, n_bases);
-    int32_t rc = ms_pipeline(ctx, lane, packed, d_offsets, n_reads, n_bases, T, scratch, counts, ctx->d_status, st);
+    int32_t rc = ms_pipeline(ctx, lane, packed, d_offsets, n_reads, n_bases, T, scratch, counts, ctx->d_status, st, mode == 0);
     if (rc) return rc;
     if (wait_scan) NTC_CUDA_TRY(cudaStreamWaitEvent(st, wait_scan, 0));
     {

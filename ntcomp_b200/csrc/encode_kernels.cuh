@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(kPackThreads) pack2bit_kernel(const uint8_t* _
 // than the tile length T is processed as independent tiles of T positions (ms_thread), each counting
 // its runs from its own first position; a run that reaches the start of its tile continues with the
 // run ending at the last position of the previous tile.
-NTC_HD uint32_t unique_run(const uint64_t* __restrict__ sc, uint32_t q, uint32_t T, uint32_t limit) {
+NTC_HD uint32_t unique_run(const uint64_t* sc, uint32_t q, uint32_t T, uint32_t limit) {
     uint32_t run = entry_urun(sc[q]);
     uint32_t total = run;
     while (total < limit) {
@@ -96,7 +96,8 @@ NTC_HD uint32_t unique_run(const uint64_t* __restrict__ sc, uint32_t q, uint32_t
 }
 
 template <typename Sink>
-NTC_HD uint32_t segment_read(const uint64_t* __restrict__ sc, uint32_t len, uint32_t k, uint32_t T, Sink&& sink) {
+NTC_HD uint32_t segment_read(const uint64_t* sc,   // no __restrict__: CountSink parks records in dead entries
+                              uint32_t len, uint32_t k, uint32_t T, Sink&& sink) {
     uint32_t i = len, cnt = 0;
     while (i > 0) {
         uint64_t ent = sc[i - 1];
@@ -131,9 +132,34 @@ NTC_HD uint32_t segment_read(const uint64_t* __restrict__ sc, uint32_t len, uint
 //   ncu r1 v1: inner retry loop + byte-wise LCS scans = 60% of issued instructions at ~1 thread/warp
 //   ncu r1 v2: vectorised scans in a separate state   = 51% of issued instructions at ~2 threads/warp
 // ------------------------------------------------------------------------------------------
+// Sink of the counting pass.  With `dst` set it also builds the record words (src/encode.rs:144-160) and parks record c
+// of the read at dst[-c], dst = the read's last scratch entry: after c+1 records the segmentation has consumed at
+// least c+1 bases and never again reads an entry at or right of its cursor, so the slot is dead by then.  emit_kernel<0>
+// is then a gather of `count` contiguous words per read instead of a second segmentation over ~12 scattered
+// sectors (ncu r1 v12: emit_kernel 0.87 ms, 5.1 GB of DRAM reads, 76 % DRAM busy).
 struct CountSink {
+    const uint64_t* packed;   // generic pointer: the block's staged reads (shared memory) or the packed stream
+    uint64_t a;
+    uint64_t* dst;            // null: count only (triples mode segments again in emit_kernel<1>)
+    uint64_t first = 1;
     uint32_t big = 0;
-    NTC_HD void operator()(uint32_t L, uint32_t, uint32_t, uint32_t) { big |= (L >= (1u << 24)); }
+    NTC_HD void operator()(uint32_t L, uint32_t v, uint32_t end_pos, uint32_t) {
+        big |= (L >= (1u << 24));
+        if (!dst) return;
+        uint64_t word;
+        if (L > kLiteralMax) {                                        // src/encode.rs:146-149
+            word = (uint64_t)v | ((uint64_t)(L & 0xFFFFFFu) << 32) | (first << 56);
+        } else {                                                      // src/encode.rs:150-156
+            const uint64_t p = a + end_pos - L;
+            const uint32_t sh = (uint32_t)(p & 31) * 2;
+            uint64_t lit = packed[p >> 5] >> sh;
+            if (sh && (p & 31) + L > 32) lit |= packed[(p >> 5) + 1] << (64 - sh);
+            lit &= (1ull << (2 * L)) - 1ull;                          // L <= 11
+            word = lit | (((first + 2) | ((uint64_t)L << 2)) << 56);
+        }
+        *dst-- = word;
+        first = 0;
+    }
 };
 
 // scratch position of read r: its entries start on a 32-byte sector so that groups of four 8-byte
@@ -177,7 +203,7 @@ struct TileDescPost {
 // indexed [slot * stride + lane]
 NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t* __restrict__ offsets, uint64_t item_desc, uint32_t T,
                       uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts, uint32_t* __restrict__ status,
-                      uint64_t* stage, uint32_t stride) {
+                      uint64_t* stage, uint32_t stride, bool keep_records) {
     const uint64_t r = item_desc >> kDescTileBits;
     const uint32_t tile = (uint32_t)item_desc & ((1u << kDescTileBits) - 1u);
     const uint64_t base0 = NTC_LDG(offsets);
@@ -293,22 +319,24 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         return;
     }
     if (counts && !multi) {
-        CountSink sink;
+        CountSink sink{packed, a, keep_records ? sc + (len - 1u) : nullptr};
         counts[r] = segment_read(sc, len, k, T, sink);
         if (sink.big) NTC_ATOMIC_OR(status, (uint32_t)ST_LEN24);      // src/lib.rs:226
     }
 }
 
 // record count of a read that was processed as several tiles (single-tile reads are counted by ms_thread)
-NTC_HD void count_thread(const DevIndex& ix, const uint64_t* __restrict__ offsets, uint64_t n_reads, uint32_t T,
-                         const uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t r) {
+NTC_HD void count_thread(const DevIndex& ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offsets, uint64_t n_reads,
+                         uint32_t T, uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts, uint32_t* __restrict__ status,
+                         bool keep_records, uint64_t r) {
     if (r >= n_reads) return;
     const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
     if (len <= T) return;
     if (*status & ST_BAD_BASE) { counts[r] = 0; return; }             // some d == 0: segmentation would not terminate (Q3)
     const uint64_t a = offsets[r] - NTC_LDG(offsets);
-    CountSink sink;
-    counts[r] = segment_read(scratch + scratch_base(a, r), len, ix.k, T, sink);
+    uint64_t* sc = scratch + scratch_base(a, r);
+    CountSink sink{packed, a, keep_records ? sc + (len - 1u) : nullptr};
+    counts[r] = segment_read(sc, len, ix.k, T, sink);
     if (sink.big) NTC_ATOMIC_OR(status, (uint32_t)ST_LEN24);
 }
 
@@ -354,7 +382,7 @@ __global__ void __launch_bounds__(kMsThreads, NTC_MS_MIN_BLOCKS) ms_kernel(DevIn
                                                         const uint64_t* __restrict__ offsets, const uint64_t* __restrict__ desc,
                                                         const uint64_t* __restrict__ n_items, uint32_t T,
                                                         uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts,
-                                                        uint32_t* __restrict__ status) {
+                                                        uint32_t* __restrict__ status, int keep_records) {
     __shared__ __align__(16) uint64_t s_packed[kMsStageWords];
     __shared__ uint64_t s_stage[4 * kMsThreads];
     __shared__ __align__(8) uint64_t s_bar;
@@ -384,13 +412,13 @@ __global__ void __launch_bounds__(kMsThreads, NTC_MS_MIN_BLOCKS) ms_kernel(DevIn
     const uint64_t* pk = staged ? (s_packed - w_lo) : packed;                // generic pointer: shared or global
     const uint64_t i = i0 + threadIdx.x;
     if (i >= i1) return;
-    ms_thread(ix, pk, offsets, desc[i], T, scratch, counts, status, s_stage + threadIdx.x, kMsThreads);
+    ms_thread(ix, pk, offsets, desc[i], T, scratch, counts, status, s_stage + threadIdx.x, kMsThreads, keep_records != 0);
 }
 
-__global__ void __launch_bounds__(256) count_kernel(DevIndex ix, const uint64_t* __restrict__ offsets, uint64_t n_reads, uint32_t T,
-                                                    const uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts,
-                                                    uint32_t* __restrict__ status) {
-    count_thread(ix, offsets, n_reads, T, scratch, counts, status, (uint64_t)blockIdx.x * 256 + threadIdx.x);
+__global__ void __launch_bounds__(256) count_kernel(DevIndex ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offsets,
+                                                    uint64_t n_reads, uint32_t T, uint64_t* __restrict__ scratch,
+                                                    uint32_t* __restrict__ counts, uint32_t* __restrict__ status, int keep_records) {
+    count_thread(ix, packed, offsets, n_reads, T, scratch, counts, status, keep_records != 0, (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -437,8 +465,17 @@ NTC_HD void emit_thread(const DevIndex& ix, const uint64_t* __restrict__ packed,
     const uint64_t a = offsets[r] - base0;
     const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
     if (rec_offsets[r + 1] - rel0 > cap) { NTC_ATOMIC_OR(status, (uint32_t)ST_CAPACITY); return; }
-    EmitSink<MODE> sink{ix, packed, out, a, rec_offsets[r] - rel0, 1};
-    segment_read(scratch + scratch_base(a, r), len, ix.k, T, sink);
+    const uint64_t* sc = scratch + scratch_base(a, r);
+    if (MODE == 0) {
+        // the counting pass left record c at entry len-1-c (CountSink): copy them out in order
+        const uint32_t cnt = counts[r];
+        const uint64_t* src = sc + (len - 1u);
+        uint64_t* dst = out + (rec_offsets[r] - rel0);
+        for (uint32_t c = 0; c < cnt; c++) dst[c] = src[-(int64_t)c];
+    } else {
+        EmitSink<MODE> sink{ix, packed, out, a, rec_offsets[r] - rel0, 1};
+        segment_read(sc, len, ix.k, T, sink);
+    }
 }
 
 template <int MODE>

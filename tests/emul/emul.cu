@@ -42,7 +42,7 @@ void emul_index_free(void* p) { delete (EmulIndex*)p; }
 void emul_set_tile_len(void* p, uint32_t T) { ((EmulIndex*)p)->tile_len = T ? (T + 3u) & ~3u : 1u << 22; }
 
 static void run_ms(const EmulIndex* e, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads, std::vector<uint64_t>* packed,
-                   std::vector<uint64_t>* scratch, uint64_t** scratch_aligned, uint32_t* counts, uint32_t* status) {
+                   std::vector<uint64_t>* scratch, uint64_t** scratch_aligned, uint32_t* counts, uint32_t* status, bool keep_records = false) {
     uint64_t nb = offsets[n_reads] - offsets[0];
     packed->assign(nb / 32 + 6, 0);
     scratch->assign(scratch_entries(nb, n_reads) + 4, 0);
@@ -60,8 +60,8 @@ static void run_ms(const EmulIndex* e, const uint8_t* bases, const uint64_t* off
     for (uint64_t r = 0; r < n_reads; r++) tpost(r, Pair64{tile_off[r], 0}, tl(r));
     uint64_t stage[4];
     // items in reverse order: tiles of a read must not depend on the order in which they run
-    for (uint64_t i = tile_off[n_reads]; i-- > 0;) ms_thread(e->dix, packed->data(), offsets, desc[i], T, sc, counts, status, stage, 1);
-    if (counts) for (uint64_t r = 0; r < n_reads; r++) count_thread(e->dix, offsets, n_reads, T, sc, counts, status, r);
+    for (uint64_t i = tile_off[n_reads]; i-- > 0;) ms_thread(e->dix, packed->data(), offsets, desc[i], T, sc, counts, status, stage, 1, keep_records);
+    if (counts) for (uint64_t r = 0; r < n_reads; r++) count_thread(e->dix, packed->data(), offsets, n_reads, T, sc, counts, status, keep_records, r);
 }
 
 // mode 0 records, 1 triples.  Returns the accumulated status bits.
@@ -72,7 +72,7 @@ uint32_t emul_encode(void* ep, const uint8_t* bases, const uint64_t* offsets, ui
     std::vector<uint64_t> packed, scratch;
     std::vector<uint32_t> counts(n_reads + 1, 0);
     uint64_t* sc = nullptr;
-    run_ms(e, bases, offsets, n_reads, &packed, &scratch, &sc, counts.data(), &status);
+    run_ms(e, bases, offsets, n_reads, &packed, &scratch, &sc, counts.data(), &status, mode == 0);
     std::vector<uint64_t> roff(n_reads + 1, 0);
     for (uint64_t r = 0; r < n_reads; r++) roff[r + 1] = roff[r] + counts[r];   // exclusive scan (scan.cuh on the GPU)
     for (uint64_t r = 0; r < n_reads; r++) {
