@@ -291,6 +291,9 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     build_jump_table(*idx, &jump, threads);
     std::vector<uint32_t> lcs;
     build_lcs_words(*idx, &lcs);
+    std::vector<uint32_t> pfx;
+    const bool use_pfx = idx->k >= 10 && !getenv("NTC_NO_PREFIX_TABLE");   // a tile's warm-up (k-1 bases) must cover the 8 bases
+    if (use_pfx) build_prefix_table(rank, idx->n, &pfx, ctx->dix.c_start);
     auto fail = [&](const char* what, cudaError_t err) {
         set_error(std::string(what) + ": " + cudaGetErrorString(err));
         ntc_ctx_destroy(ctx);
@@ -305,6 +308,10 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     if ((e = cudaMemcpy(ctx->d_rank, rank.data(), ctx->index_bytes[0], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload rank", e);
     if ((e = cudaMemcpy(ctx->d_lcs, lcs.data(), ctx->index_bytes[1], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload lcs", e);
     if ((e = cudaMemcpy(ctx->d_jump, jump.data(), ctx->index_bytes[2], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload jump", e);
+    if (use_pfx) {
+        if ((e = cudaMalloc(&ctx->d_pfx, pfx.size() * 4)) != cudaSuccess) return fail("cudaMalloc prefix table", e);
+        if ((e = cudaMemcpy(ctx->d_pfx, pfx.data(), pfx.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload prefix table", e);
+    }
     if ((e = cudaMalloc((void**)&ctx->d_status, 16)) != cudaSuccess) return fail("cudaMalloc status", e);
     if ((e = cudaMalloc((void**)&ctx->d_totals, 64)) != cudaSuccess) return fail("cudaMalloc totals", e);
     cudaMemset(ctx->d_status, 0, 16);
@@ -319,6 +326,7 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     ctx->dix.rank = (const uint4*)ctx->d_rank;
     ctx->dix.lcsx = (const uint32_t*)ctx->d_lcs;
     ctx->dix.jump = (const uint64_t*)ctx->d_jump;
+    ctx->dix.pfx = (const uint4*)ctx->d_pfx;
     ctx->dix.n = (uint32_t)idx->n;
     ctx->dix.k = idx->k;
     spec_window(idx->n, &ctx->dix.spec_lo, &ctx->dix.spec_span);
@@ -369,7 +377,7 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
     free_column_decode_work(ctx);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
     for (auto ev : ctx->event_pool) cudaEventDestroy(ev);
-    cudaFree(ctx->d_rank); cudaFree(ctx->d_lcs); cudaFree(ctx->d_jump);
+    cudaFree(ctx->d_rank); cudaFree(ctx->d_lcs); cudaFree(ctx->d_jump); cudaFree(ctx->d_pfx);
     cudaFree(ctx->d_status); cudaFree(ctx->d_totals);
     delete ctx;
 }

@@ -41,6 +41,7 @@ struct ntc_ctx {
     void* d_rank = nullptr;
     void* d_lcs = nullptr;
     void* d_jump = nullptr;
+    void* d_pfx = nullptr;   // prefix table (null when k < 10)
     uint64_t index_bytes[3] = {0, 0, 0};
     uint32_t k = 0;
     uint64_t n = 0;

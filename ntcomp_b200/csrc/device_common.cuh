@@ -39,6 +39,8 @@ struct DevIndex {
                            //   row bits, Q bits, 0}
     const uint32_t* lcsx;  // [n + 1] LCS[i] | dist to previous smaller << 8 | LCS[i+1] << 16 | dist to next smaller of i+1 << 24
     const uint64_t* jump;  // [n] pred^16 | chars16 << 32
+    const uint4* pfx;      // [4^8 * 2] prefix table (host_index.h), null when k < 10
+    uint32_t c_start[4];   // interval start after the single base c
     uint32_t n;
     uint32_t k;
     uint32_t spec_lo, spec_span;  // ms_kernel speculates LCS loads while spec_lo <= d < spec_lo + spec_span

@@ -230,6 +230,31 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
     uint32_t left = 16u - (uint32_t)((a + j) & 15);
     uint32_t word = *wp >> (((uint32_t)(a + j) & 15u) * 2u);
     uint32_t c = word & 3u;
+    // the first 8 bases of a read (or of a tile's warm-up) start from the empty match: their 8 iterations -- 16 rank
+    // probes in different blocks, the interval is wide -- are one 32-byte prefix-table entry (host_index.h)
+    if (ix.pfx && p1 - j >= 8u) {
+        const uint32_t pre = (left >= 8u ? word : (word | (wp[1] << (2u * left)))) & 0xFFFFu;
+        const uint4 lo = ld16_keep(ix.pfx + 2u * pre, keep), hi = ld16_keep(ix.pfx + 2u * pre + 1u, keep);
+        if (hi.w > hi.z) {                                            // every prefix of these 8 bases is in the index
+            if (tile == 0) {                                          // entries 0..3: one sector; 4..6 wait for entry 7 in the stage
+                const uint32_t c0 = pre & 3u;   // select chain: indexing the by-value parameter struct would copy it to local memory
+                const uint32_t s1 = c0 == 0u ? ix.c_start[0] : c0 == 1u ? ix.c_start[1] : c0 == 2u ? ix.c_start[2] : ix.c_start[3];
+                st32_stream(sc, make_entry(s1, 1, 0), make_entry(lo.x, 2, 0), make_entry(lo.y, 3, 0),
+                            make_entry(lo.z, 4, 0), ix.pol_stream);
+                stage[0] = make_entry(lo.w, 5, 0);
+                stage[stride] = make_entry(hi.x, 6, 0);
+                stage[2 * stride] = make_entry(hi.y, 7, 0);
+            }
+            s = hi.z; e = hi.w; d = 8; j += 8;
+            if (left > 8u) { word >>= 16; left -= 8u; }
+            else {
+                const uint32_t used = 8u - left;                      // bases taken from the next word
+                word = j < p1 ? *++wp >> (2u * used) : 0u;
+                left = 16u - used;
+            }
+            c = word & 3u;
+        }
+    }
     while (j < p1) {
         // a singleton interval [s, s+1) -- the common case once the match is longer than ~log4(n) -- needs one
         // entry only, also when s is the last node of its block: rank(s+1) = rank(s) + row bit of s

@@ -56,6 +56,32 @@ int32_t finalize_index(ntc_index* idx) {
     return NTC_OK;
 }
 
+void build_prefix_table(const std::vector<uint32_t>& rb, uint64_t n, std::vector<uint32_t>* out, uint32_t c_start[4]) {
+    // the same arithmetic as the device's extend_right: entry count + popcount of the row bits below the offset
+    auto rank = [&](uint32_t c, uint64_t i) -> uint32_t {
+        const uint32_t* e = rb.data() + (i / kBlockNodes) * 16 + c * 4;
+        const uint32_t off = (uint32_t)(i % kBlockNodes);
+        return e[0] + (uint32_t)__builtin_popcount(e[1] & ((1u << off) - 1u));
+    };
+    const uint32_t n_entries = 1u << (2 * kPrefixBases);
+    out->assign((size_t)n_entries * 8, 0);
+    for (uint32_t c = 0; c < 4; c++) c_start[c] = rank(c, 0);
+    for (uint32_t x = 0; x < n_entries; x++) {
+        uint32_t s = 0, e = (uint32_t)n, w[8];
+        bool ok = true;
+        for (uint32_t l = 1; l <= kPrefixBases && ok; l++) {
+            const uint32_t c = (x >> (2 * (l - 1))) & 3u;
+            s = rank(c, s);
+            e = rank(c, e);
+            ok = s < e;
+            if (l >= 2) w[l - 2] = s;
+        }
+        if (!ok) continue;
+        w[7] = e;
+        for (int i = 0; i < 8; i++) (*out)[(size_t)x * 8 + i] = w[i];
+    }
+}
+
 void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out, int n_threads) {
     const uint64_t n = idx.n;
     const uint32_t k = idx.k;

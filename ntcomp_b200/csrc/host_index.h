@@ -43,6 +43,14 @@ void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out /* 16 u3
 void build_lcs_words(const ntc_index& idx, std::vector<uint32_t>* out);
 void spec_window(uint64_t n_sets, uint32_t* lo, uint32_t* span);
 
+// Prefix table for the first kPrefixBases bases of a read (or of a tile's warm-up): entry x (base i of the prefix at
+// bits 2i..2i+1) = 8 x u32 = interval starts after 2..8 bases, interval end after 8 bases -- what the first 8
+// iterations of matching_statistics compute from the empty match (16 rank probes) in one 32-byte sector.  All
+// zero when some prefix of x is absent from the index (the kernel then takes the ordinary path).
+// c_start[c] = interval start after the single base c.
+constexpr uint32_t kPrefixBases = 8;
+void build_prefix_table(const std::vector<uint32_t>& rank_blocks, uint64_t n, std::vector<uint32_t>* out, uint32_t c_start[4]);
+
 // Decode jump table: one u64 per node = pred^16(v) (low 32 bits) | last 16 bases of node v's k-mer
 // (high 32 bits, base at string position k-16+i in bits 2i..2i+1).  Root and '$' positions code 0.
 void build_jump_table(const ntc_index& idx, std::vector<uint64_t>* out, int n_threads);

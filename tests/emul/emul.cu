@@ -20,6 +20,7 @@ struct EmulIndex {
     std::vector<uint32_t> rank;
     std::vector<uint64_t> jump;
     std::vector<uint32_t> lcs;
+    std::vector<uint32_t> pfx;
     DevIndex dix;
 };
 
@@ -33,6 +34,11 @@ void* emul_index_create(const ntc_index* idx) {
     e->dix.rank = (const uint4*)e->rank.data();
     e->dix.lcsx = e->lcs.data();
     e->dix.jump = e->jump.data();
+    e->dix.pfx = nullptr;
+    if (idx->k >= 10) {                                              // as ntc_ctx_create
+        build_prefix_table(e->rank, idx->n, &e->pfx, e->dix.c_start);
+        e->dix.pfx = (const uint4*)e->pfx.data();
+    }
     e->dix.n = (uint32_t)idx->n;
     e->dix.k = idx->k;
     spec_window(idx->n, &e->dix.spec_lo, &e->dix.spec_span);

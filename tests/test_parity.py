@@ -425,3 +425,34 @@ def test_record_length_limit_2_pow_24(backend):
     assert int(lens[int(roff[0]): int(roff[1])].sum()) == n_ok        # src/lib.rs:227
     db, doff = ctx.decode_batch(rec)
     assert (doff == off).all() and (db == bases).all()
+
+
+def test_prefix_table_boundaries(small_cases):
+    """ms_kernel takes the first 8 bases of a read (and of a tile's warm-up) from the prefix table when k >= 10:
+    read lengths around 8 and around the 16-base word boundary, reads at every alignment of the packed stream,
+    reads whose first 8-mer is not in the index (table entry empty -> ordinary path), with and without tiles."""
+    rng = np.random.default_rng(88)
+    for case in small_cases:
+        src = [c for c in case.contigs if len(c) > 0]
+        reads = helpers.sample_reads(rng, src, 120, lengths=[1, 2, 7, 8, 9, 10, 15, 16, 17, 23, 24, 25, 31, 32, 33, 40, 300],
+                                     error_rates=[0, 0.02, 0.1], k=case.k)
+        # foreign starts: random 8-mers (mostly absent from a small index) in front of genuine sequence
+        for _ in range(40):
+            r = helpers.sample_reads(rng, src, 1, lengths=[12, 60, 200], error_rates=[0], k=case.k)[0]
+            reads.append(np.concatenate([helpers.random_seq(rng, int(rng.integers(1, 12))), r]))
+        for T in (0, 256):
+            case.ctx.set_tile_len(T)
+            bases, off = nt.concat_reads(reads)
+            d, s = case.ctx.matching_statistics(bases, off)
+            for i, r in enumerate(reads):
+                od, os_, _ = case.oracle.matching_statistics(r)
+                lo, hi = int(off[i]), int(off[i + 1])
+                assert (d[lo:hi] == od).all() and (s[lo:hi] == os_).all(), (case.k, T, i, len(r))
+            rec, roff = case.ctx.encode_batch(bases, off)
+            orec, oroff = case.oracle.encode_reads(bases, off, fast=False, threads=8)
+            assert (roff == oroff).all() and (rec == orec).all(), (case.k, T)
+            for r in reads[:30]:
+                got = nt.encode_sequence(r, case.ctx)
+                want = case.oracle.encode_sequence(r, fast=False)
+                assert [(ln, (rg.start, rg.stop)) for ln, rg in got] == want, case.k
+        case.ctx.set_tile_len(0)
