@@ -117,21 +117,52 @@ NTC_HD void store_lanes(uint8_t* word_addr, uint64_t w, uint32_t lo, uint32_t hi
     }
 }
 
+// Complete words leave in descending address order; the upper half of a 16-byte unit waits in `hold` for the lower
+// half, and the two go out as one 16-byte store (ncu r1 v14: after the cost sort walk_kernel ran at the L1TEX sector
+// rate, 298 M store sectors for 51 M sectors of text -- every 8-byte store of a lane is a sector access of its own).
+#ifndef NTC_WALK_PAIR16
+#define NTC_WALK_PAIR16 1
+#endif
 struct LeftWriter {
-    uint8_t* out;   // 8-byte aligned base of the output buffer
+    uint8_t* out;   // 16-byte aligned base of the output buffer
     uint64_t p;     // bytes [p, segment end) are done; pending bytes of the word holding p sit in acc
     uint64_t acc;   // lanes [p & 7, top) of the aligned word at p & ~7
+    uint64_t hold;  // complete word at hold_pos (an upper half) waiting for its lower half
     uint32_t top;
+    bool have;
 
-    NTC_HD void init(uint8_t* base, uint64_t end) { out = base; p = end; acc = 0; top = (uint32_t)(end & 7); }
+    NTC_HD void init(uint8_t* base, uint64_t end) { out = base; p = end; acc = 0; hold = 0; have = false; top = (uint32_t)(end & 7); }
+    // lanes [0, hi) of the aligned word at byte position pos (a multiple of 8)
+    NTC_HD void put(uint64_t pos, uint64_t w, uint32_t hi) {
+        if (hi != 8) { store_lanes(out + pos, w, 0, hi); return; }      // right edge of the segment: nothing is held yet
+#if !NTC_WALK_PAIR16
+        *(uint64_t*)(out + pos) = w;
+        return;
+#endif
+        if (pos & 8) {
+            if (have) *(uint64_t*)(out + pos + 8) = hold;              // (not reached: words arrive 8 bytes apart)
+            hold = w;
+            have = true;
+        } else if (have) {
+#if defined(__CUDA_ARCH__)
+            *(ulonglong2*)(out + pos) = make_ulonglong2(w, hold);
+#else
+            *(uint64_t*)(out + pos) = w;
+            *(uint64_t*)(out + pos + 8) = hold;
+#endif
+            have = false;
+        } else {
+            *(uint64_t*)(out + pos) = w;
+        }
+    }
     // x = the 8 bytes for positions [p-8, p)
     NTC_HD void push8(uint64_t x) {
         uint32_t q = (uint32_t)(p & 7);
         if (q == 0) {
-            *(uint64_t*)(out + p - 8) = x;
+            put(p - 8, x, 8);
         } else {
             uint32_t sh = 8 * q;
-            store_lanes(out + (p & ~7ull), acc | (x >> (64 - sh)), 0, top);
+            put(p & ~7ull, acc | (x >> (64 - sh)), top);
             acc = x << sh;
             top = 8;
         }
@@ -146,7 +177,7 @@ struct LeftWriter {
         const uint32_t sh = 8 * q;
         const uint64_t w = acc | (x >> (64 - sh));
         if (n < q) { acc = w; p -= n; return; }                        // lanes [q-n, top) pending
-        store_lanes(out + (p & ~7ull), w, 0, top);                     // the word holding p is complete
+        put(p & ~7ull, w, top);                                        // the word holding p is complete
         acc = x << sh;                                                 // the other n-q bytes open the next word
         top = 8;
         p -= n;
@@ -154,19 +185,8 @@ struct LeftWriter {
     // writes what is pending; the writer's bytes end at p
     NTC_HD void finish() {
         const uint32_t q = (uint32_t)(p & 7);
+        if (have) { *(uint64_t*)(out + ((p + 7) & ~7ull)) = hold; have = false; }   // the held word is the one right of p's word
         if (q) store_lanes(out + (p & ~7ull), acc, q, top);
-    }
-    // x holds n < 8 bytes for positions [p-n, p) in its UPPER lanes; ends the segment
-    NTC_HD void push_last(uint64_t x, uint32_t n) {
-        uint32_t q = (uint32_t)(p & 7);
-        uint8_t* wa = out + (p & ~7ull);
-        if (n == 0) { if (q) store_lanes(wa, acc, q, top); return; }
-        if (q == 0) { store_lanes(wa - 8, x, 8 - n, 8); return; }
-        uint32_t sh = 8 * q;
-        uint64_t w = acc | (x >> (64 - sh));
-        if (n <= q) { store_lanes(wa, w, q - n, top); return; }
-        store_lanes(wa, w, 0, top);
-        store_lanes(wa - 8, x << sh, 8 - (n - q), 8);
     }
 };
 
@@ -215,30 +235,51 @@ NTC_HD void emit_header(LeftWriter& lw, uint64_t no, bool leading_newline) {
     lw.push_n(acc, n);
 }
 
-// one thread per record: walk / unpack and store ASCII bases (+ the FASTA framing left of a START segment)
-NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, uint64_t n_rec, const uint64_t* __restrict__ base_off,
-                        const uint64_t* __restrict__ seq_idx, const uint64_t* __restrict__ seq_endkey, const uint64_t* __restrict__ totals,
-                        uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes, const uint64_t* __restrict__ counts,
-                        uint32_t* __restrict__ status, uint64_t i) {
-    if (i >= n_rec) return;
-    if (counts[1] > cap_bytes) return;  // capacity error already flagged
+// What a record's thread needs, gathered with record i on thread i (coalesced loads) before the block's records are
+// re-dealt by cost: with the metadata loaded after the deal, every lane touched its own sectors of rec / base_off /
+// seq_idx (ncu r1 v14: 284 M load sectors, ~100 M of them jump-table entries).
+struct WalkItem {
+    uint64_t w;        // record word
+    uint64_t seg_end;  // output position just right of the record's last base
+    uint64_t sid;      // sequence (0-based in this batch)
+    uint32_t L;        // bases
+    uint32_t flags;    // bit 0: something to write, bit 1: START segment of its sequence (writes the FASTA framing)
+};
+
+NTC_HD WalkItem walk_prepare(const uint64_t* __restrict__ rec, uint64_t n_rec, const uint64_t* __restrict__ base_off,
+                             const uint64_t* __restrict__ seq_idx, const uint64_t* __restrict__ seq_endkey, const uint64_t* __restrict__ totals,
+                             int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes, const uint64_t* __restrict__ counts, uint64_t i) {
+    WalkItem it{0, 0, 0, 0, 0};
+    if (i >= n_rec) return it;
+    if (counts[1] > cap_bytes) return it;  // capacity error already flagged
     const uint64_t w = NTC_LDG(rec + i);
     const uint32_t flag = (uint32_t)(w >> 56);
     const uint64_t incl = seq_idx[i] + (flag & 1u);  // sequences opened up to and including this record
-    if (incl == 0) return;                            // records before the first `first` flag are dropped (src/lib.rs:308-317)
+    if (incl == 0) return it;                         // records before the first `first` flag are dropped (src/lib.rs:308-317)
     const uint64_t sid = incl - 1;
     const uint64_t bo = base_off[i];
     const uint32_t L = (uint32_t)(base_off[i + 1] - bo);
-    // records of a sequence run from its END to its START: this one ends at (sequence end) - (bases before it)
-    const uint64_t seg_end = seq_endkey[sid] - bo;
     // START segment of its sequence = last record before the next `first` flag
     const bool closes = fasta && (i + 1 == n_rec || record_first(NTC_LDG(rec + i + 1)));
     if (fasta && (flag & 1u) && sid + 1 == totals[1]) out[counts[1] - 1] = '\n';   // the stream's final newline
-    if (L == 0 && !closes) return;
+    if (L == 0 && !closes) return it;
+    it.w = w;
+    it.seg_end = seq_endkey[sid] - bo;  // records of a sequence run from its END to its START: (sequence end) - (bases before it)
+    it.sid = sid;
+    it.L = L;
+    it.flags = 1u | (closes ? 2u : 0u);
+    return it;
+}
+
+// walk / unpack one record and store its ASCII bases (+ the FASTA framing left of a START segment)
+NTC_HD void walk_emit(const DevIndex& ix, const WalkItem& it, uint64_t first_no, uint8_t* __restrict__ out, uint32_t* __restrict__ status) {
+    if (!(it.flags & 1u)) return;
+    const uint64_t w = it.w;
+    const uint32_t flag = (uint32_t)(w >> 56), L = it.L;
     // the output buffer may be misaligned by the caller: fold the misalignment into the position
-    const uint64_t mis = (uint64_t)((uintptr_t)out & 7u);
+    const uint64_t mis = (uint64_t)((uintptr_t)out & 15u);
     LeftWriter lw;
-    lw.init(out - mis, seg_end + mis);
+    lw.init(out - mis, it.seg_end + mis);
 
     if (flag & 2u) {  // literal record (<= 32 bases), src/lib.rs:295-306
         uint64_t bits = L >= 32 ? (w & 0x00FFFFFFFFFFFFFFull) : (w & ((1ull << (2 * L)) - 1ull));   // 56 payload bits + zeros
@@ -262,9 +303,19 @@ NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, ui
             v = (uint32_t)ent;
         }
     }
-    if (closes) emit_header(lw, first_no + sid, sid != 0);
+    if (it.flags & 2u) emit_header(lw, first_no + it.sid, it.sid != 0);
     lw.finish();
 }
+
+// one thread per record (the CPU emulation's entry point; the kernel deals prepared items to threads by cost)
+NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, uint64_t n_rec, const uint64_t* __restrict__ base_off,
+                        const uint64_t* __restrict__ seq_idx, const uint64_t* __restrict__ seq_endkey, const uint64_t* __restrict__ totals,
+                        uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes, const uint64_t* __restrict__ counts,
+                        uint32_t* __restrict__ status, uint64_t i) {
+    const WalkItem it = walk_prepare(rec, n_rec, base_off, seq_idx, seq_endkey, totals, fasta, out, cap_bytes, counts, i);
+    walk_emit(ix, it, first_no, out, status);
+}
+
 // Work assignment inside a block.  A record costs one dependent jump-table load + two word pushes per 16 bases, and the
 // lengths of neighbouring records differ by an order of magnitude (150 bp reads at 1 %: 92, 58, a 1-base literal, ...), so
 // with record i on thread i every warp ran as long as its longest record (ncu r1 v12: 8.9 active threads per
@@ -293,25 +344,27 @@ __global__ void __launch_bounds__(kWalkThreads) walk_kernel(DevIndex ix, const u
                                                    uint64_t first_no, int fasta, uint8_t* __restrict__ out, uint64_t cap_bytes,
                                                    const uint64_t* __restrict__ counts, uint32_t* __restrict__ status) {
     const uint64_t i0 = (uint64_t)blockIdx.x * kWalkThreads;
+    const uint32_t tid = threadIdx.x;
+    // record i0 + tid on thread tid: coalesced loads of everything the walk needs
+    const WalkItem mine = walk_prepare(rec, n_rec, base_off, seq_idx, seq_endkey, totals, fasta, out, cap_bytes, counts, i0 + tid);
 #if NTC_WALK_SORT
     __shared__ uint32_t s_hist[kWalkBuckets];
-    __shared__ uint16_t s_perm[kWalkThreads];
-    const uint32_t tid = threadIdx.x;
+    __shared__ uint64_t s_w[kWalkThreads], s_end[kWalkThreads], s_sid[kWalkThreads];
+    __shared__ uint32_t s_L[kWalkThreads], s_flags[kWalkThreads];
     if (tid < kWalkBuckets) s_hist[tid] = 0;
     __syncthreads();
-    const uint64_t mine = i0 + tid;
-    const uint32_t bucket = kWalkBuckets - 1u - (mine < n_rec ? walk_cost_key(NTC_LDG(rec + mine)) : 0u);   // heaviest first
+    const uint32_t bucket = kWalkBuckets - 1u - ((mine.flags & 1u) ? walk_cost_key(mine.w) : 0u);   // heaviest first
     const uint32_t pos = atomicAdd(&s_hist[bucket], 1u);
     __syncthreads();
-    uint32_t start = 0;
-    for (uint32_t b = 0; b < bucket; b++) start += s_hist[b];
-    s_perm[start + pos] = (uint16_t)tid;
+    uint32_t slot = pos;
+    for (uint32_t b = 0; b < bucket; b++) slot += s_hist[b];
+    s_w[slot] = mine.w; s_end[slot] = mine.seg_end; s_sid[slot] = mine.sid; s_L[slot] = mine.L; s_flags[slot] = mine.flags;
     __syncthreads();
-    const uint64_t i = i0 + s_perm[tid];
+    const WalkItem it{s_w[tid], s_end[tid], s_sid[tid], s_L[tid], s_flags[tid]};
+    walk_emit(ix, it, first_no, out, status);
 #else
-    const uint64_t i = i0 + threadIdx.x;
+    walk_emit(ix, mine, first_no, out, status);
 #endif
-    walk_thread(ix, rec, n_rec, base_off, seq_idx, seq_endkey, totals, first_no, fasta, out, cap_bytes, counts, status, i);
 }
 
 }  // namespace ntc
