@@ -362,7 +362,7 @@ def test_device_resident_api_with_torch(small_cases):
     assert (d_soff.cpu().numpy().view(np.uint64) == off).all()
     want = helpers.fasta_text(reads, 99)
     d_text = torch.zeros(len(want) + 64, dtype=torch.uint8, device=dev)
-    for mis in (1, 3, 5, 6):                              # caller-misaligned output buffer
+    for mis in (1, 3, 5, 6, 8, 9, 12, 15):                # caller-misaligned output buffer (the writer pairs words into 16-byte stores)
         d_text.zero_()
         case.ctx.decode_device(d_rec.data_ptr(), n_rec, 99, True, d_text.data_ptr() + mis, len(want), 0, 0, d_cnt.data_ptr(), stream)
         case.ctx.status(stream)
