@@ -107,7 +107,23 @@ __global__ void __launch_bounds__(256) seq_layout_kernel(const uint64_t* __restr
 // 8-byte words so the interior of a segment is written with full u64 stores; only the two edges
 // of a segment (which share words with neighbouring segments / headers) use 4/2/1-byte stores.
 // (First version, ncu r1: 1.59 G single-byte stores made walk_kernel L1TEX-bound.)
-NTC_HD void store_lanes(uint8_t* word_addr, uint64_t w, uint32_t lo, uint32_t hi) {  // lanes [lo, hi) of the aligned word
+// NTC_WALK_STREAM: the text stores carry the evict_first L2 policy the encode scratch already uses (ncu r1 v15: plain
+// stores, lts hit rate 46 %, 4.9 GB of DRAM reads per launch for ~1 GB of compulsory ones -- the 1.6 GB output stream
+// was displacing the 80 MB jump table).  A/B in profiles/r2/ab_walk_stream.txt.
+#ifndef NTC_WALK_STREAM
+#define NTC_WALK_STREAM 1
+#endif
+NTC_HD void store_lanes(uint8_t* word_addr, uint64_t w, uint32_t lo, uint32_t hi, uint64_t pol) {  // lanes [lo, hi) of the aligned word
+#if NTC_WALK_STREAM
+    if (lo == 0 && hi == 8) { st8_stream((uint64_t*)word_addr, w, pol); return; }
+    uint32_t l = lo;
+    while (l < hi) {
+        if ((l & 3u) == 0 && l + 4 <= hi) { st4_stream(word_addr + l, (uint32_t)(w >> (8 * l)), pol); l += 4; }
+        else if ((l & 1u) == 0 && l + 2 <= hi) { st2_stream(word_addr + l, (uint16_t)(w >> (8 * l)), pol); l += 2; }
+        else { st1_stream(word_addr + l, (uint8_t)(w >> (8 * l)), pol); l += 1; }
+    }
+#else
+    (void)pol;
     if (lo == 0 && hi == 8) { *(uint64_t*)word_addr = w; return; }
     uint32_t l = lo;
     while (l < hi) {
@@ -115,6 +131,15 @@ NTC_HD void store_lanes(uint8_t* word_addr, uint64_t w, uint32_t lo, uint32_t hi
         else if ((l & 1u) == 0 && l + 2 <= hi) { *(uint16_t*)(word_addr + l) = (uint16_t)(w >> (8 * l)); l += 2; }
         else { word_addr[l] = (uint8_t)(w >> (8 * l)); l += 1; }
     }
+#endif
+}
+NTC_HD void store_word(uint8_t* addr, uint64_t w, uint64_t pol) {
+#if NTC_WALK_STREAM
+    st8_stream((uint64_t*)addr, w, pol);
+#else
+    (void)pol;
+    *(uint64_t*)addr = w;
+#endif
 }
 
 // Complete words leave in descending address order; the upper half of a 16-byte unit waits in `hold` for the lower
@@ -128,23 +153,26 @@ struct LeftWriter {
     uint64_t p;     // bytes [p, segment end) are done; pending bytes of the word holding p sit in acc
     uint64_t acc;   // lanes [p & 7, top) of the aligned word at p & ~7
     uint64_t hold;  // complete word at hold_pos (an upper half) waiting for its lower half
+    uint64_t pol;   // L2 policy of the text stores (evict_first)
     uint32_t top;
     bool have;
 
-    NTC_HD void init(uint8_t* base, uint64_t end) { out = base; p = end; acc = 0; hold = 0; have = false; top = (uint32_t)(end & 7); }
+    NTC_HD void init(uint8_t* base, uint64_t end, uint64_t policy) { out = base; p = end; acc = 0; hold = 0; have = false; top = (uint32_t)(end & 7); pol = policy; }
     // lanes [0, hi) of the aligned word at byte position pos (a multiple of 8)
     NTC_HD void put(uint64_t pos, uint64_t w, uint32_t hi) {
-        if (hi != 8) { store_lanes(out + pos, w, 0, hi); return; }      // right edge of the segment: nothing is held yet
+        if (hi != 8) { store_lanes(out + pos, w, 0, hi, pol); return; } // right edge of the segment: nothing is held yet
 #if !NTC_WALK_PAIR16
-        *(uint64_t*)(out + pos) = w;
+        store_word(out + pos, w, pol);
         return;
 #endif
         if (pos & 8) {
-            if (have) *(uint64_t*)(out + pos + 8) = hold;              // (not reached: words arrive 8 bytes apart)
+            if (have) store_word(out + pos + 8, hold, pol);            // (not reached: words arrive 8 bytes apart)
             hold = w;
             have = true;
         } else if (have) {
-#if defined(__CUDA_ARCH__)
+#if NTC_WALK_STREAM
+            st16_stream(out + pos, w, hold, pol);
+#elif defined(__CUDA_ARCH__)
             *(ulonglong2*)(out + pos) = make_ulonglong2(w, hold);
 #else
             *(uint64_t*)(out + pos) = w;
@@ -152,7 +180,7 @@ struct LeftWriter {
 #endif
             have = false;
         } else {
-            *(uint64_t*)(out + pos) = w;
+            store_word(out + pos, w, pol);
         }
     }
     // x = the 8 bytes for positions [p-8, p)
@@ -185,8 +213,8 @@ struct LeftWriter {
     // writes what is pending; the writer's bytes end at p
     NTC_HD void finish() {
         const uint32_t q = (uint32_t)(p & 7);
-        if (have) { *(uint64_t*)(out + ((p + 7) & ~7ull)) = hold; have = false; }   // the held word is the one right of p's word
-        if (q) store_lanes(out + (p & ~7ull), acc, q, top);
+        if (have) { store_word(out + ((p + 7) & ~7ull), hold, pol); have = false; }   // the held word is the one right of p's word
+        if (q) store_lanes(out + (p & ~7ull), acc, q, top, pol);
     }
 };
 
@@ -279,7 +307,7 @@ NTC_HD void walk_emit(const DevIndex& ix, const WalkItem& it, uint64_t first_no,
     // the output buffer may be misaligned by the caller: fold the misalignment into the position
     const uint64_t mis = (uint64_t)((uintptr_t)out & 15u);
     LeftWriter lw;
-    lw.init(out - mis, it.seg_end + mis);
+    lw.init(out - mis, it.seg_end + mis, ix.pol_stream);
 
     if (flag & 2u) {  // literal record (<= 32 bases), src/lib.rs:295-306
         uint64_t bits = L >= 32 ? (w & 0x00FFFFFFFFFFFFFFull) : (w & ((1ull << (2 * L)) - 1ull));   // 56 payload bits + zeros

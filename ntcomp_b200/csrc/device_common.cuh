@@ -189,6 +189,40 @@ NTC_HD void st8_stream(uint64_t* dst, uint64_t v, uint64_t pol) {
 #endif
 }
 
+// hinted stores of the widths the decode writer uses (text leaves once: evict_first keeps it from displacing the jump table)
+NTC_HD void st16_stream(void* dst, uint64_t lo, uint64_t hi, uint64_t pol) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.L2::cache_hint.v2.b64 [%0], {%1,%2}, %3;" ::"l"(dst), "l"(lo), "l"(hi), "l"(pol) : "memory");
+#else
+    (void)pol;
+    ((uint64_t*)dst)[0] = lo; ((uint64_t*)dst)[1] = hi;
+#endif
+}
+NTC_HD void st4_stream(void* dst, uint32_t v, uint64_t pol) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.L2::cache_hint.b32 [%0], %1, %2;" ::"l"(dst), "r"(v), "l"(pol) : "memory");
+#else
+    (void)pol;
+    *(uint32_t*)dst = v;
+#endif
+}
+NTC_HD void st2_stream(void* dst, uint16_t v, uint64_t pol) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.L2::cache_hint.b16 [%0], %1, %2;" ::"l"(dst), "h"(v), "l"(pol) : "memory");
+#else
+    (void)pol;
+    *(uint16_t*)dst = v;
+#endif
+}
+NTC_HD void st1_stream(void* dst, uint8_t v, uint64_t pol) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.L2::cache_hint.b8 [%0], %1, %2;" ::"l"(dst), "r"((uint32_t)v), "l"(pol) : "memory");
+#else
+    (void)pol;
+    *(uint8_t*)dst = v;
+#endif
+}
+
 // ASCII of a 2-bit code
 NTC_HD uint8_t code_ascii(uint32_t c) { return (uint8_t)(0x54474341u >> (8 * (c & 3u))); }
 
