@@ -130,6 +130,12 @@ bool code_column_host(const uint64_t* v, uint64_t n, int rice, std::vector<uint6
 bool decode_column_host(const uint64_t* words, uint64_t n_words, uint64_t n, int rice, uint64_t param, std::vector<uint64_t>* out) {
     BitCursor cur{words, n_words};
     out->clear();
+    // header fields come from the file: the same checks as ntc_block_read_gpu (api_columns.inc) before anything is sized by
+    // them.  Every code is at least one bit, so n values need n bits (minimal binary with upper bound 2 or 3 has 1-bit
+    // codes; a bound below 2 would mean 0-bit codes and `x - 1` underflowing at src/decode.rs:74); a Rice parameter above
+    // 63 cannot be a shift count.
+    if (n > n_words * 64) return false;
+    if (rice ? param > 63 : param < 2) return false;
     out->reserve(n);
     if (rice) {
         for (uint64_t i = 0; i < n; i++) {
@@ -139,7 +145,6 @@ bool decode_column_host(const uint64_t* words, uint64_t n_words, uint64_t n, int
             out->push_back((q << param) | rem);
         }
     } else {
-        if (param == 0) return false;
         unsigned l; uint64_t limit;
         minimal_binary_shape(param, &l, &limit);
         for (uint64_t i = 0; i < n; i++) {
@@ -314,21 +319,32 @@ extern "C" {
 
 uint64_t ntc_block_bound(uint64_t n_records) { return 4 * 32 + 4 * 64 + n_records * 20 + (n_records * 20) / 1000; }
 
+// No exception crosses the C ABI: allocation failures (a hostile header can announce gigabytes) and anything else
+// thrown below come back as a status code.
+#define NTC_ABI_GUARD_BEGIN try {
+#define NTC_ABI_GUARD_END                                                                                   \
+    } catch (const std::bad_alloc&) { set_error("out of memory"); return NTC_ERR_IO;                        \
+    } catch (const std::exception& e) { set_error(std::string("internal error: ") + e.what()); return NTC_ERR_IO; \
+    } catch (...) { set_error("internal error"); return NTC_ERR_IO; }
+
 int32_t ntc_column_code(const uint64_t* values, uint64_t n, int32_t rice, uint64_t* words, uint64_t cap, uint64_t* n_words,
                         uint64_t* param) {
     if ((n && !values) || !n_words || !param) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    NTC_ABI_GUARD_BEGIN
     std::vector<uint64_t> w;
     if (!code_column_host(values, n, rice, &w, param)) { set_error("empty column (minimal_binary_encode, src/encode.rs:80)"); return NTC_ERR_EMPTY_COLUMN; }
     *n_words = w.size();
     if (w.size() > cap) { set_error("words buffer too small"); return NTC_ERR_CAPACITY; }
     if (!w.empty()) memcpy(words, w.data(), w.size() * 8);
     return NTC_OK;
+    NTC_ABI_GUARD_END
 }
 
 int32_t ntc_block_write(const uint64_t* records, uint64_t n_records, uint64_t num_reads, uint8_t* out, uint64_t cap, uint64_t* n_bytes) {
     if (!records || !out || !n_bytes) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
     *n_bytes = 0;
     if (n_records == 0) { set_error("empty block (EncodeError, src/encode.rs:171)"); return NTC_ERR_EMPTY_READ; }
+    NTC_ABI_GUARD_BEGIN
     BlockColumns c;
     split_records(records, n_records, &c);
     const std::vector<uint64_t>* cols[4] = {&c.colex, &c.len, &c.flags, &c.literals};
@@ -350,6 +366,7 @@ int32_t ntc_block_write(const uint64_t* records, uint64_t n_records, uint64_t nu
     memcpy(out, sink.data(), sink.size());
     *n_bytes = sink.size();
     return NTC_OK;
+    NTC_ABI_GUARD_END
 }
 
 static int32_t block_read_impl(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records, uint64_t* consumed,
@@ -358,6 +375,7 @@ static int32_t block_read_impl(const uint8_t* data, uint64_t size, uint64_t* rec
     *n_records = 0;
     *consumed = 0;
     if (size < 32) return NTC_OK;                                                   // EOF: read_exact fails, src/lib.rs:327
+    NTC_ABI_GUARD_BEGIN
     BlockColumns c;
     std::vector<uint64_t>* cols[4] = {&c.colex, &c.len, &c.flags, &c.literals};
     const int rice[4] = {0, 1, 1, 0};
@@ -375,6 +393,7 @@ static int32_t block_read_impl(const uint8_t* data, uint64_t size, uint64_t* rec
     *n_records = rec.size();
     *consumed = pos;
     return NTC_OK;
+    NTC_ABI_GUARD_END
 }
 
 int32_t ntc_block_read(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records, uint64_t* consumed) {

@@ -107,11 +107,13 @@ __global__ void __launch_bounds__(256) seq_layout_kernel(const uint64_t* __restr
 // 8-byte words so the interior of a segment is written with full u64 stores; only the two edges
 // of a segment (which share words with neighbouring segments / headers) use 4/2/1-byte stores.
 // (First version, ncu r1: 1.59 G single-byte stores made walk_kernel L1TEX-bound.)
-// NTC_WALK_STREAM: the text stores carry the evict_first L2 policy the encode scratch already uses (ncu r1 v15: plain
-// stores, lts hit rate 46 %, 4.9 GB of DRAM reads per launch for ~1 GB of compulsory ones -- the 1.6 GB output stream
-// was displacing the 80 MB jump table).  A/B in profiles/r2/ab_walk_stream.txt.
+// NTC_WALK_STREAM=1: the text stores carry the evict_first L2 policy the encode scratch uses (ncu r1 v15: plain stores,
+// lts hit rate 46 %, 4.9 GB of DRAM reads per launch for ~1 GB of compulsory ones -- the 1.6 GB output stream displaces
+// the 80 MB jump table).  Measured on B200 it is SLOWER -- 2.22 vs 1.99 ms on C3, 2.98 vs 2.78 ms on the 12 Mbp index
+// (profiles/r2/ab_walk_stream.txt): a text sector is completed by several threads at different times (the edges of
+// neighbouring records), and a partially written evict_first sector leaves L2 before the rest arrives.  Off by default.
 #ifndef NTC_WALK_STREAM
-#define NTC_WALK_STREAM 1
+#define NTC_WALK_STREAM 0
 #endif
 NTC_HD void store_lanes(uint8_t* word_addr, uint64_t w, uint32_t lo, uint32_t hi, uint64_t pol) {  // lanes [lo, hi) of the aligned word
 #if NTC_WALK_STREAM

@@ -17,6 +17,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <exception>
 #include <functional>
 #include <memory>
 #include <mutex>
@@ -86,15 +87,24 @@ void parallel_for(uint64_t n, int n_threads, const std::function<void(uint64_t)>
     std::vector<std::thread> pool;
     std::mutex m;
     uint64_t next = 0;
+    std::exception_ptr failed;                       // an exception must not leave a std::thread (std::terminate)
     for (int w = 0; w < t; w++)
         pool.emplace_back([&] {
             for (;;) {
                 uint64_t i;
-                { std::lock_guard<std::mutex> lk(m); if (next >= n) return; i = next++; }
-                fn(i);
+                { std::lock_guard<std::mutex> lk(m); if (next >= n || failed) return; i = next++; }
+                try { fn(i); } catch (...) { std::lock_guard<std::mutex> lk(m); if (!failed) failed = std::current_exception(); }
             }
         });
     for (auto& th : pool) th.join();
+    if (failed) std::rethrow_exception(failed);
+}
+
+// body of a pipeline stage thread: whatever it throws (bad_alloc on a hostile header, ...) becomes a flag the
+// calling thread turns into NTC_ERR_IO once the stages are joined; on_fail unblocks the neighbours
+template <typename Body, typename OnFail>
+void stage_guard(bool* fatal, Body&& body, OnFail&& on_fail) {
+    try { body(); } catch (...) { *fatal = true; on_fail(); }
 }
 
 // ---- output sink: a file, or stdout for "-" -------------------------------------------------------
@@ -259,8 +269,9 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
     Channel<ReadBatch> parsed(2);
     Channel<BytesBatch> coded(2);
     double t_stage[4] = {0, 0, 0, 0};                                  // busy seconds: parse, GPU, block container, write
+    bool fatal = false;
     // stage 1: parse
-    std::thread t_read([&] {
+    std::thread t_read([&] { stage_guard(&fatal, [&] {
         bool eof = false;
         size_t reserve_bases = 0;
         while (!eof) {
@@ -288,11 +299,11 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
             if (b.offsets.size() > 1 || b.err) { if (!parsed.push(std::move(b))) return; }
         }
         parsed.finish();
-    });
+    }, [&] { parsed.finish(); }); });
     // stage 3: write in order
     int32_t w_rc = NTC_OK;
     std::string w_msg;
-    std::thread t_write([&] {
+    std::thread t_write([&] { stage_guard(&fatal, [&] {
         BytesBatch bb;
         while (coded.pop(&bb)) {
             if (bb.rc != NTC_OK) { w_rc = bb.rc; w_msg = bb.msg; coded.close(); return; }
@@ -303,12 +314,12 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
             }
             t_stage[3] += now_s() - t0;
         }
-    });
+    }, [&] { coded.close(); }); });
     // stage 3: the block container per 65,536-read block on the pool (its own thread, so the GPU works on the
     // next batch meanwhile)
     struct RecordBatch { std::unique_ptr<uint64_t[]> records; std::vector<uint64_t> rec_off; uint64_t n_reads = 0; };
     Channel<RecordBatch> encoded(2);
-    std::thread t_code([&] {
+    std::thread t_code([&] { stage_guard(&fatal, [&] {
         RecordBatch rb;
         while (encoded.pop(&rb)) {
             const uint64_t n = rb.n_reads, n_blocks = (n + kBlockReads - 1) / kBlockReads;
@@ -335,7 +346,7 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
             if (!coded.push(std::move(out))) { encoded.close(); return; }
         }
         coded.finish();
-    });
+    }, [&] { encoded.close(); coded.finish(); }); });
     // stage 2 (this thread): the hot path on the GPU
     int32_t rc = NTC_OK;
     std::string msg;
@@ -372,6 +383,7 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
     if (stats) memcpy(stats, st, sizeof(st));
     if (rc != NTC_OK) { set_error(msg); return rc; }
     if (w_rc != NTC_OK) { set_error(w_msg); return w_rc; }
+    if (fatal) { set_error("out of memory or internal error in a pipeline stage"); return NTC_ERR_IO; }
     return NTC_OK;
 }
 
@@ -395,8 +407,9 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
     struct RecBatch { std::vector<uint64_t> records; uint64_t n_blocks = 0; int32_t rc = NTC_OK; std::string msg; };
     Channel<RecBatch> unpacked(2);
     Channel<BytesBatch> texts(2);
+    bool fatal = false;
     // stage 1: frame the blocks of a group, then gunzip + decode + zip them on the pool
-    std::thread t_read([&] {
+    std::thread t_read([&] { stage_guard(&fatal, [&] {
         bool eof = false;
         while (!eof) {
             std::vector<std::vector<uint8_t>> raw;
@@ -410,10 +423,17 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
                     if (got != 32) { ok = false; break; }              // EOF (or a torn header) ends the stream, src/lib.rs:327
                     uint32_t block_size;
                     memcpy(&block_size, h, 4);
-                    size_t at = blk.size();
-                    blk.resize(at + 32 + block_size);
-                    memcpy(blk.data() + at, h, 32);
-                    if (fread(blk.data() + at + 32, 1, block_size, in) != block_size) { ok = false; break; }
+                    // block_size comes from the file: grow the buffer as bytes really arrive (a hostile header announcing
+                    // 4 GiB must not become a 4 GiB allocation)
+                    blk.insert(blk.end(), h, h + 32);
+                    uint64_t left = block_size;
+                    while (left && ok) {
+                        const size_t step = (size_t)std::min<uint64_t>(left, 16u << 20), at = blk.size();
+                        blk.resize(at + step);
+                        if (fread(blk.data() + at, 1, step, in) != step) ok = false;
+                        left -= step;
+                    }
+                    if (!ok) break;
                 }
                 if (!ok) { eof = true; break; }
                 payload += blk.size();
@@ -444,21 +464,26 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
             });
             for (size_t j = 0; j < raw.size(); j++) {
                 if (brc[j] != NTC_OK && rb.rc == NTC_OK) { rb.rc = brc[j]; rb.msg = bmsg[j]; }
-                rb.records.insert(rb.records.end(), recs[j].begin(), recs[j].end());
+                // the reference decodes every block by itself (decode_block -> decode_sequence, src/lib.rs:363-365): records
+                // in front of a block's first `first` flag belong to no sequence and are dropped (src/lib.rs:308-317) --
+                // they must not be glued to the previous block's last sequence when blocks are concatenated here
+                size_t skip = 0;
+                while (skip < recs[j].size() && ((recs[j][skip] >> 56) & 1u) == 0) skip++;
+                rb.records.insert(rb.records.end(), recs[j].begin() + skip, recs[j].end());
                 st[3] += raw[j].size();
             }
             if (!unpacked.push(std::move(rb))) return;
         }
         unpacked.finish();
-    });
+    }, [&] { unpacked.finish(); }); });
     int32_t w_rc = NTC_OK;
     std::string w_msg;
-    std::thread t_write([&] {
+    std::thread t_write([&] { stage_guard(&fatal, [&] {
         BytesBatch bb;
         while (texts.pop(&bb))
             for (auto& p : bb.parts)
                 if (!sink.write(p.data(), p.size())) { w_rc = NTC_ERR_IO; w_msg = "write failed"; texts.close(); return; }
-    });
+    }, [&] { texts.close(); }); });
     // stage 2 (this thread): decode_sequence + FASTA text on the GPU
     int32_t rc = NTC_OK;
     std::string msg;
@@ -490,6 +515,7 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
     if (stats) memcpy(stats, st, sizeof(st));
     if (rc != NTC_OK) { set_error(msg); return rc; }
     if (w_rc != NTC_OK) { set_error(w_msg); return w_rc; }
+    if (fatal) { set_error("out of memory or internal error in a pipeline stage"); return NTC_ERR_IO; }
     return NTC_OK;
 }
 
