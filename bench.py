@@ -263,7 +263,7 @@ def free_host_cache(torch):
         pass
 
 
-def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap=None, want_l2=True):
+def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap=None, want_l2=True, want_columns=False):
     """One config on this rank's shard [lo, lo + n_reads): device-resident timing (CUDA events on the launching
     stream, barrier + synchronize on both sides, max over ranks) and the end-to-end leg through the host-buffer C ABI."""
     torch = R.torch
@@ -419,10 +419,55 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
                "pcie_floor_ms_per_step": (h2d / pcie[0] + d2h / pcie[1]) / 1e6 if pcie[0] else None}
         out["h_sample"] = (h_bases, h_off)
         del h_rec, h_text
+        if want_columns:
+            out["columns"] = measure_columns(ctx, h_bases, h_off, ne, read_len, lo, load_peaks()[0])
     out["e2e"] = e2e
     out["ctx"], out["index"], out["d_rec"], out["d_roff"] = ctx, index, d_rec, d_roff
     del d_out, d_g
     return out
+
+
+def measure_columns(ctx, h_bases, h_off, n_reads, read_len, lo, hbm_peak):
+    """Row f1: the fused column codec (ntc_encode_columns / ntc_decode_columns_fasta) on the first blocks of the batch.
+    Kernel time = CUDA events around the column kernels on the launching stream (classes column_encode / column_decode)."""
+    n = min(n_reads, 16 * BLOCK_READS)
+    if n < 1:
+        return None
+    bases = h_bases[: n * read_len].numpy()
+    off = h_off[: n + 1].numpy().astype(np.uint64)
+    blocks, words, n_rec = ctx.encode_columns(bases, off, BLOCK_READS)          # warm-up (workspaces, pinned buffers)
+    kept = [b for b in blocks if b.status == 0]
+    ctx.decode_columns_fasta(kept, words, lo + 1, True)
+    ctx.set_profiling(True)
+    ctx.kernel_times(reset=True)
+    reps = 3
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        blocks, words, n_rec = ctx.encode_columns(bases, off, BLOCK_READS)
+    t1 = time.perf_counter()
+    for _ in range(reps):
+        text, n_seqs, n_dec = ctx.decode_columns_fasta(kept, words, lo + 1, True)
+    t2 = time.perf_counter()
+    kt = ctx.kernel_times(reset=True)
+    ctx.set_profiling(False)
+    enc_ms, dec_ms = kt["column_encode"][0] / reps, kt["column_decode"][0] / reps
+    coded = 8 * len(words)
+    first = (b">seq.%d\n" % (lo + 1)) + bytes(bases[:read_len]) + b"\n"
+    if n_seqs != sum(int(b.num_reads) for b in kept) or text[: len(first)] != first:
+        raise SystemExit("bench.py: fused column decode does not reproduce the reads")
+    enc_bytes, dec_bytes = 8 * n_rec + coded, coded + 8 * n_dec
+    return {"reads": n, "blocks": len(blocks), "blocks_dropped_q4": len(blocks) - len(kept), "records": n_rec,
+            "d2h_bytes_per_record_before": 8.0, "d2h_bytes_per_record_after": coded / n_rec,
+            "encode": {"kernel_ms": enc_ms, "launches": kt["column_encode"][1] // reps, "records_per_s": n_rec / (enc_ms * 1e-3),
+                       "algorithmic_bytes": enc_bytes, "hbm_achieved_gbs": enc_bytes / (enc_ms * 1e-3) / 1e9,
+                       "hbm_frac": enc_bytes / (enc_ms * 1e-3) / 1e9 / hbm_peak,
+                       "call_ms_with_encode_and_copies": 1e3 * (t1 - t0) / reps},
+            "decode": {"kernel_ms": dec_ms, "launches": kt["column_decode"][1] // reps, "records_per_s": n_dec / (dec_ms * 1e-3),
+                       "algorithmic_bytes": dec_bytes, "hbm_achieved_gbs": dec_bytes / (dec_ms * 1e-3) / 1e9,
+                       "hbm_frac": dec_bytes / (dec_ms * 1e-3) / 1e9 / hbm_peak,
+                       "call_ms_with_walk_and_copies": 1e3 * (t2 - t1) / reps},
+            "note": "algorithmic bytes = 8 B per record in + coded words out (encode), the reverse for decode; batches of a few "
+                    "blocks are launch / latency bound, not HBM bound"}
 
 
 def l2_roofline(m, l2_gsect):
@@ -490,7 +535,7 @@ def main():
     # ---- this rank's shard: reads [lo, hi) of the global numbering, boundaries on 65,536 ----
     lo, hi = shard_bounds(n_reads * world, world)[rank] if (n_reads % BLOCK_READS == 0) else (rank * n_reads, (rank + 1) * n_reads)
     assert hi - lo == n_reads
-    m = measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=not args.no_e2e)
+    m = measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=not args.no_e2e, want_columns=True)
     n_bases, n_rec, ktimes, t_total = m["n_bases"], m["n_rec"], m["ktimes"], m["t_total"]
     l2 = m["l2"]
 
@@ -588,7 +633,7 @@ def main():
         "e2e": m["e2e"],
         "host_binding": ("NUMA-local CPUs of each GPU (%d CPUs on rank 0)" % len(cpus)) if cpus else "none",
         "gpu_launches": m["gpu_launches"], "roofline": roofline, "cpu_baseline": cpu, "setup_s": m["setup_s"],
-        "index_bytes": m["index_bytes"],
+        "index_bytes": m["index_bytes"], "columns": m.get("columns"),
     }
     line.update(extras)
     emit(line)

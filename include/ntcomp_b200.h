@@ -135,8 +135,9 @@ int32_t ntc_block_read(const uint8_t* data, uint64_t size, uint64_t* records, ui
 #define NTC_BLOCK_FULL_LAST_LITERAL_WORD 1
 int32_t ntc_block_read_ex(const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap, uint64_t* n_records,
                           uint64_t* consumed, int32_t flags);
-/* write_block_to with the column split and the Rice / minimal-binary bit packing on the GPU (prefix sum
- * of code lengths + atomic OR into the MSB-first stream); gzip on the host.  Same bytes as ntc_block_write. */
+/* write_block_to over HOST records with the column split and the Rice / minimal-binary bit packing on the GPU (values
+ * scattered to prefix-summed ranks, one thread per output word gathers and assembles it: no per-value atomics); gzip on
+ * the host.  Same bytes as ntc_block_write. */
 int32_t ntc_block_write_gpu(ntc_ctx* ctx, const uint64_t* records, uint64_t n_records, uint64_t num_reads, uint8_t* out,
                             uint64_t cap, uint64_t* n_bytes);
 /* decode_block up to decode_sequence (src/lib.rs:320-363) with the Rice / minimal-binary decoders (src/decode.rs:51-77)
@@ -145,6 +146,43 @@ int32_t ntc_block_write_gpu(ntc_ctx* ctx, const uint64_t* records, uint64_t n_re
  * errors as ntc_block_read_ex. */
 int32_t ntc_block_read_gpu(ntc_ctx* ctx, const uint8_t* data, uint64_t size, uint64_t* records, uint64_t cap,
                            uint64_t* n_records, uint64_t* consumed, int32_t flags);
+
+/* ---- fused, device-resident column codec ("next" row f1 as SURVEY 8(f)1 defines it) ------------------------
+ * The u64 records never leave HBM: the encoder's output goes straight into the column split and the integer coders
+ * (src/encode.rs:59-94,168-229), and only the coded word streams + their parameters cross PCIe; the decoder takes
+ * coded word streams and hands back FASTA text.  gzip / gunzip and the 32-byte headers stay on the host
+ * (ntc_block_assemble / ntc_block_disassemble = the rest of write_block_to / decode_block). */
+typedef struct ntc_coded_column {
+    uint64_t n_values;     /* BlockHeader.num_u64, src/lib.rs:41 */
+    uint64_t n_words;      /* BlockHeader.encoded_size: big-endian u64 words of the MSB-first code stream */
+    uint64_t param;        /* BlockHeader.rice_param: Rice log2(b) or minimal-binary upper bound, src/encode.rs:117 */
+    uint64_t word_offset;  /* first word of this column in the call's word array */
+} ntc_coded_column;
+typedef struct ntc_coded_block {
+    uint64_t n_records;    /* records of the block (= n_values of the flags column) */
+    uint64_t num_reads;    /* BlockHeader.num_records: the block-size argument of write_block_to (Q6) */
+    int32_t status;        /* NTC_OK, or NTC_ERR_EMPTY_COLUMN: the reference drops this block (Q4) */
+    int32_t reserved;
+    ntc_coded_column col[4]; /* colex (minimal binary), len (Rice), flags (Rice), literal words (minimal binary): src/lib.rs:242-245 */
+} ntc_coded_block;
+
+/* flat_map(encode_dictionary . encode_sequence) over the reads + the column codec per block of block_reads reads
+ * (65,536 at src/main.rs:152).  HOST reads in; per block the descriptor, and *words -> all coded words of the call in a
+ * pinned buffer owned by ctx (valid until the next-but-one call on ctx). */
+int32_t ntc_encode_columns(ntc_ctx* ctx, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads, uint64_t block_reads,
+                           ntc_coded_block* blocks, uint64_t cap_blocks, uint64_t* n_blocks, const uint64_t** words,
+                           uint64_t* n_words, uint64_t* n_records);
+/* four gzip members + 32-byte headers of one block (src/lib.rs:242-250, src/encode.rs:96-127); host only */
+int32_t ntc_block_assemble(const ntc_coded_block* blk, const uint64_t* words, uint8_t* out, uint64_t cap, uint64_t* n_bytes);
+/* four headers + gunzip of one block (src/lib.rs:326-355, src/decode.rs:79-91); host only.  *consumed == 0 at EOF. */
+int32_t ntc_block_disassemble(const uint8_t* data, uint64_t size, ntc_coded_block* blk, uint64_t* words, uint64_t cap_words,
+                              uint64_t* n_words, uint64_t* consumed);
+/* decode_block (minus gunzip) + decode_sequence + the writer loop of src/main.rs:201-209 for a batch of blocks.  Every block
+ * is decoded by itself as the reference does; numbering runs on from first_seq_number.  *text -> pinned buffer owned by
+ * ctx (valid until the next-but-one call).  flags: NTC_BLOCK_FULL_LAST_LITERAL_WORD. */
+int32_t ntc_decode_columns_fasta(ntc_ctx* ctx, const ntc_coded_block* blocks, uint64_t n_blocks, const uint64_t* words, uint64_t n_words,
+                                 uint64_t first_seq_number, int32_t flags, const uint8_t** text, uint64_t* n_bytes, uint64_t* n_seqs,
+                                 uint64_t* n_records);
 /* one column through rice_encode / minimal_binary_encode (src/encode.rs:59-94): rice != 0 selects Rice */
 int32_t ntc_column_code(const uint64_t* values, uint64_t n, int32_t rice, uint64_t* words, uint64_t cap, uint64_t* n_words,
                         uint64_t* param);
@@ -181,10 +219,10 @@ uint64_t ntc_ctx_launch_count(const ntc_ctx* ctx);
 
 /* measurement support (bench.py): per-kernel-class CUDA-event timing on the launching stream.
  * classes: 0 pack2bit, 1 matching statistics, 2 record-offset scan, 3 emit, 4 decode scan,
- * 5 sequence offsets, 6 walk, 7 misc.  ntc_ctx_kernel_times synchronises the device. */
-#define NTC_KERNEL_CLASSES 8
+ * 5 sequence offsets, 6 walk, 7 misc, 8 column encode, 9 column decode.  ntc_ctx_kernel_times synchronises the device. */
+#define NTC_KERNEL_CLASSES 10
 int32_t ntc_ctx_set_profiling(ntc_ctx* ctx, int32_t on);
-int32_t ntc_ctx_kernel_times(ntc_ctx* ctx, double* ms /*[8]*/, uint64_t* launches /*[8]*/, int32_t reset);
+int32_t ntc_ctx_kernel_times(ntc_ctx* ctx, double* ms /*[NTC_KERNEL_CLASSES]*/, uint64_t* launches /*[NTC_KERNEL_CLASSES]*/, int32_t reset);
 /* L2 random 32-byte-sector micro-benchmark: G sectors/s from a buffer of the given size */
 int32_t ntc_l2_random_bench(ntc_ctx* ctx, uint64_t buffer_bytes, uint32_t loads_per_thread, int32_t dependent,
                             uint32_t n_blocks, double* gsectors_per_s);

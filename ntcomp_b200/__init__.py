@@ -4,5 +4,6 @@ Only what the path needs: `csrc/` (CUDA kernels + the C ABI of include/ntcomp_b2
 loader (`_lib`), the host-side mirror of the reference interface (`api`), the synthetic inputs of
 SURVEY §8d (`synth`) and read sharding across GPUs (`sharding`).
 """
-from .api import Context, EncodeError, Index, block_read, block_write, concat_reads, decode_sequence, encode_dictionary, encode_sequence  # noqa: F401
+from .api import (CodedBlock, CodedColumn, Context, EncodeError, Index, block_assemble, block_disassemble, block_read, block_write,  # noqa: F401
+                  concat_reads, decode_sequence, encode_dictionary, encode_sequence)
 from ._lib import NtcError  # noqa: F401

@@ -49,6 +49,10 @@ SIGNATURES = {
     "ntc_block_read_gpu": (_i32, [_vp, _vp, _u64, _vp, _u64, _vp, _vp, _i32]),
     "ntc_block_write_gpu": (_i32, [_vp, _vp, _u64, _u64, _vp, _u64, _vp]),
     "ntc_column_code": (_i32, [_vp, _u64, _i32, _vp, _u64, _vp, _vp]),
+    "ntc_encode_columns": (_i32, [_vp, _vp, _vp, _u64, _u64, _vp, _u64, _vp, _vp, _vp, _vp]),
+    "ntc_block_assemble": (_i32, [_vp, _vp, _vp, _u64, _vp]),
+    "ntc_block_disassemble": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp]),
+    "ntc_decode_columns_fasta": (_i32, [_vp, _vp, _u64, _vp, _u64, _u64, _i32, _vp, _vp, _vp, _vp]),
     "ntc_encode_device": (_i32, [_vp, _vp, _vp, _u64, _u64, _vp, _u64, _vp, _vp, _vp]),
     "ntc_decode_device": (_i32, [_vp, _vp, _u64, _u64, _i32, _vp, _u64, _vp, _u64, _vp, _vp]),
     "ntc_ctx_status": (_i32, [_vp, _vp]),

@@ -19,6 +19,16 @@ from . import _lib
 from ._lib import NtcError, check
 
 
+class CodedColumn(C.Structure):
+    """ntc_coded_column (include/ntcomp_b200.h)"""
+    _fields_ = [("n_values", C.c_uint64), ("n_words", C.c_uint64), ("param", C.c_uint64), ("word_offset", C.c_uint64)]
+
+
+class CodedBlock(C.Structure):
+    """ntc_coded_block: one 65,536-read block as four coded columns (write_block_to minus gzip, src/lib.rs:232-252)"""
+    _fields_ = [("n_records", C.c_uint64), ("num_reads", C.c_uint64), ("status", C.c_int32), ("reserved", C.c_int32), ("col", CodedColumn * 4)]
+
+
 class EncodeError(ValueError):
     """src/encode.rs:38-47: 'invalid input to encode'."""
 
@@ -149,7 +159,7 @@ class Context:
         _lib.lib().ntc_ctx_index_bytes(self._h, _ptr(out))
         return {"rank": int(out[0]), "lcs": int(out[1]), "jump": int(out[2])}
 
-    KERNEL_CLASSES = ["pack2bit", "ms", "scan", "emit", "decode_scan", "seq_offsets", "walk", "misc"]
+    KERNEL_CLASSES = ["pack2bit", "ms", "scan", "emit", "decode_scan", "seq_offsets", "walk", "misc", "column_encode", "column_decode"]
 
     def set_tile_len(self, tile_len=0):
         """matching-statistics tile length (0 = automatic); results do not depend on it"""
@@ -172,8 +182,8 @@ class Context:
 
     def kernel_times(self, reset=True):
         """{class: (ms, launches)} from CUDA events on the launching stream (synchronises)"""
-        ms = np.zeros(8, dtype=np.float64)
-        ln = np.zeros(8, dtype=np.uint64)
+        ms = np.zeros(len(self.KERNEL_CLASSES), dtype=np.float64)
+        ln = np.zeros(len(self.KERNEL_CLASSES), dtype=np.uint64)
         check(_lib.lib().ntc_ctx_kernel_times(self._h, _ptr(ms), _ptr(ln), int(reset)))
         return {n: (float(ms[i]), int(ln[i])) for i, n in enumerate(self.KERNEL_CLASSES)}
 
@@ -251,6 +261,33 @@ class Context:
         check(_lib.lib().ntc_matching_statistics(self._h, _ptr(bases), _ptr(offsets), len(offsets) - 1, _ptr(d), _ptr(s)))
         return d[:nb], s[:nb]
 
+    # ---- fused column codec (records stay in HBM; row f1) ----
+    def encode_columns(self, bases, offsets, block_reads=65536):
+        """encode + column codec per block of block_reads reads: returns (blocks: CodedBlock array, words uint64[] copy, n_records)"""
+        bases = _u8(bases)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n = len(offsets) - 1
+        cap = max((n + block_reads - 1) // block_reads, 1)
+        blocks = (CodedBlock * cap)()
+        nb, nw, nr = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        wp = C.c_void_p()
+        check(_lib.lib().ntc_encode_columns(self._h, _ptr(bases), _ptr(offsets), n, block_reads, C.cast(blocks, C.c_void_p), cap, C.byref(nb),
+                                            C.byref(wp), C.byref(nw), C.byref(nr)))
+        words = np.ctypeslib.as_array(C.cast(wp, C.POINTER(C.c_uint64)), shape=(nw.value,)).copy() if nw.value else np.zeros(0, dtype=np.uint64)
+        return [blocks[i] for i in range(nb.value)], words, nr.value
+
+    def decode_columns_fasta(self, blocks, words, first_seq_number=1, full_last_literal_word=False):
+        """coded columns of a batch of blocks -> FASTA text (decode_block minus gunzip + decode_sequence + writer loop)"""
+        arr = (CodedBlock * max(len(blocks), 1))(*blocks)
+        words = np.ascontiguousarray(words, dtype=np.uint64)
+        tp = C.c_void_p()
+        nb, ns, nr = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        check(_lib.lib().ntc_decode_columns_fasta(self._h, C.cast(arr, C.c_void_p), len(blocks), _ptr(words) if len(words) else None, len(words),
+                                                  first_seq_number, 1 if full_last_literal_word else 0, C.byref(tp), C.byref(nb), C.byref(ns),
+                                                  C.byref(nr)))
+        text = C.string_at(tp, nb.value) if nb.value else b""
+        return text, ns.value, nr.value
+
     # ---- device-resident API (raw device pointers as ints, e.g. torch.Tensor.data_ptr()) ----
     def encode_device(self, d_bases, d_offsets, n_reads, n_bases, d_records, cap, d_rec_offsets, d_counts, stream=0):
         check(_lib.lib().ntc_encode_device(self._h, d_bases, d_offsets, n_reads, n_bases, d_records, cap, d_rec_offsets, d_counts, stream))
@@ -320,3 +357,33 @@ def block_read(data, full_last_literal_word=False):
     check(_lib.lib().ntc_block_read_ex(_ptr(buf) if len(buf) else None, len(buf), _ptr(rec), cap, C.byref(n), C.byref(used),
                                        1 if full_last_literal_word else 0))
     return rec[: n.value].copy(), used.value
+
+
+def block_assemble(block, words):
+    """the host remainder of write_block_to: four gzip members + 32-byte headers of one CodedBlock"""
+    words = np.ascontiguousarray(words, dtype=np.uint64)
+    n_w = sum(int(c.n_words) for c in block.col)
+    cap = 4 * 32 + 4 * 64 + n_w * 9 + 1024
+    out = np.zeros(cap, dtype=np.uint8)
+    nb = C.c_uint64(0)
+    check(_lib.lib().ntc_block_assemble(C.byref(block), _ptr(words) if len(words) else None, _ptr(out), cap, C.byref(nb)))
+    return out[: nb.value].tobytes()
+
+
+def block_disassemble(data, offset=0):
+    """the host head of decode_block: (CodedBlock, words, bytes consumed); consumed == 0 at EOF"""
+    buf = np.frombuffer(data, dtype=np.uint8)[offset:]
+    buf = np.ascontiguousarray(buf)
+    cap = 0
+    pos = 0
+    for q in range(4):                       # encoded_size of the four headers
+        if pos + 32 > len(buf):
+            break
+        bs, _, _, es = (int(x) for x in np.frombuffer(buf[pos: pos + 16].tobytes(), dtype=np.uint32))
+        cap += es
+        pos += 32 + bs
+    words = np.zeros(cap + 8, dtype=np.uint64)
+    blk = CodedBlock()
+    nw, used = C.c_uint64(0), C.c_uint64(0)
+    check(_lib.lib().ntc_block_disassemble(_ptr(buf) if len(buf) else None, len(buf), C.byref(blk), _ptr(words), len(words), C.byref(nw), C.byref(used)))
+    return blk, words[: nw.value].copy(), used.value

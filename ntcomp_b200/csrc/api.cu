@@ -10,6 +10,7 @@
 #include "../../include/ntcomp_b200.h"
 #include "column_decode_kernels.cuh"
 #include "column_kernels.cuh"
+#include "column_plan.h"
 #include "container.h"
 #include "ctx.h"
 #include "decode_kernels.cuh"
@@ -257,7 +258,6 @@ int32_t read_status(ntc_ctx* ctx, cudaStream_t st) {
 }  // namespace
 
 void free_column_work(ntc_ctx* ctx);
-void free_column_decode_work(ntc_ctx* ctx);
 
 extern "C" {
 
@@ -374,7 +374,6 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
         for (DevBuf* b : lb) release(b);
     }
     free_column_work(ctx);
-    free_column_decode_work(ctx);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
     for (auto ev : ctx->event_pool) cudaEventDestroy(ev);
     cudaFree(ctx->d_rank); cudaFree(ctx->d_lcs); cudaFree(ctx->d_jump); cudaFree(ctx->d_pfx);

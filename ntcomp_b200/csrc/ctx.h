@@ -13,7 +13,7 @@ namespace ntc {
 void set_error(const std::string& msg);
 
 // kernel classes for launch accounting / profiling
-enum KernelClass { KC_PACK = 0, KC_MS, KC_SCAN, KC_EMIT, KC_DSCAN, KC_SEQ, KC_WALK, KC_MISC, KC_COUNT };
+enum KernelClass { KC_PACK = 0, KC_MS, KC_SCAN, KC_EMIT, KC_DSCAN, KC_SEQ, KC_WALK, KC_MISC, KC_COLENC, KC_COLDEC, KC_COUNT };
 
 struct DevBuf {
     void* p = nullptr;
@@ -55,8 +55,7 @@ struct ntc_ctx {
     ntc::Lane lanes[2];             // lanes[0] also serves the device-resident API (on the caller's stream)
     uint64_t max_chunk_records = 4ull << 20;  // host-buffer decode: records per chunk (NTC_MAX_CHUNK_RECORDS overrides)
     cudaStream_t stream = nullptr;  // == lanes[0].stream
-    void* colwork = nullptr;        // workspaces of the GPU column codec (api_columns.inc)
-    void* coldecwork = nullptr;     // ... and of its inverse
+    void* colwork = nullptr;        // workspaces + pinned landing buffers of the GPU column codec, both directions (api_columns.inc)
 
     // optional per-kernel-class timing with CUDA events on the launching stream (bench.py roofline)
     bool profiling = false;

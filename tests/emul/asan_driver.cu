@@ -17,7 +17,10 @@ uint32_t emul_encode(void* ep, const uint8_t* bases, const uint64_t* offsets, ui
                      uint64_t* n_records, uint64_t* rec_offsets);
 uint32_t emul_decode(void* ep, const uint64_t* rec, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* out, uint64_t cap,
                      uint64_t* seq_offsets, uint64_t cap_seqs, uint64_t* counts);
-int emul_block_columns(const uint64_t* rec, uint64_t n, uint64_t* words, uint64_t cap, uint64_t* n_words, uint64_t* params);
+int emul_batch_columns(const uint64_t* rec, const uint64_t* blk_rec_in, uint32_t n_blocks, uint64_t* words, uint64_t cap, uint64_t* seg_out,
+                       int32_t* status_out, uint64_t* total_out);
+int emul_columns_decode(const uint64_t* cols_in, uint32_t n_blocks, const uint64_t* words_be, uint64_t n_words, int full_last_word, int trim,
+                        uint64_t* rec, uint64_t cap, uint64_t* n_rec_out, uint32_t* detail);
 }
 
 int main() {
@@ -62,8 +65,22 @@ int main() {
             if (emul_decode(e, rec.data(), n_rec, first_no, 1, text.data(), fbytes, nullptr, 0, counts)) return 7;
             if (counts[1] != fbytes) return 8;
         }
-        std::vector<uint64_t> words(4 * n_rec + 64), nw(4), params(4);
-        emul_block_columns(rec.data(), n_rec, words.data(), words.size(), nw.data(), params.data());
+        // column codec, both directions, over a batch of three blocks cut at read boundaries
+        const uint64_t cut[4] = {0, roff[n_reads / 3], roff[2 * n_reads / 3], n_rec};
+        std::vector<uint64_t> words(4 * n_rec + 64), seg(48), cols(48);
+        int32_t status[3];
+        uint64_t total = 0;
+        if (emul_batch_columns(rec.data(), cut, 3, words.data(), words.size(), seg.data(), status, &total)) return 9;
+        words.resize(total);                                          // exact size again
+        bool all_ok = true;
+        for (int b = 0; b < 3; b++) all_ok = all_ok && status[b] == 0;
+        if (all_ok) {
+            std::vector<uint64_t> back(n_rec);
+            uint64_t n_back = 0;
+            uint32_t detail = 0;
+            int rc = emul_columns_decode(seg.data(), 3, words.data(), total, 1, 0, back.data(), n_rec, &n_back, &detail);
+            if (rc || n_back != n_rec || memcmp(back.data(), rec.data(), n_rec * 8)) { fprintf(stderr, "column round trip mismatch rc=%d\n", rc); return 10; }
+        }
         emul_index_free(e);
         ntc_index_free(idx);
     }

@@ -8,6 +8,7 @@
 
 #include "../../ntcomp_b200/csrc/column_decode_kernels.cuh"
 #include "../../ntcomp_b200/csrc/column_kernels.cuh"
+#include "../../ntcomp_b200/csrc/column_plan.h"
 #include "../../ntcomp_b200/csrc/container.h"
 #include "../../ntcomp_b200/csrc/decode_kernels.cuh"
 #include "../../ntcomp_b200/csrc/encode_kernels.cuh"
@@ -133,75 +134,127 @@ uint32_t emul_decode(void* ep, const uint64_t* rec, uint64_t n_rec, uint64_t fir
     return status;
 }
 
-// GPU column codec bodies (column_kernels.cuh) on the CPU: returns the four coded columns back to back
-// in `words` (sizes in n_words[4], parameters in params[4]); -1 when a column is empty (Q4).
-int emul_block_columns(const uint64_t* rec, uint64_t n, uint64_t* words, uint64_t cap, uint64_t* n_words, uint64_t* params) {
-    std::vector<uint64_t> ref_idx(n + 1), lit_off(n + 1), colex(n), len(n), flags(n);
-    std::vector<unsigned long long> lits(n * 32 / 31 + 2, 0), red(3, 0);
+// GPU column codec bodies (column_kernels.cuh) on the CPU, with the host planning of column_plan.h: the records of a
+// batch cut into blocks at blk_rec[0..n_blocks] -> coded words of all (block, column) segments back to back in `words`;
+// seg_out[4 * (4 b + q) ..] = n_values, n_words, param, word_base; status_out[b] as ntc_coded_block::status.
+// Returns 0, -2 when `words` is too small.
+int emul_batch_columns(const uint64_t* rec, const uint64_t* blk_rec_in, uint32_t n_blocks, uint64_t* words, uint64_t cap, uint64_t* seg_out,
+                       int32_t* status_out, uint64_t* total_out) {
+    std::vector<uint64_t> blk_rec(blk_rec_in, blk_rec_in + n_blocks + 1);
+    const uint64_t n = blk_rec[n_blocks];
+    std::vector<uint64_t> ref_idx(n + 1), lit_off(n + 1);
+    std::vector<uint32_t> colex(n + 1), len(n + 1);
+    std::vector<uint8_t> flags(n + 1);
+    std::vector<uint64_t> lits(n * 32 / 31 + n_blocks + 2, 0);
     SplitLoad load{rec};
     uint64_t a = 0, b = 0;
     for (uint64_t i = 0; i < n; i++) { ref_idx[i] = a; lit_off[i] = b; Pair64 p = load(i); a += p.a; b += p.b; }
-    for (uint64_t i = 0; i < n; i++) split_thread(rec, n, ref_idx.data(), lit_off.data(), colex.data(), len.data(), flags.data(), lits.data(), red.data(), i);
-    const uint64_t n_ref = a, n_lw = (b + 30) / 31;
-    if (n_ref == 0 || n_lw == 0) return -1;
-    uint64_t max_lit = 0;
-    for (uint64_t i = 0; i < n_lw; i++) max_lit = std::max<uint64_t>(max_lit, lits[i]);
-    const uint64_t* vals[4] = {colex.data(), len.data(), flags.data(), (const uint64_t*)lits.data()};
-    const uint64_t cnt[4] = {n_ref, n_ref, n, n_lw};
-    CodeParams cp[4];
-    unsigned l; uint64_t limit;
-    minimal_binary_shape(red[0] + 2, &l, &limit); cp[0] = CodeParams{0, 0, l, limit}; params[0] = red[0] + 2;
-    params[1] = rice_parameter(n_ref, red[1]); cp[1] = CodeParams{1, (uint32_t)params[1], 0, 0};
-    params[2] = rice_parameter(n, red[2]); cp[2] = CodeParams{1, (uint32_t)params[2], 0, 0};
-    minimal_binary_shape(max_lit + 2, &l, &limit); cp[3] = CodeParams{0, 0, l, limit}; params[3] = max_lit + 2;
-    uint64_t pos = 0;
-    for (int q = 0; q < 4; q++) {
-        std::vector<uint64_t> off(cnt[q] + 1);
-        uint64_t bits = 0;
-        for (uint64_t i = 0; i < cnt[q]; i++) { off[i] = bits; bits += code_bits(cp[q], vals[q][i]); }
-        std::vector<unsigned long long> w((bits + 63) / 64 + 2, 0);
-        for (uint64_t i = 0; i < cnt[q]; i++) pack_thread(cp[q], vals[q], cnt[q], off.data(), w.data(), i);
-        n_words[q] = (bits + 63) / 64;
-        if (pos + n_words[q] > cap) return -2;
-        for (uint64_t i = 0; i < n_words[q]; i++) words[pos + i] = __builtin_bswap64(w[i]);
-        pos += n_words[q];
+    ref_idx[n] = a; lit_off[n] = b;
+    ColArrays arr{colex.data(), len.data(), flags.data(), lits.data()};
+    std::vector<BlkStats> stats(n_blocks, BlkStats{0, 0, 0, 0, 0, 0, 0, 0});
+    uint64_t lw = 0;
+    for (uint32_t k = 0; k < n_blocks; k++) {                          // split_kernel + blk_stats_kernel + lit_pack_kernel
+        const uint64_t rs = blk_rec[k], re = blk_rec[k + 1];
+        for (uint64_t i = re; i-- > rs;) {
+            SplitContrib c = split_thread(rec, ref_idx.data(), arr, i);
+            stats[k].max_colex = std::max(stats[k].max_colex, c.max_colex);
+            stats[k].sum_len += c.sum_len;
+            stats[k].sum_flags += c.sum_flags;
+        }
+        stats[k].n_rec = re - rs;
+        stats[k].n_ref = ref_idx[re] - ref_idx[rs];
+        stats[k].lit_bases = lit_off[re] - lit_off[rs];
+        stats[k].lit_word_base = lw;
+        const uint64_t nw = (stats[k].lit_bases + 30) / 31;
+        for (uint64_t w = nw; w-- > 0;) {
+            lits[lw + w] = lit_word_thread(rec, lit_off.data(), rs, re, w);
+            stats[k].max_lit = std::max(stats[k].max_lit, lits[lw + w]);
+        }
+        lw += nw;
     }
+    std::vector<ColSeg> segs;
+    std::vector<HostSeg> hseg;
+    std::vector<int32_t> status;
+    uint64_t bound = 0;
+    const uint64_t flat = plan_encode(stats.data(), blk_rec, &segs, &hseg, &status, &bound);
+    const uint32_t n_segs = n_blocks * 4;
+    std::vector<uint64_t> bit_off(flat + 1, 0);
+    FlatCodeLen cl{arr, segs.data(), n_segs};
+    for (uint64_t i = 0; i < flat; i++) bit_off[i + 1] = bit_off[i] + cl(i).a;
+    uint64_t total = 0;
+    seg_finish_serial(segs.data(), n_segs, bit_off.data(), &total);
+    if (total > bound) return -3;
+    if (total > cap) return -2;
+    for (uint64_t w = total; w-- > 0;) words[w] = bswap64(pack_word_thread(arr, segs.data(), n_segs, bit_off.data(), w));
+    for (uint32_t s2 = 0; s2 < n_segs; s2++) {
+        seg_out[4 * s2] = hseg[s2].n_values; seg_out[4 * s2 + 1] = segs[s2].n_words; seg_out[4 * s2 + 2] = hseg[s2].param; seg_out[4 * s2 + 3] = segs[s2].word_base;
+    }
+    for (uint32_t k = 0; k < n_blocks; k++) status_out[k] = status[k];
+    *total_out = total;
+    return 0;
+}
+
+// GPU column decoder bodies (column_decode_kernels.cuh) + plan_decode on the CPU: cols[4 * (4 b + q) ..] = n_values, n_words,
+// param, word_offset; words as stored (big-endian u64).  Returns 0 and the records of all blocks (concatenated), or the
+// C-ABI error code (7 = NTC_ERR_IO ...); *detail: 1 stream ends early, 2.. zip error bits << 1.
+int emul_columns_decode(const uint64_t* cols_in, uint32_t n_blocks, const uint64_t* words_be, uint64_t n_words, int full_last_word, int trim,
+                        uint64_t* rec, uint64_t cap, uint64_t* n_rec_out, uint32_t* detail) {
+    std::vector<HostCol> cols((size_t)n_blocks * 4);
+    for (size_t i = 0; i < cols.size(); i++) cols[i] = HostCol{cols_in[4 * i], cols_in[4 * i + 1], cols_in[4 * i + 2], cols_in[4 * i + 3]};
+    DecodePlan plan;
+    std::string err;
+    *detail = 0;
+    *n_rec_out = 0;
+    int32_t rc = plan_decode(cols.data(), n_blocks, n_words, &plan, &err);
+    if (rc) return rc;
+    if (plan.n_rec > cap) return 3;
+    const uint32_t n_segs = n_blocks * 4;
+    std::vector<uint64_t> w(n_words + 2, 0);
+    for (uint64_t i = 0; i < n_words; i++) w[i] = __builtin_bswap64(words_be[i]);      // bswap_kernel
+    std::vector<uint32_t> table(plan.table + 1), entry(plan.chunks + 1);
+    std::vector<uint64_t> first(plan.chunks + 1), values(plan.n_values + 1, 0), totals(n_segs, 0);
+    for (uint64_t i = plan.table; i-- > 0;) cw_table_thread(plan.segs.data(), n_segs, w.data(), plan.table, table.data(), i);
+    for (uint32_t s2 = 0; s2 < n_segs; s2++) cw_resolve_serial(plan.segs[s2], table.data(), entry.data(), first.data(), &totals[s2]);
+    for (uint64_t c = plan.chunks; c-- > 0;) cw_extract_thread(plan.segs.data(), n_segs, w.data(), plan.chunks, entry.data(), first.data(), values.data(), c);
+    for (uint32_t s2 = 0; s2 < n_segs; s2++) if (totals[s2] < plan.segs[s2].n_values) { *detail = 1; return 7; }
+    const uint64_t n = plan.n_rec;
+    const uint64_t* flags = values.data() + plan.region[2];
+    std::vector<uint64_t> ref_idx(n + 1), lit_off(n + 1);
+    FlagLoad load{flags};
+    uint64_t a = 0, b = 0;
+    for (uint64_t i = 0; i < n; i++) { ref_idx[i] = a; lit_off[i] = b; Pair64 pr = load(i); a += pr.a; b += pr.b; }
+    ref_idx[n] = a; lit_off[n] = b;
+    uint32_t zerr = 0;
+    for (uint64_t i = n; i-- > 0;)
+        zip_thread(values.data(), flags, plan.zb.data(), n_blocks, ref_idx.data(), lit_off.data(), full_last_word, rec, &zerr, i, n);
+    if (zerr) { *detail = zerr << 1; return 7; }
+    if (trim)                                                            // blk_trim_kernel
+        for (uint32_t k = 0; k < n_blocks; k++)
+            for (uint64_t j = plan.blk_rec[k]; j < plan.blk_rec[k + 1] && ((rec[j] >> 56) & 1u) == 0; j++) rec[j] = orphan_record();
+    *n_rec_out = n;
     return 0;
 }
 
 
-// GPU column decoder bodies (column_decode_kernels.cuh) on the CPU: words as stored (big-endian u64), n values
-// expected; returns the number of codes found (values beyond n are not stored).  -1: bad parameter.
+// one code stream through the decoder bodies (table / resolve / extract with a single segment): returns the number of
+// codes found (values beyond n are not stored).  -1: bad parameter.
 int64_t emul_column_decode(const uint64_t* words_be, uint64_t n_words, uint64_t n, int rice, uint64_t param, uint64_t* out) {
     CodeParams p;
     if (rice) { if (param > 63) return -1; p = CodeParams{1, (uint32_t)param, 0, 0}; }
     else { if (param < 2) return -1; unsigned l; uint64_t limit; minimal_binary_shape(param, &l, &limit); p = CodeParams{0, 0, l, limit}; }
     if (n_words == 0) return 0;
     std::vector<uint64_t> w(n_words);
-    for (uint64_t i = 0; i < n_words; i++) w[i] = __builtin_bswap64(words_be[i]);      // bswap_kernel
+    for (uint64_t i = 0; i < n_words; i++) w[i] = __builtin_bswap64(words_be[i]);
     const uint64_t n_chunks = (n_words * 64 + kCwChunkBits - 1) / kCwChunkBits;
     const uint32_t ns = cw_num_states(p);
+    DecSeg seg{0, n_words, n, 0, 0, n_chunks, 0, p, ns, 0};
     std::vector<uint32_t> table(n_chunks * ns), entry(n_chunks);
     std::vector<uint64_t> first(n_chunks);
-    for (uint64_t i = n_chunks * ns; i-- > 0;) cw_table_thread(p, w.data(), n_words, n_chunks, table.data(), i);
+    for (uint64_t i = n_chunks * ns; i-- > 0;) cw_table_thread(&seg, 1, w.data(), n_chunks * ns, table.data(), i);
     uint64_t total = 0;
-    cw_resolve_serial(table.data(), ns, n_chunks, entry.data(), first.data(), &total);
-    for (uint64_t c = n_chunks; c-- > 0;) cw_extract_thread(p, w.data(), n_words, n_chunks, entry.data(), first.data(), out, n, c);
+    cw_resolve_serial(seg, table.data(), entry.data(), first.data(), &total);
+    for (uint64_t c = n_chunks; c-- > 0;) cw_extract_thread(&seg, 1, w.data(), n_chunks, entry.data(), first.data(), out, c);
     return (int64_t)total;
-}
-
-// zip_thread over a block's four columns; returns the error bits (0 = ok)
-uint32_t emul_zip(const uint64_t* colex, const uint64_t* len, uint64_t n_ref, const uint64_t* flags, uint64_t n, const uint64_t* lits,
-                  uint64_t n_lit_words, int full_last_word, uint64_t* rec) {
-    std::vector<uint64_t> ref_idx(n + 1), lit_off(n + 1);
-    FlagLoad load{flags};
-    uint64_t a = 0, b = 0;
-    for (uint64_t i = 0; i < n; i++) { ref_idx[i] = a; lit_off[i] = b; Pair64 pr = load(i); a += pr.a; b += pr.b; }
-    uint64_t totals[2] = {a, b};
-    uint32_t err = 0;
-    for (uint64_t i = 0; i < n; i++)
-        zip_thread(colex, len, n_ref, flags, n, lits, n_lit_words, ref_idx.data(), lit_off.data(), totals, full_last_word, rec, &err, i);
-    return err;
 }
 
 }  // extern "C"

@@ -125,54 +125,96 @@ def _columns_of(rec):
     return [column_code(cols[q], rice)[1:] for q, rice in enumerate((False, True, True, False))]
 
 
+def _blocks_of(rec, roff, block_reads):
+    """(record slice, reads in block) per block of block_reads reads"""
+    n = len(roff) - 1
+    return [(rec[int(roff[lo]): int(roff[min(n, lo + block_reads)])], min(n, lo + block_reads) - lo) for lo in range(0, n, block_reads)]
+
+
+def _q4_free_reads(rng, g, n, k):
+    """error-free reads whose cover holds reference records only (no literal): with one such block in a batch the
+    reference drops it (Q4) while its neighbours are written"""
+    out = []
+    while len(out) < n:
+        a = int(rng.integers(0, len(g) - 2 * k - 40))
+        out.append(np.ascontiguousarray(g[a: a + k + 30]))
+    return out
+
+
 def test_gpu_column_codec_bodies_on_cpu_emulation():
-    """column_kernels.cuh (split + prefix-summed bit packing) run on the CPU == sequential coders"""
+    """column_kernels.cuh (split to ranks, gathered literal words, one code-length scan over all (block, column) segments,
+    one thread per output word) + the planning of column_plan.h, run on the CPU over MULTI-block batches == the oracle's
+    sequential coders per block (src/encode.rs:59-94,168-229)."""
     from emul_binding import lib as emul_lib
     L = emul_lib()
-    L.emul_block_columns.restype = C.c_int
-    L.emul_block_columns.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    L.emul_batch_columns.restype = C.c_int
+    L.emul_batch_columns.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
     rng = np.random.default_rng(3)
     g = helpers.random_seq(rng, 8000)
     o = ob.OracleIndex.build([g], 20, True)
-    for n_reads, rate, lens in [(400, 0.03, [150]), (50, 0.2, [40, 400]), (800, 0.01, [150, 2000])]:
+    for n_reads, rate, lens, block_reads in [(400, 0.03, [150], 64), (50, 0.2, [40, 400], 7), (800, 0.01, [150, 2000], 800), (90, 0.0, [35], 30)]:
         reads = helpers.sample_reads(rng, [g], n_reads, lens, [rate], 20)
-        rec, _ = o.encode_reads(*ob.concat_reads(reads), fast=True, threads=4)
+        rec, roff = o.encode_reads(*ob.concat_reads(reads), fast=True, threads=4)
+        blk_rec = np.array([int(roff[min(n_reads, b)]) for b in range(0, n_reads + block_reads, block_reads)][: (n_reads + block_reads - 1) // block_reads + 1], dtype=np.uint64)
+        n_blocks = len(blk_rec) - 1
         words = np.zeros(4 * len(rec) + 4096, dtype=np.uint64)
-        nw = np.zeros(4, dtype=np.uint64)
-        params = np.zeros(4, dtype=np.uint64)
-        rc = L.emul_block_columns(_ptr(rec), len(rec), _ptr(words), len(words), _ptr(nw), _ptr(params))
-        assert rc == 0
-        pos = 0
-        for q, (w, p) in enumerate(_columns_of(rec)):
-            assert int(params[q]) == p and int(nw[q]) == len(w), q
-            assert (words[pos: pos + len(w)] == w).all(), q
-            pos += len(w)
+        seg = np.zeros(16 * n_blocks, dtype=np.uint64)
+        status = np.zeros(n_blocks, dtype=np.int32)
+        total = C.c_uint64(0)
+        assert L.emul_batch_columns(_ptr(rec), _ptr(blk_rec), n_blocks, _ptr(words), len(words), _ptr(seg), _ptr(status), C.byref(total)) == 0
+        seg = seg.reshape(n_blocks, 4, 4)
+        for b in range(n_blocks):
+            brec = rec[int(blk_rec[b]): int(blk_rec[b + 1])]
+            cols = ob.split(brec)
+            if len(cols[0]) == 0 or len(cols[3]) == 0:
+                assert status[b] == 10                                   # Q4
+                continue
+            assert status[b] == 0
+            for q, rice in enumerate((False, True, True, False)):
+                ow, op = ob.code_column(cols[q], rice)
+                nv, nw, param, wb = (int(x) for x in seg[b, q])
+                assert (nv, nw, param) == (len(cols[q]), len(ow), op), (b, q)
+                assert (words[wb: wb + nw] == ow).all(), (b, q)
 
 
-@pytest.mark.gpu
-def test_block_write_gpu_is_byte_identical_to_host():
-    rng = np.random.default_rng(4)
-    g = helpers.random_seq(rng, 30000)
-    idx = nt.Index.build([g], 31)
-    ctx = nt.Context(idx, 0)
-    for n_reads, rate, lens in [(3000, 0.01, [150]), (65536, 0.01, [150]), (200, 0.3, [60, 1000])]:
-        reads = helpers.sample_reads(rng, [g], n_reads, lens, [rate], 31)
-        rec, _ = ctx.encode_batch(*nt.concat_reads(reads))
-        rc, blob = block_write(rec, n_reads)
-        cap = int(_lib.lib().ntc_block_bound(len(rec)))
-        out = np.zeros(cap, dtype=np.uint8)
-        nb = C.c_uint64(0)
-        rc2 = _lib.lib().ntc_block_write_gpu(ctx._h, _ptr(rec), len(rec), n_reads, _ptr(out), cap, C.byref(nb))
-        assert rc2 == rc
-        if rc == 0:
-            assert out[: nb.value].tobytes() == blob
-            rc3, rec2, used = block_read(blob)
-            n_lit = int((np.where(((rec >> np.uint64(56)) & np.uint64(2)) != 0, (rec >> np.uint64(58)) & np.uint64(63), 0)).sum())
-            if n_lit % 31:
-                assert rc3 == 0 and (rec2 == rec).all()
-    only_ref = rec[((rec >> np.uint64(56)) & np.uint64(2)) == 0]
-    nb = C.c_uint64(0)
-    assert _lib.lib().ntc_block_write_gpu(ctx._h, _ptr(only_ref), len(only_ref), 1, _ptr(out), cap, C.byref(nb)) == 10
+def test_gpu_literal_and_packing_bodies_edge_cases_on_cpu_emulation():
+    """literal records of every length 0..32 (foreign streams; bases 28..31 of a record read as A, src/encode.rs:215-216),
+    literal words that straddle many records, long unary runs, values needing 63-bit minimal-binary codes"""
+    from emul_binding import lib as emul_lib
+    L = emul_lib()
+    L.emul_batch_columns.restype = C.c_int
+    L.emul_batch_columns.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+    rng = np.random.default_rng(33)
+    recs = []
+    for i in range(3000):
+        if rng.random() < 0.4:
+            ln = int(rng.choice([12, 92, 150, 1 << 20, (1 << 24) - 1])) if rng.random() < 0.2 else int(rng.integers(12, 200))
+            recs.append(int(rng.integers(0, 1 << 32)) | (ln << 32) | (int(rng.integers(0, 2)) << 56))
+        else:
+            Lb = int(rng.integers(0, 33))
+            bits = int(rng.integers(0, 1 << 56)) & ((1 << min(56, 2 * Lb)) - 1) if Lb else 0
+            recs.append(bits | (((int(rng.integers(0, 2)) + 2) | (Lb << 2)) << 56))
+    rec = np.array(recs, dtype=np.uint64)
+    for cuts in ([0, 3000], [0, 1, 2, 700, 701, 3000], [0, 1500, 1500, 3000]):
+        blk_rec = np.array(cuts, dtype=np.uint64)
+        n_blocks = len(cuts) - 1
+        words = np.zeros(40 * len(rec) + 4096, dtype=np.uint64)
+        seg = np.zeros(16 * n_blocks, dtype=np.uint64)
+        status = np.zeros(n_blocks, dtype=np.int32)
+        total = C.c_uint64(0)
+        assert L.emul_batch_columns(_ptr(rec), _ptr(blk_rec), n_blocks, _ptr(words), len(words), _ptr(seg), _ptr(status), C.byref(total)) == 0
+        seg = seg.reshape(n_blocks, 4, 4)
+        for b in range(n_blocks):
+            brec = rec[cuts[b]: cuts[b + 1]]
+            cols = ob.split(brec) if len(brec) else None
+            if cols is None or len(cols[0]) == 0 or len(cols[3]) == 0:
+                assert status[b] in (4, 10)
+                continue
+            for q, rice in enumerate((False, True, True, False)):
+                ow, op = ob.code_column(cols[q], rice)
+                nv, nw, param, wb = (int(x) for x in seg[b, q])
+                assert (nv, nw, param) == (len(cols[q]), len(ow), op), (cuts, b, q)
+                assert (words[wb: wb + nw] == ow).all(), (cuts, b, q)
 
 
 def _emul_decode(words, n, rice, param):
@@ -216,38 +258,134 @@ def test_gpu_column_decoder_bodies_on_cpu_emulation():
     assert total < 1999
 
 
-def test_gpu_zip_body_on_cpu_emulation():
+def _cols_of_blocks(blobs):
+    """disassemble written blocks into the (cols, words) arrays emul_columns_decode / ntc_decode_columns_fasta take"""
+    cols, words, blocks = [], [], []
+    at = 0
+    for blob in blobs:
+        blk, w, used = nt.block_disassemble(blob)
+        assert used == len(blob)
+        for q in range(4):
+            blk.col[q].word_offset += at
+            cols += [blk.col[q].n_values, blk.col[q].n_words, blk.col[q].param, blk.col[q].word_offset]
+        at += len(w)
+        words.append(w)
+        blocks.append(blk)
+    return np.array(cols, dtype=np.uint64), (np.concatenate(words) if words else np.zeros(0, dtype=np.uint64)), blocks
+
+
+def _emul_columns_decode(cols, n_blocks, words, full, trim, cap):
     from emul_binding import lib as emul_lib
     L = emul_lib()
-    L.emul_zip.restype = C.c_uint32
-    L.emul_zip.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+    L.emul_columns_decode.restype = C.c_int
+    L.emul_columns_decode.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+    out = np.zeros(max(cap, 1), dtype=np.uint64)
+    n, detail = C.c_uint64(0), C.c_uint32(0)
+    rc = L.emul_columns_decode(_ptr(cols), n_blocks, _ptr(words), len(words), full, trim, _ptr(out), cap, C.byref(n), C.byref(detail))
+    return rc, out[: n.value], detail.value
+
+
+def test_gpu_column_decode_and_zip_bodies_on_cpu_emulation():
+    """multi-block batches through plan_decode + the decoder bodies + zip_thread (+ the per-block trim) == the records the
+    oracle reads back block by block (src/decode.rs:51-149); Q5 and zip errors as the host reader reports them"""
     rng = np.random.default_rng(19)
     g = helpers.random_seq(rng, 8000)
     o = ob.OracleIndex.build([g], 20, True)
-    for n_reads, rate in [(300, 0.03), (60, 0.2), (500, 0.01)]:
+    for n_reads, rate, block_reads in [(300, 0.03, 64), (60, 0.2, 60), (500, 0.01, 137)]:
         reads = helpers.sample_reads(rng, [g], n_reads, [150, 35, 400], [rate], 20)
-        rec, _ = o.encode_reads(*ob.concat_reads(reads), fast=True, threads=4)
-        cols = [np.ascontiguousarray(c, dtype=np.uint64) for c in ob.split(rec)]
-        n_lit = int(sum((int(f) >> 2) for f in cols[2] if int(f) & 2))
-        out = np.zeros(len(rec), dtype=np.uint64)
+        rec, roff = o.encode_reads(*ob.concat_reads(reads), fast=True, threads=4)
+        blobs, kept = [], []
+        for brec, nr in _blocks_of(rec, roff, block_reads):
+            blob = ob.write_block(brec, nr)
+            if blob is not None:
+                blobs.append(blob)
+                kept.append(brec)
+        cols, words, _ = _cols_of_blocks(blobs)
+        q5 = any(int(np.where((r >> np.uint64(57)) & np.uint64(1), (r >> np.uint64(58)) & np.uint64(63), 0).sum()) % 31 == 0 for r in kept)
         for full in (0, 1):
-            err = L.emul_zip(_ptr(cols[0]), _ptr(cols[1]), len(cols[0]), _ptr(cols[2]), len(cols[2]), _ptr(cols[3]), len(cols[3]), full, _ptr(out))
-            if n_lit % 31 == 0 and n_lit and not full:
-                assert err == 2                                         # Q5
+            rc, got, detail = _emul_columns_decode(cols, len(blobs), words, full, 0, len(rec))
+            if q5 and not full:
+                assert rc == 7 and detail == (2 << 1)                    # Q5: ZIP_ERR_LIT
             else:
-                assert err == 0 and (out == rec).all()
-    # more reference records than colex values / a literal longer than 32 bases
-    flags = np.array([1, 0, 0], dtype=np.uint64)
-    one = np.array([5], dtype=np.uint64)
-    assert L.emul_zip(_ptr(one), _ptr(one), 1, _ptr(flags), 3, _ptr(one), 1, 0, _ptr(np.zeros(3, dtype=np.uint64))) & 1
-    flags = np.array([(33 << 2) | 3], dtype=np.uint64)
-    assert L.emul_zip(_ptr(one), _ptr(one), 1, _ptr(flags), 1, _ptr(one), 1, 0, _ptr(np.zeros(1, dtype=np.uint64))) & 4
+                assert rc == 0 and (got == np.concatenate(kept)).all()
+                for blob, brec in zip(blobs, kept):
+                    orec = ob.read_block(blob) if not q5 else None
+                    assert orec is None or (orec[0] == brec).all()
+    # per-block trim: records in front of a block's first `first` flag become empty literals, other blocks untouched
+    a = np.array([5 | (20 << 32), 6 | (30 << 32), 7 | (40 << 32) | (1 << 56), (0b11 | ((2 | (1 << 2)) << 56))], dtype=np.uint64)
+    b = np.array([9 | (25 << 32) | (1 << 56), (0b10 | ((2 | (1 << 2)) << 56))], dtype=np.uint64)
+    cols, words, _ = _cols_of_blocks([ob.write_block(b, 1), ob.write_block(a, 1), ob.write_block(b, 1)])
+    rc, got, _ = _emul_columns_decode(cols, 3, words, 0, 1, 64)
+    want = np.concatenate([b, np.array([2 << 56, 2 << 56], dtype=np.uint64), a[2:], b])
+    assert rc == 0 and (got == want).all()
+    rc, got, _ = _emul_columns_decode(cols, 3, words, 0, 0, 64)
+    assert rc == 0 and (got == np.concatenate([b, a, b])).all()
+    # header fields from a hostile file: rejected by the planner before anything is sized by them
+    bad = cols.copy(); bad[4 * 1 + 2] = 64                              # Rice parameter of the len column
+    assert _emul_columns_decode(bad, 3, words, 0, 0, 64)[0] == 7
+    bad = cols.copy(); bad[2] = 1                                       # minimal-binary bound below 2
+    assert _emul_columns_decode(bad, 3, words, 0, 0, 64)[0] == 7
+    bad = cols.copy(); bad[0] = 1 << 40                                 # more values than bits
+    assert _emul_columns_decode(bad, 3, words, 0, 0, 64)[0] == 7
+    bad = cols.copy(); bad[3] = len(words) + 5                          # words outside the buffer
+    assert _emul_columns_decode(bad, 3, words, 0, 0, 64)[0] == 1
+
+
+def test_malformed_headers_are_rejected_by_the_host_reader():
+    """a hostile .dat must produce an error code, never an out-of-range shift, a 32 GiB reserve or an
+    exception across the C ABI.  The GPU reader applies the same checks (test_block_read_gpu_matches_oracle)."""
+    import struct
+    rec = np.array([7 | (40 << 32) | (1 << 56), 0b1101 | ((0 + 2) | (2 << 2)) << 56], dtype=np.uint64)
+    rc, blob = block_write(rec, 1)
+    assert rc == 0
+    for field_off, value in [(16, 64), (16, 1 << 40)]:                                     # Rice parameter of the len column (2nd sub-block)
+        bs0 = struct.unpack_from("<I", blob, 0)[0]
+        b = bytearray(blob)
+        struct.pack_into("<Q", b, 32 + bs0 + field_off, value)
+        assert block_read(bytes(b))[0] == 7
+    for value in (0, 1):                                                                    # minimal-binary bound of the colex column
+        b = bytearray(blob)
+        struct.pack_into("<Q", b, 16, value)
+        assert block_read(bytes(b))[0] == 7
+    b = bytearray(blob)
+    struct.pack_into("<I", b, 8, 0xFFFFFFFF)                                                # num_u64: 4 G values announced for a few bytes
+    assert block_read(bytes(b))[0] == 7
+    b = bytearray(blob)
+    struct.pack_into("<I", b, 0, 0xFFFFFFF0)                                                # block_size beyond the data
+    assert block_read(bytes(b))[0] == 7
 
 
 @pytest.mark.gpu
-def test_block_read_gpu_matches_host_reader():
-    """ntc_block_read_gpu (integer decoders + zip on the GPU) == ntc_block_read_ex on the same bytes, errors included"""
-    import ntcomp_b200 as nt
+def test_block_write_gpu_matches_oracle_bytes():
+    """ntc_block_write_gpu (split + codes on the GPU) against the ORACLE's write_block directly (and the host container)"""
+    rng = np.random.default_rng(4)
+    g = helpers.random_seq(rng, 30000)
+    idx = nt.Index.build([g], 31)
+    ctx = nt.Context(idx, 0)
+    o = ob.OracleIndex.from_arrays(idx.k, idx.n_sets, idx.rows(), idx.lcs())
+    for n_reads, rate, lens in [(3000, 0.01, [150]), (65536, 0.01, [150]), (200, 0.3, [60, 1000]), (3, 0.05, [150])]:
+        reads = helpers.sample_reads(rng, [g], n_reads, lens, [rate], 31)
+        rec, _ = o.encode_reads(*ob.concat_reads(reads), fast=True, threads=8)
+        want = ob.write_block(rec, n_reads)
+        cap = int(_lib.lib().ntc_block_bound(len(rec)))
+        out = np.zeros(cap, dtype=np.uint8)
+        nb = C.c_uint64(0)
+        rc = _lib.lib().ntc_block_write_gpu(ctx._h, _ptr(rec), len(rec), n_reads, _ptr(out), cap, C.byref(nb))
+        if want is None:
+            assert rc == 10
+            continue
+        assert rc == 0 and out[: nb.value].tobytes() == want
+        assert block_write(rec, n_reads) == (0, want)
+    only_ref = rec[((rec >> np.uint64(56)) & np.uint64(2)) == 0]
+    nb = C.c_uint64(0)
+    assert _lib.lib().ntc_block_write_gpu(ctx._h, _ptr(only_ref), len(only_ref), 1, _ptr(out), cap, C.byref(nb)) == 10
+
+
+@pytest.mark.gpu
+def test_block_read_gpu_matches_oracle():
+    """ntc_block_read_gpu (integer decoders + zip on the GPU) against the ORACLE's read_block directly; errors as the host
+    reader reports them"""
+    import struct
     rng = np.random.default_rng(23)
     g = helpers.random_seq(rng, 60000)
     index = nt.Index.build([g], 31)
@@ -264,22 +402,77 @@ def test_block_read_gpu_matches_host_reader():
     for n_reads, rate, lens in [(65536, 0.01, [150]), (3000, 0.05, [150, 2000, 10000]), (500, 0.3, [60]), (7, 0.0, [400])]:
         reads = helpers.sample_reads(rng, [g], n_reads, lens, [rate], 31)
         rec, _ = o.encode_reads(*ob.concat_reads(reads), fast=True, threads=8)
-        rc, blob = block_write(rec, n_reads)
-        if rc == 10:
+        blob = ob.write_block(rec, n_reads)
+        if blob is None:
             continue
         good = blob
+        n_lit = int(np.where((rec >> np.uint64(57)) & np.uint64(1), (rec >> np.uint64(58)) & np.uint64(63), 0).sum())
         for flags in (0, 1):
-            hrc, hrec, hused = block_read(blob) if flags == 0 else (0,) + nt.block_read(blob, True)
             grc, grec, gused = gpu_read(blob, flags)
+            hrc = block_read(blob)[0] if flags == 0 else 0
             assert grc == hrc, (n_reads, flags)
-            if hrc == 0:
-                assert gused == hused == len(blob) and (grec == hrec).all() and (grec == rec).all()
+            if n_lit % 31 == 0 and not flags:
+                assert grc == 7                                         # Q5: the reference panics
+                continue
+            orec, _, oused = ob.read_block(blob) if n_lit % 31 else (rec, None, len(blob))
+            assert grc == 0 and gused == oused == len(blob) and (grec == orec).all() and (grec == rec).all()
     assert gpu_read(b"")[0] == 0 and gpu_read(b"")[2] == 0          # EOF
     assert gpu_read(good[: len(good) // 2])[0] == 7                    # truncated
     # Q5 block: refused like the reference without the flag, decoded with it
     recs = [7 | (40 << 32) | (1 << 56)] + [int(rng.integers(0, 4)) | ((2 | (1 << 2)) << 56) for _ in range(31)]
     q5 = np.array(recs, dtype=np.uint64)
-    rc, blob = block_write(q5, 1)
-    assert rc == 0 and gpu_read(blob, 0)[0] == 7
+    blob = ob.write_block(q5, 1)
+    assert gpu_read(blob, 0)[0] == 7
     grc, grec, _ = gpu_read(blob, 1)
     assert grc == 0 and (grec == q5).all()
+    # malformed header fields: same verdict as the host reader
+    bs0 = struct.unpack_from("<I", good, 0)[0]
+    for off, fmt, value in [(32 + bs0 + 16, "<Q", 64), (16, "<Q", 1), (8, "<I", 0xFFFFFFFF), (0, "<I", 0xFFFFFFF0)]:
+        b = bytearray(good)
+        struct.pack_into(fmt, b, off, value)
+        assert gpu_read(bytes(b))[0] == 7 and block_read(bytes(b))[0] == 7
+
+
+@pytest.mark.gpu
+def test_fused_columns_encode_and_decode_match_oracle_blocks():
+    """Row f1 as SURVEY 8(f)1 defines it: ntc_encode_columns (records stay in HBM, only coded words travel) + the host
+    remainder ntc_block_assemble == the oracle's write_block per block, byte for byte (both link system zlib), including a
+    block the reference drops (Q4); ntc_decode_columns_fasta over the same coded blocks == the FASTA text of the reads."""
+    rng = np.random.default_rng(41)
+    g = helpers.random_seq(rng, 50000)
+    index = nt.Index.build([g], 31)
+    ctx = nt.Context(index, 0)
+    o = ob.OracleIndex.from_arrays(index.k, index.n_sets, index.rows(), index.lcs())
+    for n_reads, rate, lens, block_reads in [(5000, 0.01, [150], 512), (70000, 0.01, [150], 65536), (300, 0.05, [150, 3000], 64), (10, 0.0, [100], 100)]:
+        reads = helpers.sample_reads(rng, [g], n_reads, lens, [rate], 31)
+        if n_reads == 5000:
+            reads[1024: 1536] = _q4_free_reads(rng, g, 512, 31)          # block 2: reference records only
+        bases, off = nt.concat_reads(reads)
+        rec, roff = o.encode_reads(bases, off, fast=True, threads=8)
+        blocks, words, n_rec = ctx.encode_columns(bases, off, block_reads)
+        assert n_rec == len(rec) and len(blocks) == (n_reads + block_reads - 1) // block_reads
+        kept_blocks, kept_reads, dropped = [], [], 0
+        for b, (brec, nr) in enumerate(_blocks_of(rec, roff, block_reads)):
+            want = ob.write_block(brec, nr)
+            assert blocks[b].n_records == len(brec) and blocks[b].num_reads == nr
+            if want is None:
+                assert blocks[b].status == 10
+                dropped += 1
+                continue
+            assert blocks[b].status == 0
+            assert nt.block_assemble(blocks[b], words) == want, (n_reads, b)
+            kept_blocks.append(blocks[b])
+            kept_reads += reads[b * block_reads: b * block_reads + nr]
+        assert dropped == (1 if n_reads == 5000 else 0)
+        n_lit_ok = all(int(sum(int(c.n_values) for c in [blk.col[3]])) >= 0 for blk in kept_blocks)
+        text, n_seqs, n_dec = ctx.decode_columns_fasta(kept_blocks, words, 7, full_last_literal_word=True)
+        assert n_lit_ok and n_seqs == len(kept_reads) and n_dec == sum(int(b.n_records) for b in kept_blocks)
+        assert text == helpers.fasta_text(kept_reads, 7)
+    # blocks read back from bytes (ntc_block_disassemble), one of them with orphan records in front of its first flag
+    a = np.array([5 | (20 << 32), 7 | (40 << 32) | (1 << 56), (0b11 | ((2 | (1 << 2)) << 56))], dtype=np.uint64)
+    b = np.array([9 | (25 << 32) | (1 << 56), (0b10 | ((2 | (1 << 2)) << 56))], dtype=np.uint64)
+    _, words, blks = _cols_of_blocks([ob.write_block(b, 1), ob.write_block(a, 1), ob.write_block(b, 1)])
+    text, n_seqs, _ = ctx.decode_columns_fasta(blks, words, 1)
+    sb = b"".join(o.decode(b, fast=True)[0].tobytes() for _ in range(1))
+    sa = o.decode(a, fast=True)[0].tobytes()
+    assert n_seqs == 3 and text == b">seq.1\n" + sb + b"\n>seq.2\n" + sa + b"\n>seq.3\n" + sb + b"\n"
