@@ -197,6 +197,11 @@ int32_t ntc_column_code(const uint64_t* values, uint64_t n, int32_t rice, uint64
  * decode stats[6]: sequences, FASTA bytes written, records, bytes read, blocks, 0.  stats may be NULL. */
 int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_path, int32_t n_threads, uint64_t* stats);
 int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path, int32_t n_threads, uint64_t* stats);
+/* fastX file (FASTA / FASTQ, plain or gzip) -> the normalised sequences (needletail normalize(true) for what can reach the
+ * encoder, src/main.rs:158-163), parsed like the encode pipeline does: one reader thread cutting at record boundaries,
+ * n_threads parsers.  *bases (n_bases bytes) and *offsets (n_reads + 1) are malloc'ed: release with ntc_free. */
+int32_t ntc_fastx_load(const char* path, int32_t n_threads, uint8_t** bases, uint64_t** offsets, uint64_t* n_reads, uint64_t* n_bases);
+void ntc_free(void* p);
 /* `ntcomp build` front end (src/main.rs:97-134): every fastX record of every file is one input sequence */
 int32_t ntc_index_build_from_files(const char* const* paths, uint64_t n_paths, uint32_t k, int32_t add_revcomp,
                                    int32_t n_threads, ntc_index** out);

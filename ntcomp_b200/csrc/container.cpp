@@ -238,7 +238,9 @@ static bool gzip_member(const uint8_t* in, size_t n, std::vector<uint8_t>* out) 
     out->resize(zs.total_out);
     return true;
 }
-static bool gunzip_member(const uint8_t* in, size_t n, std::vector<uint8_t>* out) {
+// limit: stop once more than this many bytes came out (the header's encoded_size says how many there must be; a
+// hostile member must not inflate without bound)
+static bool gunzip_member(const uint8_t* in, size_t n, std::vector<uint8_t>* out, uint64_t limit) {
     z_stream zs;
     memset(&zs, 0, sizeof(zs));
     if (inflateInit2(&zs, 15 + 16) != Z_OK) return false;
@@ -253,6 +255,7 @@ static bool gunzip_member(const uint8_t* in, size_t n, std::vector<uint8_t>* out
         rc = inflate(&zs, Z_NO_FLUSH);
         if (rc != Z_OK && rc != Z_STREAM_END) { inflateEnd(&zs); return false; }
         out->insert(out->end(), buf.data(), buf.data() + (buf.size() - zs.avail_out));
+        if (out->size() > limit) { inflateEnd(&zs); return false; }
         if (rc == Z_OK && zs.avail_in == 0 && zs.avail_out != 0) { inflateEnd(&zs); return false; }  // truncated member
     } while (rc != Z_STREAM_END);
     inflateEnd(&zs);
@@ -285,7 +288,7 @@ int64_t inflate_sub_block(const uint8_t* data, uint64_t size, std::vector<uint64
     memcpy(param, data + 16, 8);
     if (32ull + block_size > size) return -2;
     std::vector<uint8_t> raw;
-    if (!gunzip_member(data + 32, block_size, &raw)) return -3;
+    if (!gunzip_member(data + 32, block_size, &raw, (uint64_t)encoded_size * 8)) return -3;
     if (raw.size() % 8 || raw.size() / 8 != encoded_size) return -5;              // src/decode.rs:90
     words->resize(raw.size() / 8);
     if (!raw.empty()) memcpy(words->data(), raw.data(), raw.size());
@@ -303,7 +306,7 @@ int64_t read_sub_block(const uint8_t* data, uint64_t size, int rice, std::vector
     memcpy(&param, data + 16, 8);
     if (32ull + block_size > size) return -2;
     std::vector<uint8_t> raw;
-    if (!gunzip_member(data + 32, block_size, &raw)) return -3;
+    if (!gunzip_member(data + 32, block_size, &raw, (uint64_t)encoded_size * 8)) return -3;
     if (raw.size() % 8 || raw.size() / 8 != encoded_size) return -5;              // src/decode.rs:90
     std::vector<uint64_t> words(raw.size() / 8);
     memcpy(words.data(), raw.data(), raw.size());

@@ -11,6 +11,7 @@
 #include <zlib.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <condition_variable>
 #include <cstdio>
@@ -19,6 +20,7 @@
 #include <deque>
 #include <exception>
 #include <functional>
+#include <map>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -62,6 +64,14 @@ public:
     bool pop(T* out) {                               // false at end of stream
         std::unique_lock<std::mutex> lk(m_);
         cv_.wait(lk, [&] { return !q_.empty() || done_ || closed_; });
+        if (q_.empty()) return false;
+        *out = std::move(q_.front());
+        q_.pop_front();
+        cv_.notify_all();
+        return true;
+    }
+    bool try_pop(T* out) {                           // non-blocking
+        std::lock_guard<std::mutex> lk(m_);
         if (q_.empty()) return false;
         *out = std::move(q_.front());
         q_.pop_front();
@@ -122,128 +132,325 @@ struct Sink {
     ~Sink() { close(); }
 };
 
-// ---- fastX reader (plain or gzip; FASTA with wrapped lines, FASTQ with 4-line or wrapped records) ----
-// Reads the stream in 4 MB pieces and walks lines with memchr; sequence bytes are copied line by line
-// and normalised in place (needletail normalize(true) for the bytes that can reach the encoder:
-// upper-case, U -> T, white space dropped; everything else passes through and is rejected by the encoder
-// unless it is A, C, G or T).
-class FastxReader {
-public:
-    bool open(const char* path) {
-        f_ = (strcmp(path, "-") == 0) ? gzdopen(0, "rb") : gzopen(path, "rb");
-        if (!f_) return false;
-        gzbuffer(f_, 1 << 20);
-        buf_.resize(4 << 20);
+// ---- fastX parsing (plain or gzip; FASTA with wrapped lines, FASTQ with 4-line or wrapped records) ----
+// needletail's parser (src/main.rs:158-163, normalize(true)) restated for the bytes that can reach the encoder: upper-case,
+// U -> T, white space dropped; everything else passes through and is rejected by the encoder unless it is A, C, G or T.
+// ---- in-memory parsing of a piece of fastX text that holds WHOLE records ------------------------------------
+// (the reader thread cuts the input at record boundaries and the pieces are parsed on the worker pool)
+struct ParsedPiece {
+    std::vector<uint8_t> bases;      // normalised sequences, concatenated
+    std::vector<uint32_t> lens;      // one per record
+    int err = 0;                     // 1 malformed record, 2 a read of 2^32 bases or more
+};
+
+inline size_t normalise_into(const uint8_t* __restrict__ s, size_t n, std::vector<uint8_t>* out) {
+    const size_t at = out->size();
+    out->insert(out->end(), s, s + n);
+    uint64_t odd = 0;
+    size_t i = 0;
+    const uint64_t k01 = 0x0101010101010101ull, k80 = 0x8080808080808080ull;
+    for (; i + 8 <= n; i += 8) {
+        uint64_t w;
+        memcpy(&w, s + i, 8);
+        const uint64_t t = w ^ (k01 * 0x09), u = w ^ (k01 * 0x55);
+        odd |= (w & (k01 * 0x20)) | ((t - k01) & ~t & k80) | ((u - k01) & ~u & k80);
+    }
+    for (; i < n; i++) odd |= (uint64_t)(s[i] & 0x20u) | (uint64_t)(s[i] == '\t') | (uint64_t)(s[i] == 'U');
+    if (!odd) return n;
+    uint8_t* d = out->data() + at;
+    size_t w = 0;
+    for (size_t j = 0; j < n; j++) {
+        uint8_t ch = d[j];
+        if (ch == ' ' || ch == '\t') continue;
+        if (ch >= 'a' && ch <= 'z') ch = (uint8_t)(ch - 32);
+        if (ch == 'U') ch = 'T';
+        d[w++] = ch;
+    }
+    out->resize(at + w);
+    return w;
+}
+
+struct MemLines {
+    const uint8_t* p;
+    const uint8_t* end;
+    bool line(const uint8_t** s, size_t* n) {                          // next line without its "\n" / "\r\n"
+        if (p >= end) return false;
+        const uint8_t* nl = (const uint8_t*)memchr(p, '\n', (size_t)(end - p));
+        *s = p;
+        *n = nl ? (size_t)(nl - p) : (size_t)(end - p);
+        p = nl ? nl + 1 : end;
+        while (*n && (*s)[*n - 1] == '\r') (*n)--;
         return true;
     }
-    ~FastxReader() { if (f_) gzclose(f_); }
-    // appends the next record's normalised sequence to *bases; 1 = got one, 0 = end of file, -1 = malformed
-    int next(std::vector<uint8_t>* bases) {
-        const uint8_t* ln;
-        size_t n;
-        do { if (!line(&ln, &n)) return 0; } while (n == 0);            // blank lines between records
+    int peek() const { return p < end ? *p : -1; }
+};
+
+void parse_piece(const uint8_t* text, size_t n, ParsedPiece* out) {
+    MemLines ml{text, text + n};
+    out->bases.reserve(n / 2 + 64);
+    const uint8_t* ln;
+    size_t len;
+    while (ml.line(&ln, &len)) {
+        if (len == 0) continue;                                        // blank lines between records
+        size_t got_bases = 0;
         if (ln[0] == '>') {
-            while (peek() >= 0 && peek() != '>') {
-                if (!line(&ln, &n)) break;
-                append_normalised(ln, n, bases);
+            while (ml.peek() >= 0 && ml.peek() != '>') {
+                if (!ml.line(&ln, &len)) break;
+                got_bases += normalise_into(ln, len, &out->bases);
             }
-            return 1;
-        }
-        if (ln[0] == '@') {
+        } else if (ln[0] == '@') {
             size_t want = 0, got = 0;                                  // quality has one byte per sequence byte
-            for (;;) {                                                 // sequence lines up to the '+' separator
-                if (!line(&ln, &n)) return -1;
-                if (n && ln[0] == '+') break;
-                want += append_normalised(ln, n, bases);
+            for (;;) {
+                if (!ml.line(&ln, &len)) { out->err = 1; return; }
+                if (len && ln[0] == '+') break;
+                size_t before = out->bases.size();
+                normalise_into(ln, len, &out->bases);
+                got_bases += out->bases.size() - before;
+                want += out->bases.size() - before;
             }
             while (got < want) {
-                if (!line(&ln, &n)) return -1;
-                got += n;
+                if (!ml.line(&ln, &len)) { out->err = 1; return; }
+                got += len;
             }
-            return got == want ? 1 : -1;
-        }
-        return -1;
+            if (got != want) { out->err = 1; return; }
+        } else { out->err = 1; return; }
+        if (got_bases >= (1ull << 32)) { out->err = 2; return; }
+        out->lens.push_back((uint32_t)got_bases);
     }
+}
 
+// Is p (the first byte of a line) the start of a record?  FASTA: '>' at a line start always is.  FASTQ: '@' may also open
+// a quality line, so the 4-line shape is checked: '@' line, sequence line, '+' line, quality line of the same length, and
+// the line after it starts with '@' (or the text ends).  A quality line that begins with '@' fails the check -- the line
+// two further on would be a sequence, which cannot start with '+'.  Multi-line FASTQ fails everywhere: the reader then
+// keeps the text together and one worker parses it serially (correct, just not parallel).
+bool record_starts_at(const uint8_t* p, const uint8_t* end, int fmt) {
+    if (p >= end) return false;
+    if (fmt == '>') return *p == '>';
+    if (*p != '@') return false;
+    MemLines ml{p, end};
+    const uint8_t* s;
+    size_t n1, n2, n3, n4;
+    if (!ml.line(&s, &n1) || !ml.line(&s, &n2) || n2 == 0 || s[0] == '@' || s[0] == '+') return false;
+    if (!ml.line(&s, &n3) || n3 == 0 || s[0] != '+') return false;
+    if (!ml.line(&s, &n4) || n4 != n2) return false;
+    return ml.peek() < 0 || ml.peek() == '@';
+}
+
+// last record start in text[lo, n) that is not at position 0; returns 0 when there is none
+size_t last_record_start(const uint8_t* text, size_t n, size_t lo, int fmt) {
+    size_t hi = n;
+    while (hi > lo + 1) {
+        const void* q = memrchr(text + lo, '\n', hi - lo - 1);         // a newline that is followed by at least one byte
+        if (!q) return 0;
+        const size_t at = (size_t)((const uint8_t*)q - text) + 1;
+        if (text[at] == (uint8_t)fmt && record_starts_at(text + at, text + n, fmt)) {
+            // FASTQ: the check looked ahead over four lines; a candidate in the unfinished tail of the buffer may have
+            // passed only because the text ends there -- require that a full record follows or the caller treats EOF
+            return at;
+        }
+        hi = at - 1 > lo ? at - 1 : lo;
+        if (hi == lo) break;
+    }
+    return 0;
+}
+
+// free list of buffers that keep their capacity (fresh multi-megabyte vectors cost a page fault per 4 KB on first touch,
+// and concurrent faults serialise in the kernel: measured here the in-order consumer spent 0.7 s per 300 MB in them)
+template <typename T>
+class Recycler {
+public:
+    T get() {
+        std::lock_guard<std::mutex> lk(m_);
+        if (free_.empty()) return T();
+        T v = std::move(free_.back());
+        free_.pop_back();
+        return v;
+    }
+    void put(T&& v) {
+        std::lock_guard<std::mutex> lk(m_);
+        if (free_.size() < 64) free_.push_back(std::move(v));
+    }
 private:
-    gzFile f_ = nullptr;
-    std::vector<uint8_t> buf_;
-    size_t lo_ = 0, hi_ = 0;      // unread bytes are buf_[lo_, hi_)
-    bool eof_ = false;
-
-    bool fill() {                 // keeps the unread tail, appends more input; false when nothing was added
-        if (eof_) return false;
-        if (lo_ > 0) { memmove(buf_.data(), buf_.data() + lo_, hi_ - lo_); hi_ -= lo_; lo_ = 0; }
-        if (hi_ == buf_.size()) buf_.resize(buf_.size() * 2);         // a single line longer than the buffer
-        int got = gzread(f_, buf_.data() + hi_, (unsigned)std::min<size_t>(buf_.size() - hi_, 1u << 30));
-        if (got <= 0) { eof_ = true; return false; }
-        hi_ += (size_t)got;
-        return true;
-    }
-    int peek() {                  // first byte of the next line, -1 at end of input
-        if (lo_ == hi_ && !fill()) return -1;
-        return buf_[lo_];
-    }
-    bool line(const uint8_t** p, size_t* n) {                          // next line without its "\n" / "\r\n"
-        for (;;) {
-            const uint8_t* nl = hi_ > lo_ ? (const uint8_t*)memchr(buf_.data() + lo_, '\n', hi_ - lo_) : nullptr;
-            if (nl) {
-                *p = buf_.data() + lo_;
-                *n = (size_t)(nl - *p);
-                lo_ += *n + 1;
-                break;
-            }
-            if (!fill()) {                                             // last line without a newline
-                if (lo_ == hi_) return false;
-                *p = buf_.data() + lo_;
-                *n = hi_ - lo_;
-                lo_ = hi_;
-                break;
-            }
-        }
-        while (*n && ((*p)[*n - 1] == '\r')) (*n)--;
-        return true;
-    }
-    size_t append_normalised(const uint8_t* __restrict__ s, size_t n, std::vector<uint8_t>* out) {
-        const size_t at = out->size();
-        out->insert(out->end(), s, s + n);                             // plain copy; upper-case ACGT lines need nothing else
-        // anything to fix?  lower case / space have bit 5 set, tab and U are looked for with the zero-byte trick;
-        // eight bytes per step (the byte-wise loop did not vectorise: 2 ns per base)
-        uint64_t odd = 0;
-        size_t i = 0;
-        const uint64_t k01 = 0x0101010101010101ull, k80 = 0x8080808080808080ull;
-        for (; i + 8 <= n; i += 8) {
-            uint64_t w;
-            memcpy(&w, s + i, 8);
-            const uint64_t t = w ^ (k01 * 0x09), u = w ^ (k01 * 0x55);
-            odd |= (w & (k01 * 0x20)) | ((t - k01) & ~t & k80) | ((u - k01) & ~u & k80);
-        }
-        for (; i < n; i++) odd |= (uint64_t)(s[i] & 0x20u) | (uint64_t)(s[i] == '\t') | (uint64_t)(s[i] == 'U');
-        if (!odd) return n;
-        uint8_t* d = out->data() + at;
-        size_t w = 0;
-        for (size_t i = 0; i < n; i++) {
-            uint8_t ch = d[i];
-            if (ch == ' ' || ch == '\t') continue;
-            if (ch >= 'a' && ch <= 'z') ch = (uint8_t)(ch - 32);
-            if (ch == 'U') ch = 'T';
-            d[w++] = ch;
-        }
-        out->resize(at + w);
-        return w;
-    }
+    std::mutex m_;
+    std::vector<T> free_;
 };
+
+// counting semaphore: bounds the pieces in flight between the reader and the batch assembly
+class Tokens {
+public:
+    explicit Tokens(size_t n) : n_(n) {}
+    bool acquire() { std::unique_lock<std::mutex> lk(m_); cv_.wait(lk, [&] { return n_ > 0 || closed_; }); if (closed_) return false; n_--; return true; }
+    void release() { std::lock_guard<std::mutex> lk(m_); n_++; cv_.notify_one(); }
+    void close() { std::lock_guard<std::mutex> lk(m_); closed_ = true; cv_.notify_all(); }
+private:
+    std::mutex m_;
+    std::condition_variable cv_;
+    size_t n_;
+    bool closed_ = false;
+};
+
+// results of a worker pool, handed on in submission order
+template <typename T>
+class Ordered {
+public:
+    void put(uint64_t seq, T&& v) {
+        std::lock_guard<std::mutex> lk(m_);
+        ready_.emplace(seq, std::move(v));
+        cv_.notify_all();
+    }
+    void finish(uint64_t total) { std::lock_guard<std::mutex> lk(m_); total_ = total; done_ = true; cv_.notify_all(); }
+    void abort() { std::lock_guard<std::mutex> lk(m_); aborted_ = true; cv_.notify_all(); }
+    bool next(T* out) {                                               // false at end of stream / abort
+        std::unique_lock<std::mutex> lk(m_);
+        cv_.wait(lk, [&] { return aborted_ || ready_.count(next_) || (done_ && next_ >= total_); });
+        if (aborted_ || !ready_.count(next_)) return false;
+        auto it = ready_.find(next_);
+        *out = std::move(it->second);
+        ready_.erase(it);
+        next_++;
+        return true;
+    }
+private:
+    std::mutex m_;
+    std::condition_variable cv_;
+    std::map<uint64_t, T> ready_;
+    uint64_t next_ = 0, total_ = 0;
+    bool done_ = false, aborted_ = false;
+};
+
+// fixed pool of worker threads running queued tasks; a task's exception is kept and re-thrown by wait_idle() / the destructor's caller
+class TaskPool {
+public:
+    explicit TaskPool(int n) {
+        for (int i = 0; i < std::max(1, n); i++) th_.emplace_back([this] { run(); });
+    }
+    ~TaskPool() {
+        { std::lock_guard<std::mutex> lk(m_); stop_ = true; cv_.notify_all(); }
+        for (auto& t : th_) t.join();
+    }
+    void submit(std::function<void()> fn) {
+        std::unique_lock<std::mutex> lk(m_);
+        cv_room_.wait(lk, [&] { return q_.size() < 4 * th_.size() + 4; });   // bounded: the producer waits instead of piling up memory
+        q_.push_back(std::move(fn));
+        cv_.notify_one();
+    }
+    bool failed() { std::lock_guard<std::mutex> lk(m_); return (bool)failed_; }
+private:
+    void run() {
+        for (;;) {
+            std::function<void()> fn;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [&] { return stop_ || !q_.empty(); });
+                if (q_.empty()) return;
+                fn = std::move(q_.front());
+                q_.pop_front();
+                cv_room_.notify_one();
+            }
+            try { fn(); } catch (...) { std::lock_guard<std::mutex> lk(m_); if (!failed_) failed_ = std::current_exception(); }
+        }
+    }
+    std::mutex m_;
+    std::condition_variable cv_, cv_room_;
+    std::deque<std::function<void()>> q_;
+    std::vector<std::thread> th_;
+    std::exception_ptr failed_;
+    bool stop_ = false;
+};
+
+// Reads fastX text from `in` (plain or gzip), cuts it into pieces of whole records, parses the pieces on `pool` and hands
+// them to on_piece(ParsedPiece&) IN FILE ORDER on the calling thread; on_piece returns false to stop early.  At most
+// `max_in_flight` pieces exist at a time.  *read_busy accumulates the reader thread's busy seconds.
+template <typename OnPiece>
+void parallel_fastx(gzFile in, TaskPool& pool, size_t max_in_flight, OnPiece&& on_piece, double* read_busy, bool* fatal) {
+    const size_t kPiece = 4u << 20;                                    // text per parse task
+    Ordered<ParsedPiece> parsed;
+    Tokens in_flight(max_in_flight);
+    std::atomic<uint64_t> parse_busy_us{0};
+    Recycler<std::vector<uint8_t>> texts;
+    Recycler<ParsedPiece> pieces;
+    double consume_busy = 0, consume_wait = 0, emit_s = 0;
+    std::thread t_read([&] { stage_guard(fatal, [&] {
+        std::vector<uint8_t> buf;
+        uint64_t seq = 0;
+        int fmt = 0;
+        bool eof = false;
+        auto emit = [&](size_t n) {                                   // buf[0, n) holds whole records
+            if (n == 0) return;
+            if (!in_flight.acquire()) { eof = true; buf.clear(); return; }
+            auto text = std::make_shared<std::vector<uint8_t>>(texts.get());
+            text->assign(buf.begin(), buf.begin() + n);
+            const uint64_t my = seq++;
+            pool.submit([text, my, &parsed, &parse_busy_us, &texts, &pieces] {
+                const double p0 = now_s();
+                ParsedPiece pp = pieces.get();
+                pp.bases.clear(); pp.lens.clear(); pp.err = 0;
+                parse_piece(text->data(), text->size(), &pp);
+                parse_busy_us += (uint64_t)((now_s() - p0) * 1e6);
+                parsed.put(my, std::move(pp));
+                texts.put(std::move(*text));
+            });
+            buf.erase(buf.begin(), buf.begin() + n);
+        };
+        size_t searched = 0;                                           // buf[0, searched) holds no usable cut
+        while (!eof) {
+            const double t0 = now_s();
+            const size_t at = buf.size();
+            buf.resize(at + kPiece);
+            int got = gzread(in, buf.data() + at, (unsigned)kPiece);
+            if (got <= 0) { got = 0; eof = true; }
+            buf.resize(at + (size_t)got);
+            if (!fmt) for (uint8_t c : buf) if (c != '\n' && c != '\r' && c != ' ') { fmt = c; break; }
+            if (fmt && fmt != '>' && fmt != '@') {                     // not fastX: let the parser report it
+                if (read_busy) *read_busy += now_s() - t0;
+                break;
+            }
+            if (!eof && fmt && buf.size() >= kPiece) {
+                const size_t cut = last_record_start(buf.data(), buf.size(), searched, fmt);
+                const double e0 = now_s();
+                if (cut) { emit(cut); searched = 0; } else searched = buf.size() > 1 ? buf.size() - 1 : 0;
+                emit_s += now_s() - e0;
+            }
+            if (read_busy) *read_busy += now_s() - t0;
+        }
+        emit(buf.size());
+        parsed.finish(seq);
+    }, [&] { parsed.abort(); }); });
+    ParsedPiece pp;
+    for (;;) {
+        const double w0 = now_s();
+        if (!parsed.next(&pp)) break;
+        const double w1 = now_s();
+        in_flight.release();
+        const bool go = on_piece(pp);
+        pieces.put(std::move(pp));
+        consume_wait += w1 - w0;
+        consume_busy += now_s() - w1;
+        if (!go) break;
+    }
+    parsed.abort();
+    in_flight.close();
+    t_read.join();
+    if (getenv("NTC_TRACE"))
+        fprintf(stderr, "[ntc trace] fastx: parse tasks %.3f s (sum over workers), in-order consumer busy %.3f s / waiting %.3f s, reader hand-over %.3f s\n",
+                parse_busy_us.load() * 1e-6, consume_busy, consume_wait, emit_s);
+}
 
 // one GPU call's worth of reads / one group of blocks travelling through the stages
 struct ReadBatch {
     std::vector<uint8_t> bases;
     std::vector<uint64_t> offsets;   // n_reads + 1
-    int err = 0;                     // reader error (malformed input)
+    int err = 0;                     // reader error (1 malformed input, 2 read too long)
 };
 struct BytesBatch {
     std::vector<std::vector<uint8_t>> parts;   // written in order
     int32_t rc = NTC_OK;
     std::string msg;
+};
+struct CodedBatch {                  // what ntc_encode_columns returned for one ReadBatch
+    std::vector<ntc_coded_block> blocks;
+    std::vector<uint64_t> words;
 };
 
 }  // namespace
@@ -251,138 +458,176 @@ struct BytesBatch {
 extern "C" {
 
 // `ntcomp encode` (src/main.rs:141-181): 32-byte zero file header, then one block per 65,536 reads.
+// Stages: reader (inflate / read + cut at record boundaries) -> parse pool -> batch assembly -> the hot path + column codec
+// on the GPU (this thread; records never leave HBM) -> gzip + headers per block on the pool -> in-order writer.
 // stats (optional): [0] reads, [1] bases, [2] records, [3] bytes written, [4] blocks written,
 // [5] blocks dropped because a column was empty (the reference drops them too: src/main.rs:170, Q4).
 int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_path, int32_t n_threads, uint64_t* stats) {
     if (!ctx || !fastx_path) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
     if (n_threads <= 0) n_threads = (int32_t)std::max(1u, std::thread::hardware_concurrency());
-    auto reader = std::make_shared<FastxReader>();
-    if (!reader->open(fastx_path)) { set_error(std::string("cannot open ") + fastx_path); return NTC_ERR_IO; }
+    gzFile in = (strcmp(fastx_path, "-") == 0) ? gzdopen(0, "rb") : gzopen(fastx_path, "rb");
+    if (!in) { set_error(std::string("cannot open ") + fastx_path); return NTC_ERR_IO; }
+    gzbuffer(in, 1 << 20);
     Sink sink;
-    if (!sink.open(out_path)) { set_error(std::string("cannot open ") + (out_path ? out_path : "-")); return NTC_ERR_IO; }
+    if (!sink.open(out_path)) { gzclose(in); set_error(std::string("cannot open ") + (out_path ? out_path : "-")); return NTC_ERR_IO; }
     uint64_t st[6] = {0, 0, 0, 0, 0, 0};
     const uint8_t file_header[32] = {0};                               // encode_file_header(0,0,0,0), src/main.rs:154
-    if (!sink.write(file_header, 32)) { set_error("write failed"); return NTC_ERR_IO; }
+    if (!sink.write(file_header, 32)) { gzclose(in); set_error("write failed"); return NTC_ERR_IO; }
     st[3] = 32;
 
     const uint64_t kBatchBlocks = batch_blocks();
-    Channel<ReadBatch> parsed(2);
-    Channel<BytesBatch> coded(2);
-    double t_stage[4] = {0, 0, 0, 0};                                  // busy seconds: parse, GPU, block container, write
+    double t_stage[5] = {0, 0, 0, 0, 0};                               // busy seconds: read + cut, assemble, GPU, gzip, write
     bool fatal = false;
-    // stage 1: parse
-    std::thread t_read([&] { stage_guard(&fatal, [&] {
-        bool eof = false;
-        size_t reserve_bases = 0;
-        while (!eof) {
+    int32_t rc = NTC_OK;
+    std::string msg;
+    {
+    TaskPool pool(n_threads);
+    Channel<ReadBatch> batches(2);
+    Channel<ReadBatch> spare(8);                                       // used batch buffers on their way back to the assembler
+    Channel<CodedBatch> coded(2);
+    Channel<BytesBatch> bytes(2);
+
+    // stage 2: parsed pieces, in order -> batches of whole 65,536-read blocks
+    std::thread t_batch([&] { stage_guard(&fatal, [&] {
+        ReadBatch b;
+        b.offsets.push_back(0);
+        bool stopped = false;
+        auto fresh = [&]() { ReadBatch n; spare.try_pop(&n); n.bases.clear(); n.offsets.clear(); n.offsets.push_back(0); n.err = 0; return n; };
+        // hands on the whole blocks of b (everything when last); the reads beyond the last block boundary move to the next buffer
+        auto flush = [&](bool last) -> bool {
+            const uint64_t n = b.offsets.size() - 1;
+            const uint64_t take = last ? n : n / kBlockReads * kBlockReads;
+            if (take == 0 && !(last && b.err)) return true;
+            ReadBatch rest = fresh();
+            const uint64_t nb = b.offsets[take];
+            rest.bases.assign(b.bases.begin() + nb, b.bases.end());
+            for (uint64_t r = take + 1; r <= n; r++) rest.offsets.push_back(b.offsets[r] - nb);
+            b.bases.resize(nb);
+            b.offsets.resize(take + 1);
+            ReadBatch out = std::move(b);
+            b = std::move(rest);
+            return batches.push(std::move(out));
+        };
+        // stage 1 lives inside parallel_fastx: read (inflate), cut at record boundaries, parse on the pool
+        parallel_fastx(in, pool, (size_t)n_threads * 3 + 8, [&](ParsedPiece& pp) -> bool {
             const double t0 = now_s();
-            ReadBatch b;
-            b.bases.reserve(reserve_bases);
-            b.offsets.reserve(kBatchBlocks * kBlockReads + 1);
-            b.offsets.push_back(0);
-            while (b.offsets.size() - 1 < kBatchBlocks * kBlockReads && b.bases.size() < kBatchBases) {
-                int r = reader->next(&b.bases);
-                if (r == 0) { eof = true; break; }
-                if (r < 0) { b.err = 1; eof = true; break; }
-                b.offsets.push_back(b.bases.size());
+            if (pp.err && !b.err) b.err = pp.err;
+            const uint64_t base0 = b.bases.size();
+            b.bases.insert(b.bases.end(), pp.bases.begin(), pp.bases.end());
+            uint64_t at = base0;
+            for (uint32_t l : pp.lens) { at += l; b.offsets.push_back(at); }
+            bool ok = true;
+            if (b.err) { ok = flush(true); stopped = true; t_stage[1] += now_s() - t0; return false; }
+            if (b.offsets.size() - 1 >= kBatchBlocks * kBlockReads || b.bases.size() >= kBatchBases) ok = flush(false);
+            t_stage[1] += now_s() - t0;
+            if (!ok) stopped = true;
+            return ok;
+        }, &t_stage[0], &fatal);
+        if (!stopped) flush(true);
+        batches.finish();
+    }, [&] { batches.finish(); }); });
+
+    // stage 4: gzip + headers per block on the pool (this thread only dispatches and collects, in order)
+    std::thread t_code([&] { stage_guard(&fatal, [&] {
+        CodedBatch cb;
+        while (coded.pop(&cb)) {
+            const double t0 = now_s();
+            const size_t n_blocks = cb.blocks.size();
+            auto out = std::make_shared<BytesBatch>();
+            out->parts.resize(n_blocks);
+            auto brc = std::make_shared<std::vector<int32_t>>(n_blocks, NTC_OK);
+            auto shared = std::make_shared<CodedBatch>(std::move(cb));
+            struct Latch { std::mutex m; std::condition_variable cv; size_t done = 0; };
+            auto latch = std::make_shared<Latch>();
+            for (size_t j = 0; j < n_blocks; j++)
+                pool.submit([j, out, brc, shared, latch] {
+                    const ntc_coded_block& blk = shared->blocks[j];
+                    int32_t r = blk.status;
+                    if (r == NTC_OK) {
+                        uint64_t n_w = 0;
+                        for (int q = 0; q < 4; q++) n_w += blk.col[q].n_words;
+                        std::vector<uint8_t>& buf = out->parts[j];
+                        buf.resize(4 * 32 + 4 * 64 + n_w * 8 + n_w / 100 + 1024);
+                        uint64_t nb = 0;
+                        r = ntc_block_assemble(&blk, shared->words.data(), buf.data(), buf.size(), &nb);
+                        buf.resize(r == NTC_OK ? nb : 0);
+                    }
+                    (*brc)[j] = r;
+                    std::lock_guard<std::mutex> lk(latch->m);
+                    latch->done++;
+                    latch->cv.notify_all();
+                });
+            { std::unique_lock<std::mutex> lk(latch->m); latch->cv.wait(lk, [&] { return latch->done == n_blocks; }); }
+            for (size_t j = 0; j < n_blocks; j++) {
+                if ((*brc)[j] == NTC_OK) st[4]++;
+                else if ((*brc)[j] == NTC_ERR_EMPTY_COLUMN) st[5]++;   // dropped, as the reference does (Q4)
+                else { out->rc = (*brc)[j]; out->msg = "block container failed"; }
             }
-            // every batch but the last holds whole 65,536-read blocks: one that stopped on the base budget
-            // is filled up to the next block boundary
-            while (!eof && (b.offsets.size() - 1) % kBlockReads != 0) {
-                int r = reader->next(&b.bases);
-                if (r == 0) { eof = true; break; }
-                if (r < 0) { b.err = 1; eof = true; break; }
-                b.offsets.push_back(b.bases.size());
-            }
-            reserve_bases = b.bases.size() + b.bases.size() / 16;
-            t_stage[0] += now_s() - t0;
-            if (b.offsets.size() > 1 || b.err) { if (!parsed.push(std::move(b))) return; }
+            t_stage[3] += now_s() - t0;
+            if (!bytes.push(std::move(*out))) { coded.close(); return; }
         }
-        parsed.finish();
-    }, [&] { parsed.finish(); }); });
-    // stage 3: write in order
+        bytes.finish();
+    }, [&] { coded.close(); bytes.finish(); }); });
+
+    // stage 5: write in order
     int32_t w_rc = NTC_OK;
     std::string w_msg;
     std::thread t_write([&] { stage_guard(&fatal, [&] {
         BytesBatch bb;
-        while (coded.pop(&bb)) {
-            if (bb.rc != NTC_OK) { w_rc = bb.rc; w_msg = bb.msg; coded.close(); return; }
+        while (bytes.pop(&bb)) {
+            if (bb.rc != NTC_OK) { w_rc = bb.rc; w_msg = bb.msg; bytes.close(); return; }
             const double t0 = now_s();
             for (auto& p : bb.parts) {
-                if (!sink.write(p.data(), p.size())) { w_rc = NTC_ERR_IO; w_msg = "write failed"; coded.close(); return; }
+                if (!sink.write(p.data(), p.size())) { w_rc = NTC_ERR_IO; w_msg = "write failed"; bytes.close(); return; }
                 st[3] += p.size();
             }
-            t_stage[3] += now_s() - t0;
+            t_stage[4] += now_s() - t0;
         }
-    }, [&] { coded.close(); }); });
-    // stage 3: the block container per 65,536-read block on the pool (its own thread, so the GPU works on the
-    // next batch meanwhile)
-    struct RecordBatch { std::unique_ptr<uint64_t[]> records; std::vector<uint64_t> rec_off; uint64_t n_reads = 0; };
-    Channel<RecordBatch> encoded(2);
-    std::thread t_code([&] { stage_guard(&fatal, [&] {
-        RecordBatch rb;
-        while (encoded.pop(&rb)) {
-            const uint64_t n = rb.n_reads, n_blocks = (n + kBlockReads - 1) / kBlockReads;
-            BytesBatch out;
-            out.parts.resize(n_blocks);
-            std::vector<int32_t> brc(n_blocks, NTC_OK);
-            const double t0 = now_s();
-            parallel_for(n_blocks, n_threads, [&](uint64_t j) {
-                const uint64_t lo = j * kBlockReads, hi = std::min(n, lo + kBlockReads);
-                const uint64_t r0 = rb.rec_off[lo], r1 = rb.rec_off[hi];
-                std::vector<uint8_t>& buf = out.parts[j];
-                buf.resize(ntc_block_bound(r1 - r0));
-                uint64_t nb = 0;
-                // src/main.rs:170,176: num_records = the block size argument (65,536, or the tail count)
-                brc[j] = ntc_block_write(rb.records.get() + r0, r1 - r0, hi - lo, buf.data(), buf.size(), &nb);
-                buf.resize(brc[j] == NTC_OK ? nb : 0);
-            });
-            t_stage[2] += now_s() - t0;
-            for (uint64_t j = 0; j < n_blocks; j++) {
-                if (brc[j] == NTC_OK) st[4]++;
-                else if (brc[j] == NTC_ERR_EMPTY_COLUMN) st[5]++;       // dropped, as the reference does (Q4)
-                else { out.rc = brc[j]; out.msg = "block container failed"; }
-            }
-            if (!coded.push(std::move(out))) { encoded.close(); return; }
-        }
-        coded.finish();
-    }, [&] { encoded.close(); coded.finish(); }); });
-    // stage 2 (this thread): the hot path on the GPU
-    int32_t rc = NTC_OK;
-    std::string msg;
+    }, [&] { bytes.close(); }); });
+
+    // stage 3 (this thread): the hot path + the column codec on the GPU
     ReadBatch b;
-    while (parsed.pop(&b)) {
-        if (b.err) { rc = NTC_ERR_IO; msg = "malformed fastX record near read " + std::to_string(st[0] + b.offsets.size()); break; }
+    while (batches.pop(&b)) {
         const uint64_t n = b.offsets.size() - 1;
-        RecordBatch rb;
-        rb.n_reads = n;
-        rb.rec_off.resize(n + 1);
-        // one record per base is the worst case (ntc_encode_bound); typical streams hold one per ~35 bases, so start
-        // with a sixth of that and fall back to the bound -- the buffers are plain arrays, not zero-filled vectors
-        uint64_t n_rec = 0;
-        const double t0 = now_s();
-        for (uint64_t cap = std::max<uint64_t>(b.bases.size() / 6, 1024);; cap = std::max<uint64_t>(b.bases.size(), 1)) {
-            rb.records.reset(new uint64_t[cap]);
-            rc = ntc_encode_batch(ctx, b.bases.data(), b.offsets.data(), n, rb.records.get(), cap, &n_rec, rb.rec_off.data());
-            if (rc != NTC_ERR_CAPACITY || cap >= b.bases.size()) break;
+        if (n) {
+            const double t0 = now_s();
+            CodedBatch cb;
+            cb.blocks.resize((n + kBlockReads - 1) / kBlockReads);
+            uint64_t n_blocks = 0, n_words = 0, n_rec = 0;
+            const uint64_t* words = nullptr;
+            rc = ntc_encode_columns(ctx, b.bases.data(), b.offsets.data(), n, kBlockReads, cb.blocks.data(), cb.blocks.size(), &n_blocks, &words,
+                                    &n_words, &n_rec);
+            if (rc == NTC_OK) cb.words.assign(words, words + n_words);   // the pinned buffer is reused by the call after next
+            t_stage[2] += now_s() - t0;
+            if (rc != NTC_OK) { msg = ntc_last_error(); break; }
+            st[0] += n; st[1] += b.bases.size(); st[2] += n_rec;
+            if (!coded.push(std::move(cb))) break;
         }
-        t_stage[1] += now_s() - t0;
-        if (rc != NTC_OK) { msg = ntc_last_error(); break; }
-        st[0] += n; st[1] += b.bases.size(); st[2] += n_rec;
-        if (!encoded.push(std::move(rb))) break;
+        const int berr = b.err;
+        spare.push(std::move(b));                                      // the buffer goes back to the assembler with its capacity
+        b = ReadBatch();
+        if (berr) {
+            rc = berr == 2 ? NTC_ERR_UNSUPPORTED : NTC_ERR_IO;
+            msg = berr == 2 ? "a read of 2^32 bases or more is not supported" : "malformed fastX record near read " + std::to_string(st[0] + 1);
+            break;
+        }
     }
-    parsed.close();
-    encoded.finish();
-    t_read.join();
+    batches.close();
+    spare.close();
+    coded.finish();
+    t_batch.join();
     t_code.join();
     t_write.join();
+    if (pool.failed()) fatal = true;
+    if (rc == NTC_OK && w_rc != NTC_OK) { rc = w_rc; msg = w_msg; }
+    }
+    gzclose(in);
     sink.close();
     if (getenv("NTC_TRACE"))
-        fprintf(stderr, "[ntc trace] encode_file busy seconds: parse %.3f, gpu %.3f, block container %.3f, write %.3f\n", t_stage[0], t_stage[1],
-                t_stage[2], t_stage[3]);
+        fprintf(stderr, "[ntc trace] encode_file busy seconds: read+cut %.3f, assemble %.3f, gpu %.3f, gzip %.3f, write %.3f\n", t_stage[0],
+                t_stage[1], t_stage[2], t_stage[3], t_stage[4]);
     if (stats) memcpy(stats, st, sizeof(st));
     if (rc != NTC_OK) { set_error(msg); return rc; }
-    if (w_rc != NTC_OK) { set_error(w_msg); return w_rc; }
     if (fatal) { set_error("out of memory or internal error in a pipeline stage"); return NTC_ERR_IO; }
     return NTC_OK;
 }
@@ -390,6 +635,8 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
 
 // `ntcomp decode` (src/main.rs:183-211): 32-byte file header, then blocks until the first header that
 // cannot be read (src/lib.rs:327); FASTA records ">seq.N" numbered from 1 across blocks.
+// Stages: reader (frames the four sub-blocks of every block) -> gunzip per block on the pool -> the column codec + decode on
+// the GPU (this thread; records never leave HBM) -> in-order writer straight from the library's pinned text buffers.
 // stats (optional): [0] sequences, [1] bases + header bytes written, [2] records, [3] bytes read, [4] blocks.
 int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path, int32_t n_threads, uint64_t* stats) {
     if (!ctx || !in_path) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
@@ -404,14 +651,24 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
     st[3] = 32;
 
     const uint64_t kBatchBlocks = batch_blocks();
-    struct RecBatch { std::vector<uint64_t> records; uint64_t n_blocks = 0; int32_t rc = NTC_OK; std::string msg; };
-    Channel<RecBatch> unpacked(2);
-    Channel<BytesBatch> texts(2);
+    struct ColBatch { std::vector<ntc_coded_block> blocks; std::vector<uint64_t> words; int32_t rc = NTC_OK; std::string msg; };
+    struct TextRef { const uint8_t* p; uint64_t n; };
     bool fatal = false;
-    // stage 1: frame the blocks of a group, then gunzip + decode + zip them on the pool
+    int32_t rc = NTC_OK;
+    std::string msg;
+    double t_stage[3] = {0, 0, 0};                                     // busy seconds: read + gunzip, GPU, write
+    {
+    Channel<ColBatch> unpacked(2);
+    Channel<TextRef> texts(1);
+    std::mutex wm;
+    std::condition_variable wcv;
+    uint64_t written = 0;                                              // batches the writer is done with
+    bool writer_gone = false;
+    // stage 1: frame the blocks of a group, then headers + gunzip on the pool
     std::thread t_read([&] { stage_guard(&fatal, [&] {
         bool eof = false;
         while (!eof) {
+            const double t0 = now_s();
             std::vector<std::vector<uint8_t>> raw;
             uint64_t payload = 0;
             while (raw.size() < kBatchBlocks && payload < (256ull << 20)) {
@@ -440,108 +697,152 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
                 raw.push_back(std::move(blk));
             }
             if (raw.empty()) break;
-            RecBatch rb;
-            rb.n_blocks = raw.size();
-            std::vector<std::vector<uint64_t>> recs(raw.size());
-            std::vector<int32_t> brc(raw.size(), NTC_OK);
-            std::vector<std::string> bmsg(raw.size());
-            parallel_for(raw.size(), n_threads, [&](uint64_t j) {
-                // a block holds at most one record per coded flag: num_u64 of the flags column (3rd sub-block)
-                uint64_t pos = 0, cap = 0;
+            ColBatch cb;
+            const size_t nb = raw.size();
+            cb.blocks.resize(nb);
+            std::vector<std::vector<uint64_t>> words(nb);
+            std::vector<int32_t> brc(nb, NTC_OK);
+            std::vector<std::string> bmsg(nb);
+            parallel_for(nb, n_threads, [&](uint64_t j) {
+                uint64_t cap = 0, pos = 0;                              // encoded_size of the four headers
                 for (int q = 0; q < 4; q++) {
-                    uint32_t bs, nu;
+                    uint32_t bs, es;
                     memcpy(&bs, raw[j].data() + pos, 4);
-                    memcpy(&nu, raw[j].data() + pos + 8, 4);
-                    if (q == 2) cap = nu;
+                    memcpy(&es, raw[j].data() + pos + 12, 4);
+                    cap += std::min<uint64_t>(es, (uint64_t)bs * 1100 + 64);   // a gzip member cannot expand more than ~1032 : 1
                     pos += 32 + bs;
                 }
-                recs[j].resize(std::max<uint64_t>(cap, 1));
-                uint64_t n_rec = 0, used = 0;
-                brc[j] = ntc_block_read_ex(raw[j].data(), raw[j].size(), recs[j].data(), recs[j].size(), &n_rec, &used,
-                                           NTC_BLOCK_FULL_LAST_LITERAL_WORD);   // Q5: the reference panics on 1 block in 31
+                words[j].resize(cap + 8);
+                uint64_t nw = 0, used = 0;
+                brc[j] = ntc_block_disassemble(raw[j].data(), raw[j].size(), &cb.blocks[j], words[j].data(), words[j].size(), &nw, &used);
                 if (brc[j] != NTC_OK) bmsg[j] = ntc_last_error();
-                recs[j].resize(brc[j] == NTC_OK ? n_rec : 0);
+                words[j].resize(brc[j] == NTC_OK ? nw : 0);
             });
-            for (size_t j = 0; j < raw.size(); j++) {
-                if (brc[j] != NTC_OK && rb.rc == NTC_OK) { rb.rc = brc[j]; rb.msg = bmsg[j]; }
-                // the reference decodes every block by itself (decode_block -> decode_sequence, src/lib.rs:363-365): records
-                // in front of a block's first `first` flag belong to no sequence and are dropped (src/lib.rs:308-317) --
-                // they must not be glued to the previous block's last sequence when blocks are concatenated here
-                size_t skip = 0;
-                while (skip < recs[j].size() && ((recs[j][skip] >> 56) & 1u) == 0) skip++;
-                rb.records.insert(rb.records.end(), recs[j].begin() + skip, recs[j].end());
+            uint64_t at = 0;
+            for (size_t j = 0; j < nb; j++) {
+                if (brc[j] != NTC_OK && cb.rc == NTC_OK) { cb.rc = brc[j] == NTC_ERR_CAPACITY ? NTC_ERR_IO : brc[j]; cb.msg = bmsg[j]; }
+                for (int q = 0; q < 4; q++) cb.blocks[j].col[q].word_offset += at;
+                at += words[j].size();
                 st[3] += raw[j].size();
             }
-            if (!unpacked.push(std::move(rb))) return;
+            cb.words.reserve(at);
+            for (size_t j = 0; j < nb; j++) cb.words.insert(cb.words.end(), words[j].begin(), words[j].end());
+            t_stage[0] += now_s() - t0;
+            if (!unpacked.push(std::move(cb))) return;
         }
         unpacked.finish();
     }, [&] { unpacked.finish(); }); });
     int32_t w_rc = NTC_OK;
     std::string w_msg;
     std::thread t_write([&] { stage_guard(&fatal, [&] {
-        BytesBatch bb;
-        while (texts.pop(&bb))
-            for (auto& p : bb.parts)
-                if (!sink.write(p.data(), p.size())) { w_rc = NTC_ERR_IO; w_msg = "write failed"; texts.close(); return; }
-    }, [&] { texts.close(); }); });
-    // stage 2 (this thread): decode_sequence + FASTA text on the GPU
-    int32_t rc = NTC_OK;
-    std::string msg;
-    RecBatch rb;
-    while (unpacked.pop(&rb)) {
-        if (rb.rc != NTC_OK) { rc = rb.rc; msg = rb.msg; break; }
-        st[4] += rb.n_blocks;
-        st[2] += rb.records.size();
-        if (rb.records.empty()) continue;
-        uint64_t n_bases = 0, n_seqs = 0, fasta_bytes = 0;
-        ntc_decode_bound(rb.records.data(), rb.records.size(), st[0] + 1, &n_bases, &n_seqs, &fasta_bytes);
-        BytesBatch out;
-        out.parts.resize(1);
-        out.parts[0].resize(fasta_bytes + 64);
-        uint64_t nb = 0, ns = 0;
-        rc = ntc_decode_fasta(ctx, rb.records.data(), rb.records.size(), st[0] + 1, out.parts[0].data(), fasta_bytes, &nb, &ns);
+        TextRef tr;
+        while (texts.pop(&tr)) {
+            const double t0 = now_s();
+            const bool ok = sink.write(tr.p, tr.n);
+            t_stage[2] += now_s() - t0;
+            { std::lock_guard<std::mutex> lk(wm); written++; wcv.notify_all(); }
+            if (!ok) { w_rc = NTC_ERR_IO; w_msg = "write failed"; texts.close(); { std::lock_guard<std::mutex> lk(wm); writer_gone = true; wcv.notify_all(); } return; }
+        }
+        { std::lock_guard<std::mutex> lk(wm); writer_gone = true; wcv.notify_all(); }
+    }, [&] { { std::lock_guard<std::mutex> lk(wm); writer_gone = true; wcv.notify_all(); } texts.close(); }); });
+    // stage 2 (this thread): integer decoders + zip + decode_sequence + FASTA text on the GPU
+    ColBatch cb;
+    uint64_t pushed = 0;
+    while (unpacked.pop(&cb)) {
+        if (cb.rc != NTC_OK) { rc = cb.rc; msg = cb.msg; break; }
+        st[4] += cb.blocks.size();
+        // the text of call i lives in a pinned buffer that call i + 2 reuses: wait until the writer is done with it
+        if (pushed >= 2) { std::unique_lock<std::mutex> lk(wm); wcv.wait(lk, [&] { return writer_gone || written + 2 > pushed; }); }
+        const double t0 = now_s();
+        const uint8_t* text = nullptr;
+        uint64_t nb = 0, ns = 0, nr = 0;
+        rc = ntc_decode_columns_fasta(ctx, cb.blocks.data(), cb.blocks.size(), cb.words.data(), cb.words.size(), st[0] + 1,
+                                      NTC_BLOCK_FULL_LAST_LITERAL_WORD, &text, &nb, &ns, &nr);   // Q5: the reference panics on 1 block in 31
+        t_stage[1] += now_s() - t0;
         if (rc != NTC_OK) { msg = ntc_last_error(); break; }
-        out.parts[0].resize(nb);
         st[0] += ns;
         st[1] += nb;
-        if (!texts.push(std::move(out))) break;
+        st[2] += nr;
+        if (nb) {
+            if (!texts.push(TextRef{text, nb})) break;
+            pushed++;
+        }
     }
     unpacked.close();
     texts.finish();
     t_read.join();
     t_write.join();
+    if (rc == NTC_OK && w_rc != NTC_OK) { rc = w_rc; msg = w_msg; }
+    }
     sink.close();
     if (in != stdin) fclose(in);
+    if (getenv("NTC_TRACE"))
+        fprintf(stderr, "[ntc trace] decode_file busy seconds: read+gunzip %.3f, gpu %.3f, write %.3f\n", t_stage[0], t_stage[1], t_stage[2]);
     if (stats) memcpy(stats, st, sizeof(st));
     if (rc != NTC_OK) { set_error(msg); return rc; }
-    if (w_rc != NTC_OK) { set_error(w_msg); return w_rc; }
     if (fatal) { set_error("out of memory or internal error in a pipeline stage"); return NTC_ERR_IO; }
     return NTC_OK;
 }
 
+
+// fastX file (plain or gzip; FASTA or FASTQ) -> normalised sequences, parsed the way the encode pipeline does it (reader thread
+// cutting at record boundaries + parse pool).  *bases / *offsets are malloc'ed: release them with ntc_free.
+int32_t ntc_fastx_load(const char* path, int32_t n_threads, uint8_t** bases_out, uint64_t** offsets_out, uint64_t* n_reads, uint64_t* n_bases) {
+    if (!path || !bases_out || !offsets_out || !n_reads) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    *bases_out = nullptr; *offsets_out = nullptr; *n_reads = 0;
+    if (n_bases) *n_bases = 0;
+    if (n_threads <= 0) n_threads = (int32_t)std::max(1u, std::thread::hardware_concurrency());
+    gzFile in = (strcmp(path, "-") == 0) ? gzdopen(0, "rb") : gzopen(path, "rb");
+    if (!in) { set_error(std::string("cannot open ") + path); return NTC_ERR_IO; }
+    gzbuffer(in, 1 << 20);
+    std::vector<uint8_t> bases;
+    std::vector<uint64_t> off(1, 0);
+    int err = 0;
+    bool fatal = false;
+    try {
+        TaskPool pool(n_threads);
+        parallel_fastx(in, pool, (size_t)n_threads * 3 + 8, [&](ParsedPiece& pp) -> bool {
+            bases.insert(bases.end(), pp.bases.begin(), pp.bases.end());
+            uint64_t at = off.back();
+            for (uint32_t l : pp.lens) { at += l; off.push_back(at); }
+            if (pp.err) { err = pp.err; return false; }
+            return true;
+        }, nullptr, &fatal);
+        if (pool.failed()) fatal = true;
+    } catch (...) { fatal = true; }
+    gzclose(in);
+    if (fatal) { set_error("out of memory or internal error while parsing"); return NTC_ERR_IO; }
+    if (err) { set_error(err == 2 ? std::string("a read of 2^32 bases or more in ") + path : std::string("malformed fastX record in ") + path + " near record " + std::to_string(off.size())); return err == 2 ? NTC_ERR_UNSUPPORTED : NTC_ERR_IO; }
+    uint8_t* b = (uint8_t*)malloc(bases.size() + 1);
+    uint64_t* o = (uint64_t*)malloc(off.size() * 8);
+    if (!b || !o) { free(b); free(o); set_error("out of memory"); return NTC_ERR_IO; }
+    if (!bases.empty()) memcpy(b, bases.data(), bases.size());
+    memcpy(o, off.data(), off.size() * 8);
+    *bases_out = b; *offsets_out = o; *n_reads = off.size() - 1;
+    if (n_bases) *n_bases = bases.size();
+    return NTC_OK;
+}
+void ntc_free(void* p) { free(p); }
 
 // `ntcomp build` front end (src/main.rs:97-134): every record of every fastX file is one input sequence of
 // kbo::build (add_revcomp = true there).  Construction itself is ntc_index_build (host, offline).
 int32_t ntc_index_build_from_files(const char* const* paths, uint64_t n_paths, uint32_t k, int32_t add_revcomp, int32_t n_threads,
                                    ntc_index** out) {
     if (!out || (n_paths && !paths)) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
-    std::vector<uint8_t> bases;
-    std::vector<uint64_t> off(1, 0);
-    for (uint64_t f = 0; f < n_paths; f++) {
-        FastxReader rd;
-        if (!rd.open(paths[f])) { set_error(std::string("cannot open ") + paths[f]); return NTC_ERR_IO; }
-        for (;;) {
-            int r = rd.next(&bases);
-            if (r == 0) break;
-            if (r < 0) { set_error(std::string("malformed fastX record in ") + paths[f]); return NTC_ERR_IO; }
-            off.push_back(bases.size());
-        }
+    std::vector<uint8_t*> fb(n_paths, nullptr);
+    std::vector<uint64_t*> fo(n_paths, nullptr);
+    std::vector<uint64_t> fn(n_paths, 0);
+    int32_t rc = NTC_OK;
+    for (uint64_t f = 0; f < n_paths && rc == NTC_OK; f++) rc = ntc_fastx_load(paths[f], n_threads, &fb[f], &fo[f], &fn[f], nullptr);
+    if (rc == NTC_OK) {
+        std::vector<const uint8_t*> ptrs;
+        std::vector<uint64_t> lens;
+        for (uint64_t f = 0; f < n_paths; f++)
+            for (uint64_t i = 0; i < fn[f]; i++) { ptrs.push_back(fb[f] + fo[f][i]); lens.push_back(fo[f][i + 1] - fo[f][i]); }
+        rc = ntc_index_build(ptrs.data(), lens.data(), ptrs.size(), k, add_revcomp, n_threads, out);
     }
-    const uint64_t n = off.size() - 1;
-    std::vector<const uint8_t*> ptrs(n);
-    std::vector<uint64_t> lens(n);
-    for (uint64_t i = 0; i < n; i++) { ptrs[i] = bases.data() + off[i]; lens[i] = off[i + 1] - off[i]; }
-    return ntc_index_build(ptrs.data(), lens.data(), n, k, add_revcomp, n_threads, out);
+    for (uint64_t f = 0; f < n_paths; f++) { free(fb[f]); free(fo[f]); }
+    return rc;
 }
 
 }  // extern "C"

@@ -61,6 +61,59 @@ def test_build_from_files_matches_in_memory_build(tmp_path, genome_and_reads):
         nt.Index.build_from_files([bad], 31)
 
 
+def _fastx_load(path, n_threads=3):
+    import ctypes as C
+    L = _lib.lib()
+    b, o = C.c_void_p(), C.c_void_p()
+    n, nb = C.c_uint64(0), C.c_uint64(0)
+    rc = L.ntc_fastx_load(str(path).encode(), n_threads, C.byref(b), C.byref(o), C.byref(n), C.byref(nb))
+    if rc:
+        return rc, None
+    bases = np.ctypeslib.as_array(C.cast(b, C.POINTER(C.c_uint8)), shape=(max(nb.value, 1),))[: nb.value].copy()
+    off = np.ctypeslib.as_array(C.cast(o, C.POINTER(C.c_uint64)), shape=(n.value + 1,)).copy()
+    L.ntc_free(b)
+    L.ntc_free(o)
+    return 0, [bytes(bases[int(off[i]): int(off[i + 1])]) for i in range(n.value)]
+
+
+def test_parallel_fastx_parser(tmp_path):
+    """The encode pipeline's front end (reader thread cutting at record boundaries + parse pool, in-order hand-over):
+    files of several pieces, FASTA with wrapped / CRLF / lower-case lines, 4-line FASTQ whose quality lines start with
+    '@', multi-line FASTQ (no safe cut: parsed serially), gzip input, malformed input."""
+    rng = np.random.default_rng(123)
+    seqs = [helpers.random_seq(rng, int(n)) for n in rng.integers(1, 400, size=60000)]       # ~12 MB of sequence: several 4 MB pieces
+    seqs[17] = helpers.random_seq(rng, 5_000_000)                                             # one record longer than a piece
+    want = [bytes(s) for s in seqs]
+    fa = tmp_path / "a.fa"
+    _write_fasta(fa, seqs, width=61, lower=True)
+    assert _fastx_load(fa) == (0, want)
+    assert _fastx_load(fa, 1) == (0, want)
+    fq = tmp_path / "a.fq"
+    _write_fastq(fq, seqs)
+    assert _fastx_load(fq) == (0, want)
+    fqz = tmp_path / "a.fq.gz"
+    _write_fastq(fqz, seqs[:3000], opener=lambda p, m: gzip.open(p, m, compresslevel=1))
+    assert _fastx_load(fqz) == (0, want[:3000])
+    ml = tmp_path / "multi.fq"                                                                 # wrapped FASTQ: sequence and quality over several lines
+    with open(ml, "wb") as f:
+        for i, s in enumerate(seqs[:40000]):
+            b = bytes(s)
+            f.write(b"@r%d\n" % i + b"\n".join(b[j:j + 50] for j in range(0, len(b), 50)) + b"\n+\n" +
+                    b"\n".join(b"@" * len(b[j:j + 50]) for j in range(0, len(b), 50)) + b"\n")
+    assert _fastx_load(ml) == (0, want[:40000])
+    u = tmp_path / "u.fa"
+    u.write_bytes(b">x\nacgu ACGU\tnn\n\n>y\n\n>z\nA")
+    assert _fastx_load(u) == (0, [b"ACGTACGTNN", b"", b"A"])
+    for bad in (b"@r1\nACGT\n+\nII\n", b"@r1\nACGT\n", b"hello\n"):
+        p = tmp_path / "bad.fq"
+        p.write_bytes(bad)
+        assert _fastx_load(p)[0] == 7, bad
+    assert _fastx_load(tmp_path / "missing")[0] == 7
+    e = tmp_path / "empty.fa"
+    e.write_bytes(b"")
+    assert _fastx_load(e) == (0, [])
+
+
 def test_cli_build_and_no_gpu_failure(tmp_path, genome_and_reads):
     contigs, reads = genome_and_reads
     assert os.path.exists(CLI), "ntcomp-b200 is built by make -C ntcomp_b200/csrc"
