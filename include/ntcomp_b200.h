@@ -70,6 +70,12 @@ void ntc_index_free(ntc_index* idx);
 /* ---------------- context (one per GPU) ---------------------------------------------------- */
 
 int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out);
+/* The same, holding only the derived arrays one direction reads (the CLI's encode / decode subcommands; the
+ * reference loads one index for either, src/main.rs:138,185): NTC_USE_ENCODE = rank blocks + LCS words + prefix
+ * table, NTC_USE_DECODE = jump table.  Entry points of the other direction fail with NTC_ERR_UNSUPPORTED. */
+#define NTC_USE_ENCODE 1u
+#define NTC_USE_DECODE 2u
+int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, ntc_ctx** out);
 void ntc_ctx_destroy(ntc_ctx* ctx);
 /* bytes of HBM held by the re-laid-out index: [0]=rank blocks, [1]=LCS, [2]=decode jump table */
 void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]);
@@ -174,6 +180,9 @@ int32_t ntc_encode_columns(ntc_ctx* ctx, const uint8_t* bases, const uint64_t* o
                            uint64_t* n_words, uint64_t* n_records);
 /* four gzip members + 32-byte headers of one block (src/lib.rs:242-250, src/encode.rs:96-127); host only */
 int32_t ntc_block_assemble(const ntc_coded_block* blk, const uint64_t* words, uint8_t* out, uint64_t cap, uint64_t* n_bytes);
+/* One sub-block of the four (0 colex ranks, 1 match lengths, 2 flags, 3 literal words; src/lib.rs:242-250): header + gzip
+ * member.  ntc_block_assemble's output is the concatenation of columns 0..3. */
+int32_t ntc_sub_block_assemble(const ntc_coded_block* blk, int32_t column, const uint64_t* words, uint8_t* out, uint64_t cap, uint64_t* n_bytes);
 /* four headers + gunzip of one block (src/lib.rs:326-355, src/decode.rs:79-91); host only.  *consumed == 0 at EOF. */
 int32_t ntc_block_disassemble(const uint8_t* data, uint64_t size, ntc_coded_block* blk, uint64_t* words, uint64_t cap_words,
                               uint64_t* n_words, uint64_t* consumed);
@@ -197,6 +206,11 @@ int32_t ntc_column_code(const uint64_t* values, uint64_t n, int32_t rice, uint64
  * decode stats[6]: sequences, FASTA bytes written, records, bytes read, blocks, 0.  stats may be NULL. */
 int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_path, int32_t n_threads, uint64_t* stats);
 int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path, int32_t n_threads, uint64_t* stats);
+/* Page-locked host memory for the buffers handed to the host-buffer entry points: copies to and from it run at full
+ * PCIe rate without a staging pass (the file pipeline fills its read batches in such buffers).  Needs a GPU. */
+int32_t ntc_pinned_alloc(uint64_t bytes, void** out);
+void ntc_pinned_free(void* p);
+
 /* fastX file (FASTA / FASTQ, plain or gzip) -> the normalised sequences (needletail normalize(true) for what can reach the
  * encoder, src/main.rs:158-163), parsed like the encode pipeline does: one reader thread cutting at record boundaries,
  * n_threads parsers.  *bases (n_bases bytes) and *offsets (n_reads + 1) are malloc'ed: release with ntc_free. */

@@ -5,5 +5,5 @@ loader (`_lib`), the host-side mirror of the reference interface (`api`), the sy
 SURVEY §8d (`synth`) and read sharding across GPUs (`sharding`).
 """
 from .api import (CodedBlock, CodedColumn, Context, EncodeError, Index, block_assemble, block_disassemble, block_read, block_write,  # noqa: F401
-                  concat_reads, decode_sequence, encode_dictionary, encode_sequence)
+                  concat_reads, decode_sequence, encode_dictionary, encode_sequence, sub_block_assemble)
 from ._lib import NtcError  # noqa: F401

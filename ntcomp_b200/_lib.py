@@ -33,6 +33,9 @@ SIGNATURES = {
     "ntc_index_get_lcs": (None, [_vp, _vp]),
     "ntc_index_free": (None, [_vp]),
     "ntc_ctx_create": (_i32, [_i32, _vp, _pp]),
+    "ntc_ctx_create_for": (_i32, [_i32, _vp, _u32, _pp]),
+    "ntc_pinned_alloc": (_i32, [_u64, _pp]),
+    "ntc_pinned_free": (None, [_vp]),
     "ntc_ctx_destroy": (None, [_vp]),
     "ntc_ctx_index_bytes": (None, [_vp, _vp]),
     "ntc_encode_batch": (_i32, [_vp, _vp, _vp, _u64, _vp, _u64, _vp, _vp]),
@@ -51,6 +54,7 @@ SIGNATURES = {
     "ntc_column_code": (_i32, [_vp, _u64, _i32, _vp, _u64, _vp, _vp]),
     "ntc_encode_columns": (_i32, [_vp, _vp, _vp, _u64, _u64, _vp, _u64, _vp, _vp, _vp, _vp]),
     "ntc_block_assemble": (_i32, [_vp, _vp, _vp, _u64, _vp]),
+    "ntc_sub_block_assemble": (_i32, [_vp, _i32, _vp, _vp, _u64, _vp]),
     "ntc_block_disassemble": (_i32, [_vp, _u64, _vp, _vp, _u64, _vp, _vp]),
     "ntc_decode_columns_fasta": (_i32, [_vp, _vp, _u64, _vp, _u64, _u64, _i32, _vp, _vp, _vp, _vp]),
     "ntc_encode_device": (_i32, [_vp, _vp, _vp, _u64, _u64, _vp, _u64, _vp, _vp, _vp]),

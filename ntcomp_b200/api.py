@@ -135,9 +135,11 @@ class Index:
 class Context:
     """One GPU: index in HBM + workspaces.  Raises NtcError(NTC_ERR_CUDA) when no GPU is present."""
 
-    def __init__(self, index, device=0):
+    USE_ENCODE, USE_DECODE = 1, 2
+
+    def __init__(self, index, device=0, uses=3):
         h = C.c_void_p()
-        check(_lib.lib().ntc_ctx_create(device, index._h, C.byref(h)))
+        check(_lib.lib().ntc_ctx_create_for(device, index._h, uses, C.byref(h)))
         self._h = h
         self.device = device
         self.k = index.k
@@ -367,6 +369,16 @@ def block_assemble(block, words):
     out = np.zeros(cap, dtype=np.uint8)
     nb = C.c_uint64(0)
     check(_lib.lib().ntc_block_assemble(C.byref(block), _ptr(words) if len(words) else None, _ptr(out), cap, C.byref(nb)))
+    return out[: nb.value].tobytes()
+
+
+def sub_block_assemble(block, column, words):
+    """one of the four sub-blocks of block_assemble (0 colex, 1 lengths, 2 flags, 3 literal words): header + gzip member"""
+    words = np.ascontiguousarray(words, dtype=np.uint64)
+    cap = 32 + 64 + (int(block.col[column].n_words) if 0 <= column < 4 else 0) * 9 + 1024
+    out = np.zeros(cap, dtype=np.uint8)
+    nb = C.c_uint64(0)
+    check(_lib.lib().ntc_sub_block_assemble(C.byref(block), column, _ptr(words) if len(words) else None, _ptr(out), cap, C.byref(nb)))
     return out[: nb.value].tobytes()
 
 

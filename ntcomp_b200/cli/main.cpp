@@ -86,8 +86,9 @@ int main(int argc, char** argv) {
     fprintf(stderr, "Loading SBWT index...\n");
     int32_t rc = ntc_index_load(idx_path.c_str(), &idx);
     if (rc) return fail("index load", rc);
+    if (getenv("NTC_TRACE")) fprintf(stderr, "[ntc trace] index file loaded in %.3f s\n", now() - t0);
     ntc_ctx* ctx = nullptr;
-    rc = ntc_ctx_create(device, idx, &ctx);
+    rc = ntc_ctx_create_for(device, idx, cmd == "encode" ? NTC_USE_ENCODE : NTC_USE_DECODE, &ctx);
     ntc_index_free(idx);
     if (rc) return fail("context", rc);
     uint64_t st[6] = {0};

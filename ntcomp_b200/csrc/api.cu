@@ -2,8 +2,10 @@
 // device pipelines, and the host-buffer entry points a Rust/cgo/ctypes caller binds.
 // There is no CPU fallback here: without a GPU every compute entry point returns NTC_ERR_CUDA.
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <exception>
 #include <thread>
 #include <vector>
 
@@ -103,6 +105,7 @@ uint32_t tile_len_for(const ntc_ctx* ctx, uint64_t n_bases) {
 // the items -> record counts of multi-tile reads.  counts may be null (diagnostic entry point).
 int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint64_t* d_offsets, uint64_t n_reads, uint64_t n_bases,
                     uint32_t T, uint64_t* scratch, uint32_t* counts, uint32_t* status, cudaStream_t st, bool keep_records = false) {
+    if (!(ctx->uses & NTC_USE_ENCODE)) { set_error("this context was created without NTC_USE_ENCODE (no rank blocks / LCS words in HBM)"); return NTC_ERR_UNSUPPORTED; }
     const uint64_t max_items = n_reads + n_bases / T;                 // sum over reads of max(1, ceil(len / T)) is at most this
     NTC_CUDA_TRY(ensure(&lane.tile_off, (n_reads + 2) * 8 + 16));
     NTC_CUDA_TRY(ensure(&lane.desc, (max_items + 1) * 8));
@@ -221,6 +224,7 @@ int32_t decode_prepare(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint
 int32_t decode_walk(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* d_out,
                     uint64_t cap, const uint64_t* d_counts, cudaStream_t st) {
     if (n_rec == 0) return NTC_OK;
+    if (!(ctx->uses & NTC_USE_DECODE)) { set_error("this context was created without NTC_USE_DECODE (no jump table in HBM)"); return NTC_ERR_UNSUPPORTED; }
     {
         // (a two-pass variant -- walk to 2-bit slots per record, then one thread per sequence formatting header + bases
         // left to right -- measured slower on B200: 3.31 vs 2.56 ms on C3, 9.6 vs 6.0 ms on C5; r1 A/B, profiles/r1)
@@ -262,10 +266,56 @@ void free_column_work(ntc_ctx* ctx);
 extern "C" {
 
 int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
+    return ntc_ctx_create_for(device, idx, NTC_USE_ENCODE | NTC_USE_DECODE, out);
+}
+
+int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, ntc_ctx** out) {
     if (!idx || !out) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
     *out = nullptr;
+    if ((uses & (NTC_USE_ENCODE | NTC_USE_DECODE)) == 0 || (uses & ~(uint32_t)(NTC_USE_ENCODE | NTC_USE_DECODE))) {
+        set_error("uses must be NTC_USE_ENCODE, NTC_USE_DECODE or both");
+        return NTC_ERR_INVALID_ARG;
+    }
+    const bool trace = getenv("NTC_TRACE") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
+    auto since = [&]() { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); };
+    // The derived HBM layouts are built on the host cores WHILE the CUDA context comes up on another thread (the
+    // driver's start-up is the longer of the two on a cold process); an encode-only / decode-only context (the CLI)
+    // builds and uploads only the arrays its path reads.
     int n_dev = 0;
-    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    cudaError_t e_init = cudaSuccess;
+    double t_cuda = 0;
+    std::thread cuda_up([&]() {
+        e_init = cudaGetDeviceCount(&n_dev);
+        if (e_init == cudaSuccess && device >= 0 && device < n_dev) {
+            e_init = cudaSetDevice(device);
+            if (e_init == cudaSuccess) e_init = cudaFree(0);
+        }
+        t_cuda = since();
+    });
+    const int threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    std::vector<uint32_t> rank, lcs, pfx;
+    std::vector<uint64_t> jump;
+    uint32_t c_start[4] = {0, 0, 0, 0};
+    const bool use_pfx = idx->k >= 10 && !getenv("NTC_NO_PREFIX_TABLE");   // a tile's warm-up (k-1 bases) must cover the 8 bases
+    double t_rank = 0, t_lcs = 0, t_jump = 0;
+    std::exception_ptr build_err;
+    {
+        std::thread lcs_thread;
+        try {
+            if (uses & NTC_USE_ENCODE) lcs_thread = std::thread([&]() { build_lcs_words(*idx, &lcs); t_lcs = since(); });   // serial stack pass
+            if (uses & NTC_USE_ENCODE) {
+                build_rank_blocks(*idx, &rank, std::max(1, threads - 1));
+                if (use_pfx) build_prefix_table(rank, idx->n, &pfx, c_start);
+                t_rank = since();
+            }
+            if (uses & NTC_USE_DECODE) { build_jump_table(*idx, &jump, std::max(1, threads - 1)); t_jump = since(); }
+        } catch (...) { build_err = std::current_exception(); }
+        if (lcs_thread.joinable()) lcs_thread.join();
+    }
+    cuda_up.join();
+    if (build_err) { set_error("out of host memory while deriving the index layouts"); return NTC_ERR_INVALID_ARG; }
+    cudaError_t e = e_init;
     if (e != cudaSuccess || n_dev == 0) {
         set_error(std::string("no CUDA device available (this library has no CPU fallback): ") + cudaGetErrorString(e));
         return NTC_ERR_CUDA;
@@ -276,6 +326,8 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     ctx->device = device;
     ctx->k = idx->k;
     ctx->n = idx->n;
+    ctx->uses = uses;
+    memcpy(ctx->dix.c_start, c_start, sizeof c_start);
     if (const char* env = getenv("NTC_MAX_CHUNK_BASES")) {
         unsigned long long v = strtoull(env, nullptr, 10);
         if (v >= 1024) ctx->max_chunk_bases = v;
@@ -284,16 +336,6 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
         unsigned long long v = strtoull(env, nullptr, 10);
         if (v >= 16) ctx->max_chunk_records = v;
     }
-    int threads = (int)std::max(1u, std::thread::hardware_concurrency());
-    std::vector<uint32_t> rank;
-    std::vector<uint64_t> jump;
-    build_rank_blocks(*idx, &rank, threads);
-    build_jump_table(*idx, &jump, threads);
-    std::vector<uint32_t> lcs;
-    build_lcs_words(*idx, &lcs);
-    std::vector<uint32_t> pfx;
-    const bool use_pfx = idx->k >= 10 && !getenv("NTC_NO_PREFIX_TABLE");   // a tile's warm-up (k-1 bases) must cover the 8 bases
-    if (use_pfx) build_prefix_table(rank, idx->n, &pfx, ctx->dix.c_start);
     auto fail = [&](const char* what, cudaError_t err) {
         set_error(std::string(what) + ": " + cudaGetErrorString(err));
         ntc_ctx_destroy(ctx);
@@ -302,13 +344,17 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     ctx->index_bytes[0] = rank.size() * 4;
     ctx->index_bytes[1] = lcs.size() * 4;
     ctx->index_bytes[2] = jump.size() * 8;
-    if ((e = cudaMalloc(&ctx->d_rank, ctx->index_bytes[0])) != cudaSuccess) return fail("cudaMalloc rank", e);
-    if ((e = cudaMalloc(&ctx->d_lcs, ctx->index_bytes[1])) != cudaSuccess) return fail("cudaMalloc lcs", e);
-    if ((e = cudaMalloc(&ctx->d_jump, ctx->index_bytes[2])) != cudaSuccess) return fail("cudaMalloc jump", e);
-    if ((e = cudaMemcpy(ctx->d_rank, rank.data(), ctx->index_bytes[0], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload rank", e);
-    if ((e = cudaMemcpy(ctx->d_lcs, lcs.data(), ctx->index_bytes[1], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload lcs", e);
-    if ((e = cudaMemcpy(ctx->d_jump, jump.data(), ctx->index_bytes[2], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload jump", e);
-    if (use_pfx) {
+    if (uses & NTC_USE_ENCODE) {
+        if ((e = cudaMalloc(&ctx->d_rank, ctx->index_bytes[0])) != cudaSuccess) return fail("cudaMalloc rank", e);
+        if ((e = cudaMalloc(&ctx->d_lcs, ctx->index_bytes[1])) != cudaSuccess) return fail("cudaMalloc lcs", e);
+        if ((e = cudaMemcpy(ctx->d_rank, rank.data(), ctx->index_bytes[0], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload rank", e);
+        if ((e = cudaMemcpy(ctx->d_lcs, lcs.data(), ctx->index_bytes[1], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload lcs", e);
+    }
+    if (uses & NTC_USE_DECODE) {
+        if ((e = cudaMalloc(&ctx->d_jump, ctx->index_bytes[2])) != cudaSuccess) return fail("cudaMalloc jump", e);
+        if ((e = cudaMemcpy(ctx->d_jump, jump.data(), ctx->index_bytes[2], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload jump", e);
+    }
+    if (use_pfx && (uses & NTC_USE_ENCODE)) {
         if ((e = cudaMalloc(&ctx->d_pfx, pfx.size() * 4)) != cudaSuccess) return fail("cudaMalloc prefix table", e);
         if ((e = cudaMemcpy(ctx->d_pfx, pfx.data(), pfx.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload prefix table", e);
     }
@@ -357,6 +403,9 @@ int32_t ntc_ctx_create(int32_t device, const ntc_index* idx, ntc_ctx** out) {
     if (const char* env = getenv("NTC_TILE_LEN")) ntc_ctx_set_tile_len(ctx, (uint32_t)strtoul(env, nullptr, 10));
     if (const char* env = getenv("NTC_SPEC_LO")) ctx->dix.spec_lo = (uint32_t)strtoul(env, nullptr, 10);      // tuning knobs
     if (const char* env = getenv("NTC_SPEC_SPAN")) ctx->dix.spec_span = (uint32_t)strtoul(env, nullptr, 10);
+    if (trace)
+        fprintf(stderr, "[ntc trace] ctx_create %.3f s: CUDA context up at %.3f (own thread) | host layouts: rank+prefix done at %.3f, lcs at %.3f, "
+                "jump at %.3f | uploads + policies %.3f\n", since(), t_cuda, t_rank, t_lcs, t_jump, since() - std::max(std::max(t_cuda, t_jump), std::max(t_rank, t_lcs)));
     *out = ctx;
     return NTC_OK;
 }
@@ -380,6 +429,15 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
     cudaFree(ctx->d_status); cudaFree(ctx->d_totals);
     delete ctx;
 }
+
+int32_t ntc_pinned_alloc(uint64_t bytes, void** out) {
+    if (!out) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    *out = nullptr;
+    cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable);
+    if (e != cudaSuccess) { *out = nullptr; set_error(std::string("cudaHostAlloc: ") + cudaGetErrorString(e)); return NTC_ERR_CUDA; }
+    return NTC_OK;
+}
+void ntc_pinned_free(void* p) { if (p) cudaFreeHost(p); }
 
 void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]) { memcpy(out, ctx->index_bytes, 24); }
 uint64_t ntc_ctx_launch_count(const ntc_ctx* ctx) { return ctx ? ctx->launches : 0; }

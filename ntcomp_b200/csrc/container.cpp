@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -219,10 +220,19 @@ int zip_columns(const BlockColumns& c, std::vector<uint64_t>* rec, bool full_las
 }
 
 // ---- gzip ----------------------------------------------------------------------------------------
+// flate2's Compression::default() is level 6 (src/encode.rs:53); NTC_GZIP_LEVEL (1..9) trades size for speed in experiments
+static int gzip_level() {
+    static const int level = [] {
+        const char* env = getenv("NTC_GZIP_LEVEL");
+        const int v = env ? atoi(env) : 6;
+        return v >= 1 && v <= 9 ? v : 6;
+    }();
+    return level;
+}
 static bool gzip_member(const uint8_t* in, size_t n, std::vector<uint8_t>* out) {
     z_stream zs;
     memset(&zs, 0, sizeof(zs));
-    if (deflateInit2(&zs, 6, Z_DEFLATED, 15 + 16, 8, Z_DEFAULT_STRATEGY) != Z_OK) return false;
+    if (deflateInit2(&zs, gzip_level(), Z_DEFLATED, 15 + 16, 8, Z_DEFAULT_STRATEGY) != Z_OK) return false;
     gz_header hd;
     memset(&hd, 0, sizeof(hd));
     hd.os = 255;
@@ -276,6 +286,40 @@ void put_sub_block(const CodedColumn& col, uint64_t num_records, std::vector<uin
     h[24] = 8;                                                       // bitpacker_exponent, src/encode.rs:118
     sink->insert(sink->end(), h, h + 32);
     sink->insert(sink->end(), gz.begin(), gz.end());
+}
+
+// the same sub-block from a plain word pointer straight into a caller buffer (one gzip task of the file pipeline)
+int32_t put_sub_block_raw(const uint64_t* words, uint64_t n_words, uint64_t n_values, uint64_t param, uint64_t num_records, uint8_t* out,
+                          uint64_t cap, uint64_t* n_bytes) {
+    *n_bytes = 0;
+    if (cap < 32 + 64) return -2;
+    z_stream zs;
+    memset(&zs, 0, sizeof(zs));
+    if (deflateInit2(&zs, gzip_level(), Z_DEFLATED, 15 + 16, 8, Z_DEFAULT_STRATEGY) != Z_OK) return -1;
+    gz_header hd;
+    memset(&hd, 0, sizeof(hd));
+    hd.os = 255;
+    deflateSetHeader(&zs, &hd);
+    if (n_words * 8 > 0xFFFFFFF0ull || cap - 32 > 0xFFFFFFF0ull) { deflateEnd(&zs); return -1; }
+    zs.next_in = const_cast<Bytef*>((const Bytef*)words);
+    zs.avail_in = (uInt)(n_words * 8);
+    zs.next_out = out + 32;
+    zs.avail_out = (uInt)(cap - 32);
+    const int rc = deflate(&zs, Z_FINISH);
+    const uint64_t gz = zs.total_out;
+    deflateEnd(&zs);
+    if (rc != Z_STREAM_END) return rc == Z_OK || rc == Z_BUF_ERROR ? -2 : -1;
+    uint8_t* h = out;
+    memset(h, 0, 32);
+    uint32_t v32;
+    v32 = (uint32_t)gz; memcpy(h + 0, &v32, 4);
+    v32 = (uint32_t)num_records; memcpy(h + 4, &v32, 4);
+    v32 = (uint32_t)n_values; memcpy(h + 8, &v32, 4);
+    v32 = (uint32_t)n_words; memcpy(h + 12, &v32, 4);
+    memcpy(h + 16, &param, 8);
+    h[24] = 8;
+    *n_bytes = 32 + gz;
+    return 0;
 }
 
 // header fields + gunzip of one sub-block, without decoding the integer codes (the GPU column decoder's input)

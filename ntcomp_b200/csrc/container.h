@@ -21,6 +21,9 @@ bool decode_column_host(const uint64_t* words, uint64_t n_words, uint64_t n, int
 void split_records(const uint64_t* rec, uint64_t n, BlockColumns* c);
 int zip_columns(const BlockColumns& c, std::vector<uint64_t>* rec, bool full_last_word = false);
 void put_sub_block(const CodedColumn& col, uint64_t num_records, std::vector<uint8_t>* sink, bool* ok);
+// 0 ok, -1 deflate failed, -2 out too small
+int32_t put_sub_block_raw(const uint64_t* words, uint64_t n_words, uint64_t n_values, uint64_t param, uint64_t num_records, uint8_t* out,
+                          uint64_t cap, uint64_t* n_bytes);
 int64_t inflate_sub_block(const uint8_t* data, uint64_t size, std::vector<uint64_t>* words, uint64_t* n_values, uint64_t* param);
 int64_t read_sub_block(const uint8_t* data, uint64_t size, int rice, std::vector<uint64_t>* values);
 

@@ -45,6 +45,7 @@ struct ntc_ctx {
     uint64_t index_bytes[3] = {0, 0, 0};
     uint32_t k = 0;
     uint64_t n = 0;
+    uint32_t uses = 3;       // NTC_USE_* mask: which derived arrays are resident
 
     uint32_t* d_status = nullptr;   // [4]
     uint64_t* d_totals = nullptr;   // [8]: ring of 3 encode scan totals (Pair64 each) + decode totals at [6]

@@ -8,6 +8,10 @@
 // from this file.  needletail's parser (src/main.rs:158-163, normalize(true)) is restated for plain and
 // gzip-compressed FASTA / FASTQ; bytes other than ACGT after normalisation make the encoder return
 // NTC_ERR_BAD_BASE (the reference underflows at src/lib.rs:207).
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <zlib.h>
 
 #include <algorithm>
@@ -37,13 +41,13 @@ using ntc::set_error;
 namespace {
 
 constexpr uint64_t kBlockReads = 65536;            // src/main.rs:152
-constexpr uint64_t kBatchBlocksDefault = 8;        // blocks handed to the GPU per call (stage overlap granularity)
+constexpr uint64_t kBatchBlocksDefault = 4;        // blocks handed to the GPU per call (stage overlap granularity)
 constexpr uint64_t kBatchBases = 768ull << 20;     // ... or this many bases, whichever comes first
 
 uint64_t batch_blocks() {                          // NTC_PIPELINE_BATCH_BLOCKS overrides (tests: several groups from small files)
     if (const char* env = getenv("NTC_PIPELINE_BATCH_BLOCKS")) {
         unsigned long long v = strtoull(env, nullptr, 10);
-        if (v >= 1 && v <= 4096) return v;
+        if (v >= 1 && v <= 64) return v;
     }
     return kBatchBlocksDefault;
 }
@@ -237,18 +241,15 @@ bool record_starts_at(const uint8_t* p, const uint8_t* end, int fmt) {
     return ml.peek() < 0 || ml.peek() == '@';
 }
 
-// last record start in text[lo, n) that is not at position 0; returns 0 when there is none
-size_t last_record_start(const uint8_t* text, size_t n, size_t lo, int fmt) {
+// last record start in text[lo, n) that is not at position 0; returns 0 when there is none.  Candidates are verified
+// against the text up to n_total (>= n): a mapped file shows the bytes after the window, a stream does not (n_total == n)
+size_t last_record_start(const uint8_t* text, size_t n, size_t lo, int fmt, size_t n_total) {
     size_t hi = n;
     while (hi > lo + 1) {
         const void* q = memrchr(text + lo, '\n', hi - lo - 1);         // a newline that is followed by at least one byte
         if (!q) return 0;
         const size_t at = (size_t)((const uint8_t*)q - text) + 1;
-        if (text[at] == (uint8_t)fmt && record_starts_at(text + at, text + n, fmt)) {
-            // FASTQ: the check looked ahead over four lines; a candidate in the unfinished tail of the buffer may have
-            // passed only because the text ends there -- require that a full record follows or the caller treats EOF
-            return at;
-        }
+        if (text[at] == (uint8_t)fmt && record_starts_at(text + at, text + n_total, fmt)) return at;
         hi = at - 1 > lo ? at - 1 : lo;
         if (hi == lo) break;
     }
@@ -359,90 +360,182 @@ private:
     bool stop_ = false;
 };
 
-// Reads fastX text from `in` (plain or gzip), cuts it into pieces of whole records, parses the pieces on `pool` and hands
-// them to on_piece(ParsedPiece&) IN FILE ORDER on the calling thread; on_piece returns false to stop early.  At most
-// `max_in_flight` pieces exist at a time.  *read_busy accumulates the reader thread's busy seconds.
-template <typename OnPiece>
-void parallel_fastx(gzFile in, TaskPool& pool, size_t max_in_flight, OnPiece&& on_piece, double* read_busy, bool* fatal) {
-    const size_t kPiece = 4u << 20;                                    // text per parse task
-    Ordered<ParsedPiece> parsed;
-    Tokens in_flight(max_in_flight);
-    std::atomic<uint64_t> parse_busy_us{0};
-    Recycler<std::vector<uint8_t>> texts;
-    Recycler<ParsedPiece> pieces;
-    double consume_busy = 0, consume_wait = 0, emit_s = 0;
-    std::thread t_read([&] { stage_guard(fatal, [&] {
-        std::vector<uint8_t> buf;
-        uint64_t seq = 0;
-        int fmt = 0;
-        bool eof = false;
-        auto emit = [&](size_t n) {                                   // buf[0, n) holds whole records
-            if (n == 0) return;
-            if (!in_flight.acquire()) { eof = true; buf.clear(); return; }
-            auto text = std::make_shared<std::vector<uint8_t>>(texts.get());
-            text->assign(buf.begin(), buf.begin() + n);
-            const uint64_t my = seq++;
-            pool.submit([text, my, &parsed, &parse_busy_us, &texts, &pieces] {
-                const double p0 = now_s();
-                ParsedPiece pp = pieces.get();
-                pp.bases.clear(); pp.lens.clear(); pp.err = 0;
-                parse_piece(text->data(), text->size(), &pp);
-                parse_busy_us += (uint64_t)((now_s() - p0) * 1e6);
-                parsed.put(my, std::move(pp));
-                texts.put(std::move(*text));
-            });
-            buf.erase(buf.begin(), buf.begin() + n);
-        };
-        size_t searched = 0;                                           // buf[0, searched) holds no usable cut
-        while (!eof) {
-            const double t0 = now_s();
-            const size_t at = buf.size();
-            buf.resize(at + kPiece);
-            int got = gzread(in, buf.data() + at, (unsigned)kPiece);
-            if (got <= 0) { got = 0; eof = true; }
-            buf.resize(at + (size_t)got);
-            if (!fmt) for (uint8_t c : buf) if (c != '\n' && c != '\r' && c != ' ') { fmt = c; break; }
-            if (fmt && fmt != '>' && fmt != '@') {                     // not fastX: let the parser report it
-                if (read_busy) *read_busy += now_s() - t0;
-                break;
+// fastX input: a gzip stream / pipe read through zlib, or -- a plain regular file -- a read-only mapping the parse workers
+// read in place (no copy on the reader thread; the page faults spread over the workers)
+struct FastxInput {
+    gzFile gz = nullptr;
+    const uint8_t* map = nullptr;
+    size_t map_size = 0;
+    bool open(const char* path) {
+        if (strcmp(path, "-") != 0 && !getenv("NTC_NO_MMAP")) {
+            int fd = ::open(path, O_RDONLY);
+            if (fd < 0) return false;
+            struct stat sb;
+            uint8_t magic[2] = {0, 0};
+            if (fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size > 0 && pread(fd, magic, 2, 0) == 2 && !(magic[0] == 0x1f && magic[1] == 0x8b)) {
+                void* m = mmap(nullptr, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+                if (m != MAP_FAILED) {
+                    madvise(m, (size_t)sb.st_size, MADV_SEQUENTIAL);
+                    map = (const uint8_t*)m;
+                    map_size = (size_t)sb.st_size;
+                    ::close(fd);
+                    return true;
+                }
             }
-            if (!eof && fmt && buf.size() >= kPiece) {
-                const size_t cut = last_record_start(buf.data(), buf.size(), searched, fmt);
-                const double e0 = now_s();
-                if (cut) { emit(cut); searched = 0; } else searched = buf.size() > 1 ? buf.size() - 1 : 0;
-                emit_s += now_s() - e0;
-            }
-            if (read_busy) *read_busy += now_s() - t0;
+            ::close(fd);
         }
-        emit(buf.size());
+        gz = (strcmp(path, "-") == 0) ? gzdopen(0, "rb") : gzopen(path, "rb");
+        if (gz) gzbuffer(gz, 1 << 20);
+        return gz != nullptr;
+    }
+    void close() {
+        if (gz) { gzclose(gz); gz = nullptr; }
+        if (map) { munmap((void*)map, map_size); map = nullptr; }
+    }
+    ~FastxInput() { close(); }
+};
+
+// Cuts the fastX text of `in` into pieces of whole records, parses the pieces on `pool` and hands them to
+// on_piece(std::shared_ptr<ParsedPiece>) IN FILE ORDER on the calling thread; on_piece returns false to stop early and may
+// keep the pointer (the piece's buffers are recycled when the last reference goes).  At most `max_in_flight` pieces exist
+// at a time.  *read_busy accumulates the reader thread's busy seconds.
+template <typename OnPiece>
+void parallel_fastx(FastxInput& in, TaskPool& pool, size_t max_in_flight, OnPiece&& on_piece, double* read_busy, bool* fatal) {
+    const size_t kPiece = 4u << 20;                                    // text per parse task
+    using PiecePtr = std::shared_ptr<ParsedPiece>;
+    // declared before the channel: pieces still queued there are recycled by the destructors running in reverse order
+    auto in_flight = std::make_shared<Tokens>(max_in_flight);
+    auto texts = std::make_shared<Recycler<std::vector<uint8_t>>>();
+    auto pieces = std::make_shared<Recycler<ParsedPiece>>();
+    Ordered<PiecePtr> parsed;
+    std::atomic<uint64_t> parse_busy_us{0};
+    std::atomic<int64_t> tasks_out{0};                                 // parse tasks submitted and not finished (they refer to this frame)
+    double consume_busy = 0, consume_wait = 0;
+    uint64_t seq = 0;
+    bool stop = false;
+    // a piece of text holding whole records goes to the pool; own (may be null) keeps a copied text alive
+    auto emit = [&](const uint8_t* p, size_t n, std::shared_ptr<std::vector<uint8_t>> own) {
+        if (n == 0) return;
+        if (!in_flight->acquire()) { stop = true; return; }
+        const uint64_t my = seq++;
+        tasks_out++;
+        pool.submit([p, n, own, my, &parsed, &parse_busy_us, &tasks_out, texts, pieces, in_flight] {
+            struct Done { std::atomic<int64_t>& c; ~Done() { c--; } } done{tasks_out};
+            const double p0 = now_s();
+            ParsedPiece* raw = new ParsedPiece(pieces->get());
+            raw->bases.clear(); raw->lens.clear(); raw->err = 0;
+            PiecePtr pp(raw, [pieces, in_flight](ParsedPiece* q) { pieces->put(std::move(*q)); delete q; in_flight->release(); });
+            parse_piece(p, n, raw);
+            if (own) texts->put(std::move(*own));
+            parse_busy_us += (uint64_t)((now_s() - p0) * 1e6);
+            parsed.put(my, std::move(pp));
+        });
+    };
+    std::thread t_read([&] { stage_guard(fatal, [&] {
+        int fmt = 0;
+        if (in.map) {
+            const uint8_t* base = in.map;
+            const size_t size = in.map_size;
+            for (size_t i = 0; i < size; i++) if (base[i] != '\n' && base[i] != '\r' && base[i] != ' ') { fmt = base[i]; break; }
+            size_t pos = 0;
+            if (fmt != '>' && fmt != '@') { emit(base, std::min<size_t>(size, 1u << 16), nullptr); pos = size; }   // not fastX: the parser reports it
+            while (pos < size && !stop) {
+                const double t0 = now_s();
+                size_t cut = 0, win = kPiece, searched = 0;
+                for (;;) {
+                    if (pos + win >= size) { cut = size - pos; break; }
+                    cut = last_record_start(base + pos, win, searched, fmt, size - pos);
+                    if (cut) break;
+                    searched = win - 1;
+                    win += kPiece;
+                }
+                if (read_busy) *read_busy += now_s() - t0;
+                emit(base + pos, cut, nullptr);
+                pos += cut;
+            }
+        } else {
+            std::vector<uint8_t> buf;
+            bool eof = false;
+            size_t searched = 0;                                       // buf[0, searched) holds no usable cut
+            auto emit_front = [&](size_t n) {                          // buf[0, n) holds whole records
+                if (n == 0) return;
+                auto text = std::make_shared<std::vector<uint8_t>>(texts->get());
+                text->assign(buf.begin(), buf.begin() + n);
+                emit(text->data(), n, text);
+                buf.erase(buf.begin(), buf.begin() + n);
+            };
+            while (!eof && !stop) {
+                const double t0 = now_s();
+                const size_t at = buf.size();
+                buf.resize(at + kPiece);
+                int got = gzread(in.gz, buf.data() + at, (unsigned)kPiece);
+                if (got <= 0) { got = 0; eof = true; }
+                buf.resize(at + (size_t)got);
+                if (!fmt) for (uint8_t c : buf) if (c != '\n' && c != '\r' && c != ' ') { fmt = c; break; }
+                if (fmt && fmt != '>' && fmt != '@') {                 // not fastX: let the parser report it
+                    if (read_busy) *read_busy += now_s() - t0;
+                    break;
+                }
+                if (!eof && fmt && buf.size() >= kPiece) {
+                    const size_t cut = last_record_start(buf.data(), buf.size(), searched, fmt, buf.size());
+                    if (cut) { emit_front(cut); searched = 0; } else searched = buf.size() > 1 ? buf.size() - 1 : 0;
+                }
+                if (read_busy) *read_busy += now_s() - t0;
+            }
+            if (!stop) emit_front(buf.size());
+        }
         parsed.finish(seq);
     }, [&] { parsed.abort(); }); });
-    ParsedPiece pp;
     for (;;) {
+        PiecePtr pp;
         const double w0 = now_s();
         if (!parsed.next(&pp)) break;
         const double w1 = now_s();
-        in_flight.release();
         const bool go = on_piece(pp);
-        pieces.put(std::move(pp));
+        pp.reset();
         consume_wait += w1 - w0;
         consume_busy += now_s() - w1;
         if (!go) break;
     }
     parsed.abort();
-    in_flight.close();
+    in_flight->close();
     t_read.join();
+    while (tasks_out.load() > 0) std::this_thread::sleep_for(std::chrono::microseconds(200));   // early stop only: a few queued tasks
     if (getenv("NTC_TRACE"))
-        fprintf(stderr, "[ntc trace] fastx: parse tasks %.3f s (sum over workers), in-order consumer busy %.3f s / waiting %.3f s, reader hand-over %.3f s\n",
-                parse_busy_us.load() * 1e-6, consume_busy, consume_wait, emit_s);
+        fprintf(stderr, "[ntc trace] fastx (%s): %llu pieces, parse tasks %.3f s (sum over workers), in-order consumer busy %.3f s / waiting %.3f s\n",
+                in.map ? "mapped file" : "stream", (unsigned long long)seq, parse_busy_us.load() * 1e-6, consume_busy, consume_wait);
 }
 
 // one GPU call's worth of reads / one group of blocks travelling through the stages
 struct ReadBatch {
-    std::vector<uint8_t> bases;
-    std::vector<uint64_t> offsets;   // n_reads + 1
+    uint8_t* bases = nullptr;        // page-locked (ntc_pinned_alloc): the H2D copy of the GPU stage reads it in place
+    uint64_t cap = 0;                // bytes allocated
+    uint64_t first_cap = 0;          // size of the first allocation (a batch of short reads fits without growing)
+    uint64_t n_bases = 0, n_reads = 0;
+    std::vector<uint64_t> offsets;   // n_reads + 1 once the copy tasks are done
     int err = 0;                     // reader error (1 malformed input, 2 read too long)
+    // copy tasks still writing into bases / offsets
+    std::mutex m;
+    std::condition_variable cv;
+    uint64_t pending = 0;
+    void task_begin() { std::lock_guard<std::mutex> lk(m); pending++; }
+    void task_end() { std::lock_guard<std::mutex> lk(m); pending--; cv.notify_all(); }
+    void wait_filled() { std::unique_lock<std::mutex> lk(m); cv.wait(lk, [&] { return pending == 0; }); }
+    bool reserve(uint64_t want) {    // grows (long reads); the caller holds the only writer role and no task is pending
+        if (want <= cap) return true;
+        wait_filled();
+        uint64_t ncap = std::max<uint64_t>(std::max<uint64_t>(want + want / 4, 2 * cap), first_cap);
+        void* p = nullptr;
+        if (ntc_pinned_alloc(ncap, &p) != NTC_OK) return false;
+        if (n_bases) memcpy(p, bases, n_bases);
+        if (bases) ntc_pinned_free(bases);
+        bases = (uint8_t*)p;
+        cap = ncap;
+        return true;
+    }
+    ~ReadBatch() { wait_filled(); if (bases) ntc_pinned_free(bases); }   // copy tasks hold a plain pointer to this batch
 };
+using BatchPtr = std::unique_ptr<ReadBatch>;
 struct BytesBatch {
     std::vector<std::vector<uint8_t>> parts;   // written in order
     int32_t rc = NTC_OK;
@@ -465,65 +558,90 @@ extern "C" {
 int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_path, int32_t n_threads, uint64_t* stats) {
     if (!ctx || !fastx_path) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
     if (n_threads <= 0) n_threads = (int32_t)std::max(1u, std::thread::hardware_concurrency());
-    gzFile in = (strcmp(fastx_path, "-") == 0) ? gzdopen(0, "rb") : gzopen(fastx_path, "rb");
-    if (!in) { set_error(std::string("cannot open ") + fastx_path); return NTC_ERR_IO; }
-    gzbuffer(in, 1 << 20);
+    FastxInput in;
+    if (!in.open(fastx_path)) { set_error(std::string("cannot open ") + fastx_path); return NTC_ERR_IO; }
     Sink sink;
-    if (!sink.open(out_path)) { gzclose(in); set_error(std::string("cannot open ") + (out_path ? out_path : "-")); return NTC_ERR_IO; }
+    if (!sink.open(out_path)) { set_error(std::string("cannot open ") + (out_path ? out_path : "-")); return NTC_ERR_IO; }
     uint64_t st[6] = {0, 0, 0, 0, 0, 0};
     const uint8_t file_header[32] = {0};                               // encode_file_header(0,0,0,0), src/main.rs:154
-    if (!sink.write(file_header, 32)) { gzclose(in); set_error("write failed"); return NTC_ERR_IO; }
+    if (!sink.write(file_header, 32)) { set_error("write failed"); return NTC_ERR_IO; }
     st[3] = 32;
 
     const uint64_t kBatchBlocks = batch_blocks();
+    const uint64_t kBatchReads = kBatchBlocks * kBlockReads;
     double t_stage[5] = {0, 0, 0, 0, 0};                               // busy seconds: read + cut, assemble, GPU, gzip, write
+    std::atomic<uint64_t> copy_us{0}, gzip_us{0};                      // summed over the pool's workers
     bool fatal = false;
     int32_t rc = NTC_OK;
     std::string msg;
     {
     TaskPool pool(n_threads);
-    Channel<ReadBatch> batches(2);
-    Channel<ReadBatch> spare(8);                                       // used batch buffers on their way back to the assembler
+    Channel<BatchPtr> batches(2);
+    Channel<BatchPtr> spare(8);                                        // used batch buffers on their way back to the assembler
     Channel<CodedBatch> coded(2);
     Channel<BytesBatch> bytes(2);
 
-    // stage 2: parsed pieces, in order -> batches of whole 65,536-read blocks
+    // stage 2: parsed pieces, in order -> batches of whole 65,536-read blocks.  This thread only decides where every piece
+    // goes; the bytes are moved by copy tasks on the pool, straight into the page-locked buffer the GPU stage uploads from.
     std::thread t_batch([&] { stage_guard(&fatal, [&] {
-        ReadBatch b;
-        b.offsets.push_back(0);
-        bool stopped = false;
-        auto fresh = [&]() { ReadBatch n; spare.try_pop(&n); n.bases.clear(); n.offsets.clear(); n.offsets.push_back(0); n.err = 0; return n; };
-        // hands on the whole blocks of b (everything when last); the reads beyond the last block boundary move to the next buffer
-        auto flush = [&](bool last) -> bool {
-            const uint64_t n = b.offsets.size() - 1;
-            const uint64_t take = last ? n : n / kBlockReads * kBlockReads;
-            if (take == 0 && !(last && b.err)) return true;
-            ReadBatch rest = fresh();
-            const uint64_t nb = b.offsets[take];
-            rest.bases.assign(b.bases.begin() + nb, b.bases.end());
-            for (uint64_t r = take + 1; r <= n; r++) rest.offsets.push_back(b.offsets[r] - nb);
-            b.bases.resize(nb);
-            b.offsets.resize(take + 1);
-            ReadBatch out = std::move(b);
-            b = std::move(rest);
-            return batches.push(std::move(out));
+        uint64_t made = 0;
+        auto fresh = [&]() -> BatchPtr {
+            BatchPtr n;
+            if (made >= 3) { if (!spare.pop(&n)) return nullptr; }     // three buffers circulate: filling, queued, on the GPU
+            else if (!spare.try_pop(&n)) {
+                n.reset(new ReadBatch());
+                n->first_cap = std::min<uint64_t>(kBatchReads * 152 + (1u << 20), 256ull << 20);
+                made++;
+            }
+            n->n_bases = n->n_reads = 0;
+            n->err = 0;
+            n->offsets.resize(kBatchReads + 1);
+            n->offsets[0] = 0;
+            return n;
         };
-        // stage 1 lives inside parallel_fastx: read (inflate), cut at record boundaries, parse on the pool
-        parallel_fastx(in, pool, (size_t)n_threads * 3 + 8, [&](ParsedPiece& pp) -> bool {
+        BatchPtr b = fresh();
+        bool stopped = false;
+        auto hand_on = [&]() -> bool {
+            BatchPtr out = std::move(b);
+            if (!batches.push(std::move(out))) return false;
+            b = fresh();
+            return (bool)b;
+        };
+        // stage 1 lives inside parallel_fastx: cut at record boundaries (reader), parse on the pool
+        parallel_fastx(in, pool, (size_t)n_threads * 3 + 8, [&](const std::shared_ptr<ParsedPiece>& pp) -> bool {
             const double t0 = now_s();
-            if (pp.err && !b.err) b.err = pp.err;
-            const uint64_t base0 = b.bases.size();
-            b.bases.insert(b.bases.end(), pp.bases.begin(), pp.bases.end());
-            uint64_t at = base0;
-            for (uint32_t l : pp.lens) { at += l; b.offsets.push_back(at); }
-            bool ok = true;
-            if (b.err) { ok = flush(true); stopped = true; t_stage[1] += now_s() - t0; return false; }
-            if (b.offsets.size() - 1 >= kBatchBlocks * kBlockReads || b.bases.size() >= kBatchBases) ok = flush(false);
-            t_stage[1] += now_s() - t0;
-            if (!ok) stopped = true;
-            return ok;
+            struct Timer { double& acc; double t0; ~Timer() { acc += now_s() - t0; } } timer{t_stage[1], t0};
+            if (pp->err && !b->err) b->err = pp->err;
+            const uint64_t n = pp->lens.size();
+            uint64_t i = 0, src = 0;
+            while (i < n) {
+                const uint64_t take = std::min<uint64_t>(kBatchReads - b->n_reads, n - i);
+                uint64_t tb = 0;
+                if (i == 0 && take == n) tb = pp->bases.size();
+                else for (uint64_t j = i; j < i + take; j++) tb += pp->lens[j];
+                if (!b->reserve(b->n_bases + tb + 64)) { b->err = 3; break; }
+                ReadBatch* dst = b.get();
+                const uint64_t r0 = dst->n_reads, b0 = dst->n_bases;
+                dst->task_begin();
+                pool.submit([pp, dst, i, take, src, tb, r0, b0, &copy_us] {
+                    const double c0 = now_s();
+                    if (tb) memcpy(dst->bases + b0, pp->bases.data() + src, tb);
+                    uint64_t at = b0;
+                    for (uint64_t j = 0; j < take; j++) { at += pp->lens[i + j]; dst->offsets[r0 + j + 1] = at; }
+                    copy_us += (uint64_t)((now_s() - c0) * 1e6);
+                    dst->task_end();
+                });
+                dst->n_reads += take;
+                dst->n_bases += tb;
+                i += take;
+                src += tb;
+                if (dst->n_reads == kBatchReads && !hand_on()) { stopped = true; return false; }
+            }
+            if (b->err) { hand_on(); stopped = true; return false; }
+            return true;
         }, &t_stage[0], &fatal);
-        if (!stopped) flush(true);
+        if (!stopped && b && (b->n_reads || b->err)) batches.push(std::move(b));
+        if (b) b->wait_filled();
         batches.finish();
     }, [&] { batches.finish(); }); });
 
@@ -534,34 +652,40 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
             const double t0 = now_s();
             const size_t n_blocks = cb.blocks.size();
             auto out = std::make_shared<BytesBatch>();
-            out->parts.resize(n_blocks);
-            auto brc = std::make_shared<std::vector<int32_t>>(n_blocks, NTC_OK);
+            out->parts.resize(n_blocks * 4);                           // one gzip task per sub-block: 4 x finer than per block
+            auto brc = std::make_shared<std::vector<int32_t>>(n_blocks * 4, NTC_OK);
             auto shared = std::make_shared<CodedBatch>(std::move(cb));
             struct Latch { std::mutex m; std::condition_variable cv; size_t done = 0; };
             auto latch = std::make_shared<Latch>();
-            for (size_t j = 0; j < n_blocks; j++)
-                pool.submit([j, out, brc, shared, latch] {
-                    const ntc_coded_block& blk = shared->blocks[j];
+            for (size_t j = 0; j < n_blocks * 4; j++)
+                pool.submit([j, out, brc, shared, latch, &gzip_us] {
+                    const double g0 = now_s();
+                    const ntc_coded_block& blk = shared->blocks[j / 4];
                     int32_t r = blk.status;
                     if (r == NTC_OK) {
-                        uint64_t n_w = 0;
-                        for (int q = 0; q < 4; q++) n_w += blk.col[q].n_words;
+                        const uint64_t n_w = blk.col[j % 4].n_words;
                         std::vector<uint8_t>& buf = out->parts[j];
-                        buf.resize(4 * 32 + 4 * 64 + n_w * 8 + n_w / 100 + 1024);
+                        buf.resize(32 + 64 + n_w * 8 + n_w / 100 + 1024);
                         uint64_t nb = 0;
-                        r = ntc_block_assemble(&blk, shared->words.data(), buf.data(), buf.size(), &nb);
+                        r = ntc_sub_block_assemble(&blk, (int32_t)(j % 4), shared->words.data(), buf.data(), buf.size(), &nb);
                         buf.resize(r == NTC_OK ? nb : 0);
                     }
                     (*brc)[j] = r;
+                    gzip_us += (uint64_t)((now_s() - g0) * 1e6);
                     std::lock_guard<std::mutex> lk(latch->m);
                     latch->done++;
                     latch->cv.notify_all();
                 });
-            { std::unique_lock<std::mutex> lk(latch->m); latch->cv.wait(lk, [&] { return latch->done == n_blocks; }); }
+            { std::unique_lock<std::mutex> lk(latch->m); latch->cv.wait(lk, [&] { return latch->done == n_blocks * 4; }); }
             for (size_t j = 0; j < n_blocks; j++) {
-                if ((*brc)[j] == NTC_OK) st[4]++;
-                else if ((*brc)[j] == NTC_ERR_EMPTY_COLUMN) st[5]++;   // dropped, as the reference does (Q4)
-                else { out->rc = (*brc)[j]; out->msg = "block container failed"; }
+                int32_t r = NTC_OK;
+                for (int q = 0; q < 4; q++) if ((*brc)[j * 4 + q] != NTC_OK) r = (*brc)[j * 4 + q];
+                if (r == NTC_OK) st[4]++;
+                else {
+                    for (int q = 0; q < 4; q++) out->parts[j * 4 + q].clear();
+                    if (r == NTC_ERR_EMPTY_COLUMN) st[5]++;            // dropped, as the reference does (Q4)
+                    else { out->rc = r; out->msg = "block container failed"; }
+                }
             }
             t_stage[3] += now_s() - t0;
             if (!bytes.push(std::move(*out))) { coded.close(); return; }
@@ -586,29 +710,30 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
     }, [&] { bytes.close(); }); });
 
     // stage 3 (this thread): the hot path + the column codec on the GPU
-    ReadBatch b;
+    BatchPtr b;
     while (batches.pop(&b)) {
-        const uint64_t n = b.offsets.size() - 1;
+        b->wait_filled();
+        const uint64_t n = b->n_reads;
         if (n) {
             const double t0 = now_s();
             CodedBatch cb;
             cb.blocks.resize((n + kBlockReads - 1) / kBlockReads);
             uint64_t n_blocks = 0, n_words = 0, n_rec = 0;
             const uint64_t* words = nullptr;
-            rc = ntc_encode_columns(ctx, b.bases.data(), b.offsets.data(), n, kBlockReads, cb.blocks.data(), cb.blocks.size(), &n_blocks, &words,
+            rc = ntc_encode_columns(ctx, b->bases, b->offsets.data(), n, kBlockReads, cb.blocks.data(), cb.blocks.size(), &n_blocks, &words,
                                     &n_words, &n_rec);
             if (rc == NTC_OK) cb.words.assign(words, words + n_words);   // the pinned buffer is reused by the call after next
             t_stage[2] += now_s() - t0;
             if (rc != NTC_OK) { msg = ntc_last_error(); break; }
-            st[0] += n; st[1] += b.bases.size(); st[2] += n_rec;
+            st[0] += n; st[1] += b->n_bases; st[2] += n_rec;
             if (!coded.push(std::move(cb))) break;
         }
-        const int berr = b.err;
-        spare.push(std::move(b));                                      // the buffer goes back to the assembler with its capacity
-        b = ReadBatch();
+        const int berr = b->err;
+        spare.push(std::move(b));                                      // the buffer goes back to the assembler
         if (berr) {
             rc = berr == 2 ? NTC_ERR_UNSUPPORTED : NTC_ERR_IO;
-            msg = berr == 2 ? "a read of 2^32 bases or more is not supported" : "malformed fastX record near read " + std::to_string(st[0] + 1);
+            msg = berr == 2 ? "a read of 2^32 bases or more is not supported"
+                : berr == 3 ? "cannot page-lock a batch buffer" : "malformed fastX record near read " + std::to_string(st[0] + 1);
             break;
         }
     }
@@ -621,11 +746,12 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
     if (pool.failed()) fatal = true;
     if (rc == NTC_OK && w_rc != NTC_OK) { rc = w_rc; msg = w_msg; }
     }
-    gzclose(in);
+    in.close();
     sink.close();
     if (getenv("NTC_TRACE"))
-        fprintf(stderr, "[ntc trace] encode_file busy seconds: read+cut %.3f, assemble %.3f, gpu %.3f, gzip %.3f, write %.3f\n", t_stage[0],
-                t_stage[1], t_stage[2], t_stage[3], t_stage[4]);
+        fprintf(stderr, "[ntc trace] encode_file busy seconds: cut %.3f, place %.3f, gpu %.3f, gzip (wall, dispatch + wait) %.3f, write %.3f | pool work: "
+                "copy into batch %.3f, headers + gzip %.3f\n", t_stage[0], t_stage[1], t_stage[2], t_stage[3], t_stage[4], copy_us.load() * 1e-6,
+                gzip_us.load() * 1e-6);
     if (stats) memcpy(stats, st, sizeof(st));
     if (rc != NTC_OK) { set_error(msg); return rc; }
     if (fatal) { set_error("out of memory or internal error in a pipeline stage"); return NTC_ERR_IO; }
@@ -738,7 +864,7 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
         TextRef tr;
         while (texts.pop(&tr)) {
             const double t0 = now_s();
-            const bool ok = sink.write(tr.p, tr.n);
+            const bool ok = sink.write(tr.p, tr.n);   // one buffered write per batch: a single file takes ~3.5 GB/s (page-cache / tmpfs writes serialise on the inode; parallel pwrite measured no faster, r2)
             t_stage[2] += now_s() - t0;
             { std::lock_guard<std::mutex> lk(wm); written++; wcv.notify_all(); }
             if (!ok) { w_rc = NTC_ERR_IO; w_msg = "write failed"; texts.close(); { std::lock_guard<std::mutex> lk(wm); writer_gone = true; wcv.notify_all(); } return; }
@@ -792,25 +918,24 @@ int32_t ntc_fastx_load(const char* path, int32_t n_threads, uint8_t** bases_out,
     *bases_out = nullptr; *offsets_out = nullptr; *n_reads = 0;
     if (n_bases) *n_bases = 0;
     if (n_threads <= 0) n_threads = (int32_t)std::max(1u, std::thread::hardware_concurrency());
-    gzFile in = (strcmp(path, "-") == 0) ? gzdopen(0, "rb") : gzopen(path, "rb");
-    if (!in) { set_error(std::string("cannot open ") + path); return NTC_ERR_IO; }
-    gzbuffer(in, 1 << 20);
+    FastxInput in;
+    if (!in.open(path)) { set_error(std::string("cannot open ") + path); return NTC_ERR_IO; }
     std::vector<uint8_t> bases;
     std::vector<uint64_t> off(1, 0);
     int err = 0;
     bool fatal = false;
     try {
         TaskPool pool(n_threads);
-        parallel_fastx(in, pool, (size_t)n_threads * 3 + 8, [&](ParsedPiece& pp) -> bool {
-            bases.insert(bases.end(), pp.bases.begin(), pp.bases.end());
+        parallel_fastx(in, pool, (size_t)n_threads * 3 + 8, [&](const std::shared_ptr<ParsedPiece>& pp) -> bool {
+            bases.insert(bases.end(), pp->bases.begin(), pp->bases.end());
             uint64_t at = off.back();
-            for (uint32_t l : pp.lens) { at += l; off.push_back(at); }
-            if (pp.err) { err = pp.err; return false; }
+            for (uint32_t l : pp->lens) { at += l; off.push_back(at); }
+            if (pp->err) { err = pp->err; return false; }
             return true;
         }, nullptr, &fatal);
         if (pool.failed()) fatal = true;
     } catch (...) { fatal = true; }
-    gzclose(in);
+    in.close();
     if (fatal) { set_error("out of memory or internal error while parsing"); return NTC_ERR_IO; }
     if (err) { set_error(err == 2 ? std::string("a read of 2^32 bases or more in ") + path : std::string("malformed fastX record in ") + path + " near record " + std::to_string(off.size())); return err == 2 ? NTC_ERR_UNSUPPORTED : NTC_ERR_IO; }
     uint8_t* b = (uint8_t*)malloc(bases.size() + 1);

@@ -355,6 +355,27 @@ def test_malformed_headers_are_rejected_by_the_host_reader():
     assert block_read(bytes(b))[0] == 7
 
 
+def test_block_disassemble_and_assemble_round_trip_on_the_host():
+    """the host halves of the fused codec (headers + gzip members) need no GPU: oracle block -> ntc_block_disassemble ->
+    ntc_block_assemble / 4 x ntc_sub_block_assemble (what the file pipeline's gzip tasks call) -> the same bytes"""
+    rng = np.random.default_rng(12)
+    rec = []
+    for i in range(3000):
+        if rng.random() < 0.3:
+            L = int(rng.integers(1, 12))
+            rec.append(int(rng.integers(0, 1 << (2 * L))) | (((i % 7 == 0) + 2) | (L << 2)) << 56)
+        else:
+            rec.append(int(rng.integers(0, 1 << 32)) | (int(rng.integers(12, 1 << 24)) << 32) | (int(i % 7 == 0) << 56))
+    rec = np.array(rec, dtype=np.uint64)
+    want = ob.write_block(rec, 65536)
+    blk, words, used = nt.block_disassemble(want)
+    assert used == len(want) and blk.n_records == len(rec) and blk.num_reads == 65536
+    assert nt.block_assemble(blk, words) == want
+    assert b"".join(nt.sub_block_assemble(blk, q, words) for q in range(4)) == want
+    with pytest.raises(nt.NtcError):
+        nt.sub_block_assemble(blk, 4, words)
+
+
 @pytest.mark.gpu
 def test_block_write_gpu_matches_oracle_bytes():
     """ntc_block_write_gpu (split + codes on the GPU) against the ORACLE's write_block directly (and the host container)"""
@@ -461,6 +482,7 @@ def test_fused_columns_encode_and_decode_match_oracle_blocks():
                 continue
             assert blocks[b].status == 0
             assert nt.block_assemble(blocks[b], words) == want, (n_reads, b)
+            assert b"".join(nt.sub_block_assemble(blocks[b], q, words) for q in range(4)) == want
             kept_blocks.append(blocks[b])
             kept_reads += reads[b * block_reads: b * block_reads + nr]
         assert dropped == (1 if n_reads == 5000 else 0)
