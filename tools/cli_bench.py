@@ -53,21 +53,38 @@ def main():
         r = subprocess.run([CLI, "encode", "-i", prefix, os.path.join(tmp, "reads.fa")] + thr, stdout=f, stderr=subprocess.PIPE)
     if r.returncode:
         raise SystemExit("encode failed: " + r.stderr.decode())
-    sys.stderr.write(r.stderr.decode())
-    enc_log = r.stderr.decode().strip().splitlines()[-1]
+    enc_err = r.stderr.decode()
+    sys.stderr.write(enc_err)
+    enc_log = enc_err.strip().splitlines()[-1]
     t2 = time.time()
     with open(os.path.join(tmp, "decoded.fa"), "wb") as f:
         r = subprocess.run([CLI, "decode", "-i", prefix, os.path.join(tmp, "encoded.dat")] + thr, stdout=f, stderr=subprocess.PIPE)
     if r.returncode:
         raise SystemExit("decode failed: " + r.stderr.decode())
-    sys.stderr.write(r.stderr.decode())
-    dec_log = r.stderr.decode().strip().splitlines()[-1]
+    dec_err = r.stderr.decode()
+    sys.stderr.write(dec_err)
+    dec_log = dec_err.strip().splitlines()[-1]
     t3 = time.time()
     want = b"".join(b">seq.%d\n%s\n" % (i + 1, bytes(bases[i * L:(i + 1) * L])) for i in range(min(cfg["n_reads"], 1000)))
     got = open(os.path.join(tmp, "decoded.fa"), "rb").read()
     n_bases = cfg["n_reads"] * L
     ok = got.startswith(want) and got.endswith(bytes(bases[-L:]) + b"\n") and got.count(b"\n") == 2 * cfg["n_reads"]
+    import hashlib
+    import re
+    def pipe_seconds(log):               # "... | 0.41 s (+0.90 s index)"
+        m = re.search(r"\| ([0-9.]+) s \(\+([0-9.]+) s index\)", log)
+        return (float(m.group(1)), float(m.group(2))) if m else (None, None)
+    def traces(err):                     # NTC_TRACE=1: the stage lines, without the per-call ones
+        return [ln[len("[ntc trace] "):] for ln in err.splitlines()
+                if ln.startswith("[ntc trace]") and "encode_columns ms" not in ln and "decode_columns_fasta ms" not in ln]
+    enc_s, enc_setup = pipe_seconds(enc_log)
+    dec_s, dec_setup = pipe_seconds(dec_log)
     line = {"config": args.config, "reads": cfg["n_reads"], "bases": n_bases, "round_trip_ok": ok,
+            "encode_pipeline_s": enc_s, "encode_setup_s": enc_setup, "decode_pipeline_s": dec_s, "decode_setup_s": dec_setup,
+            "encode_gbases_per_s": n_bases / enc_s / 1e9 if enc_s else None, "decode_gbases_per_s": n_bases / dec_s / 1e9 if dec_s else None,
+            "encoded_sha256": hashlib.sha256(open(os.path.join(tmp, "encoded.dat"), "rb").read()).hexdigest(),
+            "trace": {"encode": traces(enc_err), "decode": traces(dec_err)},
+            "env": {k: v for k, v in os.environ.items() if k.startswith("NTC_")},
             "build_s": t1 - t0, "encode_wall_s": t2 - t1, "decode_wall_s": t3 - t2,
             "encode_log": enc_log, "decode_log": dec_log,
             "encoded_bytes": os.path.getsize(os.path.join(tmp, "encoded.dat")),
