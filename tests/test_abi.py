@@ -75,3 +75,26 @@ def test_kernel_bodies_under_address_sanitizer():
     env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0:protect_shadow_gap=0")
     out = subprocess.run([os.path.join(emul, "asan_driver")], capture_output=True, text=True, env=env, timeout=600)
     assert out.returncode == 0 and "ASAN_DRIVER_OK" in out.stdout, out.stdout[-1500:] + out.stderr[-3000:]
+
+
+def test_rust_sys_crate_declares_every_header_symbol():
+    """rust/ntcomp-b200-sys/src/lib.rs (the FFI crate a Rust host links) is written by hand against the
+    header -- there is no cargo in this image -- so its `extern "C"` block is held to the header's symbol list and argument
+    counts here."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "ntcomp_b200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    rust = open(os.path.join(root, "rust", "ntcomp-b200-sys", "src", "lib.rs")).read()
+    rust = re.sub(r"//[^\n]*", "", rust)
+    c_decl = {m.group(1): m.group(2) for m in re.finditer(r"\b(ntc_[a-zA-Z_0-9]+)\s*\(([^;{]*?)\)\s*;", header)}
+    r_decl = {m.group(1): m.group(2) for m in re.finditer(r"pub fn (ntc_[a-zA-Z_0-9]+)\s*\(([^;{]*?)\)\s*(?:->\s*[^;]+)?;", rust, flags=re.S)}
+    assert set(c_decl) == set(r_decl), (sorted(set(c_decl) - set(r_decl)), sorted(set(r_decl) - set(c_decl)))
+
+    def n_args(s):
+        s = s.strip()
+        return 0 if s in ("", "void") else s.count(",") + 1
+    bad = [n for n in c_decl if n_args(c_decl[n]) != n_args(r_decl[n])]
+    assert not bad, bad
+    for const in ("NTC_USE_ENCODE", "NTC_USE_DECODE", "NTC_BLOCK_FULL_LAST_LITERAL_WORD", "NTC_ERR_EMPTY_COLUMN"):
+        assert const in rust
