@@ -1,6 +1,9 @@
 /* ntcomp_b200.h -- C ABI of the B200-native ntcomp encode/decode hot path (libntcomp_b200.so).
  *
- * Drop-in boundary for tmaklin/ntcomp's sequence codec (reference file:line in each comment).
+ * The boundary a host of tmaklin/ntcomp's sequence codec binds (reference file:line in each comment).  Results are
+ * bit-exact with this repository's CPU oracle (oracle/), a statement-by-statement restatement of src/lib.rs, encode.rs and
+ * decode.rs over restated crate semantics; equality with the Rust binary itself is NOT yet pinned (no toolchain where this
+ * was built; DESIGN.md section 2, INTEGRATION.md section 0 and rust/ref_dump say how to pin it).
  * Plain pointers and sizes only; every call returns an int32 status (NTC_OK == 0) and never
  * throws/panics across the boundary; ntc_last_error() returns the calling thread's last message.
  * One ntc_ctx per GPU, used from one host thread at a time; different contexts are independent.
