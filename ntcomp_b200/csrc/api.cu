@@ -82,6 +82,7 @@ __global__ void __launch_bounds__(256) synth_reads_kernel(const uint8_t* __restr
 }
 
 int32_t status_to_code(uint32_t st) {
+    if (st & ST_READ_TOO_LONG) { set_error("a read of 2^32 bases or more is not supported"); return NTC_ERR_UNSUPPORTED; }
     if (st & ST_BAD_BASE) { set_error("read holds a non-ACGT byte or a base absent from the index (reference underflows at src/lib.rs:207)"); return NTC_ERR_BAD_BASE; }
     if (st & ST_EMPTY_READ) { set_error("empty read (EncodeError, src/lib.rs:224)"); return NTC_ERR_EMPTY_READ; }
     if (st & ST_LEN24) { set_error("record length >= 2^24 (src/lib.rs:226)"); return NTC_ERR_LEN24; }

@@ -30,6 +30,7 @@ enum : uint32_t {
     ST_LEN24 = 1u << 2,
     ST_CAPACITY = 1u << 3,
     ST_BAD_RECORD = 1u << 4,
+    ST_READ_TOO_LONG = 1u << 5,   // a read of 2^32 bases or more: positions inside a read are 32-bit
 };
 
 // Index as the kernels see it.  All arrays are L2-resident at the BASELINE configs

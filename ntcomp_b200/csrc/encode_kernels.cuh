@@ -208,10 +208,11 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
     const uint32_t tile = (uint32_t)item_desc & ((1u << kDescTileBits) - 1u);
     const uint64_t base0 = NTC_LDG(offsets);
     const uint64_t a = offsets[r] - base0;
-    const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
-    if (len == 0) {                                                   // EncodeError, src/lib.rs:224
+    const uint64_t len64 = offsets[r + 1] - offsets[r];
+    const uint32_t len = (uint32_t)len64;
+    if (len == 0 || (len64 >> 32)) {                                  // EncodeError, src/lib.rs:224; or unsupported length
         if (counts) counts[r] = 0;
-        NTC_ATOMIC_OR(status, (uint32_t)ST_EMPTY_READ);
+        NTC_ATOMIC_OR(status, (uint32_t)(len64 >> 32 ? ST_READ_TOO_LONG : ST_EMPTY_READ));
         return;
     }
     const uint32_t n = ix.n, k = ix.k;
@@ -357,7 +358,7 @@ NTC_HD void count_thread(const DevIndex& ix, const uint64_t* __restrict__ packed
     if (r >= n_reads) return;
     const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
     if (len <= T) return;
-    if (*status & ST_BAD_BASE) { counts[r] = 0; return; }             // some d == 0: segmentation would not terminate (Q3)
+    if (*status & (ST_BAD_BASE | ST_READ_TOO_LONG)) { counts[r] = 0; return; }   // some d == 0: segmentation would not terminate (Q3)
     const uint64_t a = offsets[r] - NTC_LDG(offsets);
     uint64_t* sc = scratch + scratch_base(a, r);
     CountSink sink{packed, a, keep_records ? sc + (len - 1u) : nullptr};
