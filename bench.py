@@ -566,10 +566,22 @@ def main():
     if world > 1 and cfg["name"] == "C3" and args.reads is None and not args.no_extras:
         c4 = config_of("C4")
         lo4, hi4 = shard_bounds(c4["n_reads"], world)[rank]
-        m4 = measure(R, c4, lo4, hi4 - lo4, 3, 3, args, want_e2e=not args.no_e2e, e2e_reads_cap=191 * 65536, want_l2=False)
+        # a GPU's share is worked through in passes of at most 382 blocks (25.0 M reads, ~70 GB of workspaces): 2 passes at N = 2
+        passes = shard_bounds(hi4 - lo4, -(-(hi4 - lo4) // (382 * BLOCK_READS)))
+        m4 = None
+        for (a, b) in passes:
+            mp = measure(R, c4, lo4 + a, b - a, 3, 3, args, want_e2e=(m4 is None and not args.no_e2e), e2e_reads_cap=191 * 65536, want_l2=False)
+            release(R, mp)
+            if m4 is None:
+                m4 = mp
+            else:
+                for key in ("t_total", "t_enc", "t_dec", "n_rec", "n_reads", "gpu_launches"):
+                    m4[key] += mp[key]
+                m4["ktimes"] = {k: (m4["ktimes"][k][0] + mp["ktimes"][k][0], m4["ktimes"][k][1] + mp["ktimes"][k][1]) for k in m4["ktimes"]}
         m4["total_bases"] = c4["n_reads"] * c4["read_len"]
         extras["c4"] = summarize_extra(m4, 3, l2["gsectors"], "C4: 12 Mbp genome, k=91, 100 M x 150 bp reads split over %d GPUs on 65,536-read "
-                                       "boundaries (strong split; e2e leg on the first <= 12.5 M reads of each shard)" % world)
+                                       "boundaries (strong split, %d pass(es) of <= 25.0 M reads per GPU; e2e leg on the first <= 12.5 M "
+                                       "reads of each shard)" % (world, len(passes)))
         release(R, m4)
         if world == 8:
             c5 = config_of("C5")

@@ -120,7 +120,13 @@ int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint
     }
     {
         Timed t(ctx, KC_MS, st);
-        ms_kernel<<<blocks_for(max_items, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, (const uint64_t*)lane.desc.p,
+        // NTC_MS_PAD_SMEM: extra dynamic shared memory per block (experiments: how the kernel takes fewer resident blocks per SM)
+        static const size_t pad = [] { const char* e = getenv("NTC_MS_PAD_SMEM"); return e ? (size_t)strtoull(e, nullptr, 10) : (size_t)0; }();
+        if (pad) cudaFuncSetAttribute(ms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
+        // NTC_MS_CARVEOUT: preferred shared-memory carve-out in percent of the maximum (the rest of the 256 KB is L1)
+        static const int carve = [] { const char* e = getenv("NTC_MS_CARVEOUT"); return e ? atoi(e) : -1; }();
+        if (carve >= 0) cudaFuncSetAttribute(ms_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        ms_kernel<<<blocks_for(max_items, kMsThreads), kMsThreads, pad, st>>>(ctx->dix, packed, d_offsets, (const uint64_t*)lane.desc.p,
                                                                             tile_off + n_reads, T, scratch, counts, status, keep_records ? 1 : 0);
     }
     if (counts && n_bases > (uint64_t)T) {                            // no read can exceed T otherwise

@@ -399,7 +399,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 #endif
 
-constexpr uint32_t kMsStageWords = 1024;  // 8 KB of packed reads per block (128 reads x up to 256 bases); longer reads load from global
+#ifndef NTC_MS_STAGE_WORDS
+#define NTC_MS_STAGE_WORDS 1024
+#endif
+constexpr uint32_t kMsStageWords = NTC_MS_STAGE_WORDS;  // 8 KB of packed reads per block (128 reads x up to 256 bases); longer reads load from global
 
 #ifndef NTC_MS_MIN_BLOCKS
 #define NTC_MS_MIN_BLOCKS 10
