@@ -120,14 +120,25 @@ int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint
     }
     {
         Timed t(ctx, KC_MS, st);
-        // NTC_MS_PAD_SMEM: extra dynamic shared memory per block (experiments: how the kernel takes fewer resident blocks per SM)
+        // stage buffer for the block's packed reads: 128 reads of the batch's mean length (+ alignment slack), at most 8 KB
+        const uint64_t mean_len = n_reads ? (n_bases + n_reads - 1) / n_reads : 0;
+        uint32_t stage_words = (uint32_t)std::min<uint64_t>(kMsStageWordsMax, ((kMsThreads * mean_len + 31) / 32 + 8 + 15) & ~15ull);
+        static const long stage_env = [] { const char* e = getenv("NTC_MS_STAGE_WORDS"); return e ? atol(e) : -1L; }();   // experiments
+        if (stage_env >= 0) stage_words = (uint32_t)std::min<long>(stage_env, (long)kMsStageWordsMax) & ~1u;
+        // NTC_MS_PAD_SMEM: extra dynamic shared memory per block (experiments: the kernel against the L1 / shared-memory split)
         static const size_t pad = [] { const char* e = getenv("NTC_MS_PAD_SMEM"); return e ? (size_t)strtoull(e, nullptr, 10) : (size_t)0; }();
-        if (pad) cudaFuncSetAttribute(ms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
-        // NTC_MS_CARVEOUT: preferred shared-memory carve-out in percent of the maximum (the rest of the 256 KB is L1)
         static const int carve = [] { const char* e = getenv("NTC_MS_CARVEOUT"); return e ? atoi(e) : -1; }();
-        if (carve >= 0) cudaFuncSetAttribute(ms_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-        ms_kernel<<<blocks_for(max_items, kMsThreads), kMsThreads, pad, st>>>(ctx->dix, packed, d_offsets, (const uint64_t*)lane.desc.p,
-                                                                            tile_off + n_reads, T, scratch, counts, status, keep_records ? 1 : 0);
+        static const int force_blocks = [] { const char* e = getenv("NTC_MS_BLOCKS"); return e ? atoi(e) : 0; }();
+        const size_t smem = (size_t)stage_words * 8 + pad;
+        const bool twelve = force_blocks ? force_blocks == 12 : stage_words <= 640;
+        auto launch = [&](auto kernel) {
+            if (pad) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (carve >= 0) cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            kernel<<<blocks_for(max_items, kMsThreads), kMsThreads, smem, st>>>(ctx->dix, packed, d_offsets, (const uint64_t*)lane.desc.p,
+                                                                                tile_off + n_reads, T, scratch, counts, status, keep_records ? 1 : 0,
+                                                                                stage_words);
+        };
+        if (twelve) launch(ms_kernel<12>); else launch(ms_kernel<10>);
     }
     if (counts && n_bases > (uint64_t)T) {                            // no read can exceed T otherwise
         Timed t(ctx, KC_SCAN, st);

@@ -399,20 +399,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 #endif
 
-#ifndef NTC_MS_STAGE_WORDS
-#define NTC_MS_STAGE_WORDS 1024
-#endif
-constexpr uint32_t kMsStageWords = NTC_MS_STAGE_WORDS;  // 8 KB of packed reads per block (128 reads x up to 256 bases); longer reads load from global
-
-#ifndef NTC_MS_MIN_BLOCKS
-#define NTC_MS_MIN_BLOCKS 10
-#endif
-__global__ void __launch_bounds__(kMsThreads, NTC_MS_MIN_BLOCKS) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
+constexpr uint32_t kMsStageWordsMax = 1024;  // at most 8 KB of packed reads per block (128 reads x up to 256 bases); longer reads load from global
+// The stage buffer is dynamic shared memory sized for the batch's mean read length (api.cu): 4.75 KB for 150 bp reads.  With
+// 9.8 KB per block twelve blocks fit one SM beside a 124 KB L1 -- the kernel needs ~100 KB of L1 (profiles/r2/ab_ms_scratch_on_chip.txt)
+// -- and twelve blocks of 40 registers measure 11.49 against 11.69 ms for ten of 48 (profiles/r2/ab_ms_blocks.txt).  Batches of longer
+// reads take the ten-block instantiation: twelve blocks with an 8 KB stage each would push the L1 below that size (12.55 ms, r1).
+template <int MIN_BLOCKS>
+__global__ void __launch_bounds__(kMsThreads, MIN_BLOCKS) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
                                                         const uint64_t* __restrict__ offsets, const uint64_t* __restrict__ desc,
                                                         const uint64_t* __restrict__ n_items, uint32_t T,
                                                         uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts,
-                                                        uint32_t* __restrict__ status, int keep_records) {
-    __shared__ __align__(16) uint64_t s_packed[kMsStageWords];
+                                                        uint32_t* __restrict__ status, int keep_records, uint32_t stage_words) {
+    extern __shared__ __align__(16) uint64_t s_packed[];               // stage_words words
     __shared__ uint64_t s_stage[4 * kMsThreads];
     __shared__ __align__(8) uint64_t s_bar;
     // the grid covers an upper bound of the item count (n_reads + n_bases / T); the exact count is on the device
@@ -431,7 +429,7 @@ __global__ void __launch_bounds__(kMsThreads, NTC_MS_MIN_BLOCKS) ms_kernel(DevIn
     const uint64_t hi = offsets[rb] - base0 + (len_b > T ? tmin<uint64_t>(len_b, ((uint64_t)tb + 1) * T) : len_b);
     const uint64_t w_lo = (lo >> 5) & ~1ull;                                 // 16-byte aligned
     const uint64_t w_hi = ((hi >> 5) + 2) & ~1ull;                           // exclusive, 16-byte aligned (buffer is padded)
-    const bool staged = (w_hi - w_lo) <= kMsStageWords;
+    const bool staged = (w_hi - w_lo) <= stage_words;
     if (staged) {
         if (threadIdx.x == 0) mbar_init(&s_bar, 1);
         __syncthreads();
