@@ -312,7 +312,8 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
         t_cuda = since();
     });
     const int threads = (int)std::max(1u, std::thread::hardware_concurrency());
-    std::vector<uint32_t> rank, lcs, pfx;
+    std::vector<uint32_t> rank, pfx;
+    std::vector<ntc_lcsx_t> lcs;
     std::vector<uint64_t> jump;
     uint32_t c_start[4] = {0, 0, 0, 0};
     const bool use_pfx = idx->k >= 10 && !getenv("NTC_NO_PREFIX_TABLE");   // a tile's warm-up (k-1 bases) must cover the 8 bases
@@ -360,7 +361,7 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
         return NTC_ERR_CUDA;
     };
     ctx->index_bytes[0] = rank.size() * 4;
-    ctx->index_bytes[1] = lcs.size() * 4;
+    ctx->index_bytes[1] = lcs.size() * sizeof(ntc_lcsx_t);
     ctx->index_bytes[2] = jump.size() * 8;
     if (uses & NTC_USE_ENCODE) {
         if ((e = cudaMalloc(&ctx->d_rank, ctx->index_bytes[0])) != cudaSuccess) return fail("cudaMalloc rank", e);
@@ -388,7 +389,7 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
     }
     ctx->stream = ctx->lanes[0].stream;
     ctx->dix.rank = (const uint4*)ctx->d_rank;
-    ctx->dix.lcsx = (const uint32_t*)ctx->d_lcs;
+    ctx->dix.lcsx = (const ntc_lcsx_t*)ctx->d_lcs;
     ctx->dix.jump = (const uint64_t*)ctx->d_jump;
     ctx->dix.pfx = (const uint4*)ctx->d_pfx;
     ctx->dix.n = (uint32_t)idx->n;

@@ -38,7 +38,7 @@ enum : uint32_t {
 struct DevIndex {
     const uint4* rank;     // [(n/32+1) * 4] entries, c = entry index & 3: {C[c] + ones of row c before the block,
                            //   row bits, Q bits, 0}
-    const uint32_t* lcsx;  // [n + 1] LCS[i] | dist to previous smaller << 8 | LCS[i+1] << 16 | dist to next smaller of i+1 << 24
+    const ntc_lcsx_t* lcsx;  // [n + 1] LCS side array (layout.h)
     const uint64_t* jump;  // [n] pred^16 | chars16 << 32
     const uint4* pfx;      // [4^8 * 2] prefix table (host_index.h), null when k < 10
     uint32_t c_start[4];   // interval start after the single base c
@@ -139,6 +139,19 @@ NTC_HD uint32_t ld4_keep_if(const uint32_t* ptr, uint64_t pol, bool on) {
 #else
     (void)pol;
     return on ? *ptr : 0u;
+#endif
+}
+NTC_HD uint32_t ld2_keep_if(const unsigned short* ptr, uint64_t pol, bool on) {
+#if defined(__CUDA_ARCH__)
+    uint32_t v;
+    asm volatile(
+        "{\n .reg .pred p;\n .reg .u16 h;\n setp.ne.u32 p, %3, 0;\n mov.u16 h, 0;\n"
+        " @p ld.global.nc.L2::cache_hint.u16 h, [%1], %2;\n cvt.u32.u16 %0, h;\n}"
+        : "=&r"(v) : "l"(ptr), "l"(pol), "r"((uint32_t)on));
+    return v;
+#else
+    (void)pol;
+    return on ? (uint32_t)*ptr : 0u;
 #endif
 }
 NTC_HD uint2 ld8x2_keep_if(const uint4* ptr, uint64_t pol, bool on) {   // first two words of a rank entry

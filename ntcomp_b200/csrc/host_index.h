@@ -40,7 +40,7 @@ void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out /* 16 u3
 // LCS words for O(1) contract_left: u32 word i = LCS[i] | min(255, i - PSV(i)) << 8 | LCS[i+1] << 16 |
 // min(255, NSV(i+1) - (i+1)) << 24, PSV / NSV = nearest position left / right with a strictly smaller
 // LCS (LCS[n_sets] = 0 is the sentinel).  Saturated distances fall back to a scan on the device.
-void build_lcs_words(const ntc_index& idx, std::vector<uint32_t>* out);
+void build_lcs_words(const ntc_index& idx, std::vector<ntc_lcsx_t>* out);
 void spec_window(uint64_t n_sets, uint32_t* lo, uint32_t* span);
 
 // Prefix table for the first kPrefixBases bases of a read (or of a tile's warm-up): entry x (base i of the prefix at

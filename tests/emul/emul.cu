@@ -20,7 +20,7 @@ struct EmulIndex {
     uint32_t tile_len = 1u << 22;
     std::vector<uint32_t> rank;
     std::vector<uint64_t> jump;
-    std::vector<uint32_t> lcs;
+    std::vector<ntc_lcsx_t> lcs;
     std::vector<uint32_t> pfx;
     DevIndex dix;
 };

@@ -98,3 +98,43 @@ def test_rust_sys_crate_declares_every_header_symbol():
     assert not bad, bad
     for const in ("NTC_USE_ENCODE", "NTC_USE_DECODE", "NTC_BLOCK_FULL_LAST_LITERAL_WORD", "NTC_ERR_EMPTY_COLUMN"):
         assert const in rust
+
+
+@pytest.mark.gpu
+def test_one_direction_contexts_and_pinned_buffers():
+    """ntc_ctx_create_for: an encode-only context holds no jump table and refuses to decode (and the reverse) with
+    NTC_ERR_UNSUPPORTED instead of touching memory it does not have; both produce what a full context produces.
+    ntc_pinned_alloc hands out page-locked memory the host-buffer entry points accept like any other pointer."""
+    import ctypes as C
+    rng = np.random.default_rng(21)
+    g = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=20000)]
+    idx = nt.Index.build([g], 31)
+    reads = [g[p: p + 150].copy() for p in rng.integers(0, 20000 - 150, size=300)]
+    bases, off = nt.concat_reads(reads)
+    full = nt.Context(idx, 0)
+    enc = nt.Context(idx, 0, uses=nt.Context.USE_ENCODE)
+    dec = nt.Context(idx, 0, uses=nt.Context.USE_DECODE)
+    rec, roff = full.encode_batch(bases, off)
+    rec_e, roff_e = enc.encode_batch(bases, off)
+    assert (rec == rec_e).all() and (roff == roff_e).all()
+    assert enc.index_bytes()["jump"] > 0 and dec.index_bytes()["rank"] > 0      # sizes are reported either way ...
+    text, n = dec.decode_fasta(rec, 1)
+    assert (text, n) == full.decode_fasta(rec, 1)
+    with pytest.raises(nt.NtcError) as e:
+        enc.decode_fasta(rec, 1)
+    assert e.value.code == 9
+    with pytest.raises(nt.NtcError) as e:
+        dec.encode_batch(bases, off)
+    assert e.value.code == 9
+    with pytest.raises(nt.NtcError):
+        nt.Context(idx, 0, uses=0)
+    # pinned buffers through the ABI
+    L = _lib.lib()
+    p = C.c_void_p()
+    _lib.check(L.ntc_pinned_alloc(len(bases), C.byref(p)))
+    C.memmove(p, bases.ctypes.data, len(bases))
+    out = np.zeros(len(bases), dtype=np.uint64)
+    n_rec = C.c_uint64(0)
+    _lib.check(L.ntc_encode_batch(full._h, p, off.ctypes.data_as(C.c_void_p), len(reads), out.ctypes.data_as(C.c_void_p), len(out), C.byref(n_rec), None))
+    assert n_rec.value == len(rec) and (out[: len(rec)] == rec).all()
+    L.ntc_pinned_free(p)
