@@ -291,6 +291,11 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
     t_index = time.time() - t0
     t0 = time.time()
     ctx = nt.Context(index, R.local_rank)
+    # host-buffer leg: with four or more ranks copying on one host the two PCIe directions are not additive on this pool's boxes
+    # (profiles/r2/e2e_probe_n8.json: 29.8 GB/s up alone, 14.9 down alone, 19.3 for both together per GPU), so results travel
+    # after the input instead of beside it; NTC_COPY_DIRECTIONS overrides
+    copy_serial = os.environ.get("NTC_COPY_DIRECTIONS", "serial" if world >= 4 else "duplex") == "serial"
+    ctx.set_copy_directions(copy_serial)
     out["setup_s"] = {"index_build_or_load": t_index, "ctx_create": time.time() - t0}
     out["index_bytes"] = ctx.index_bytes()
 
@@ -414,6 +419,7 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
         d2h = n_rec_e * 8 + int(n_bytes_c.value)
         e2e = {"value": nbe * world * e2e_steps / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "steps": e2e_steps, "api": "ntc_encode_batch + ntc_decode_fasta, pinned host buffers", "reads_per_gpu": ne,
+               "copy_directions": "serial (all input up, then results down)" if copy_serial else "duplex (results travel back while the next chunk goes up)",
                "encode_ms_per_step": 1e3 * split[0] / e2e_steps, "decode_ms_per_step": 1e3 * split[1] / e2e_steps,
                "pcie_h2d_gbs": pcie[0], "pcie_d2h_gbs": pcie[1],   # per GPU, all ranks copying at once (min over ranks)
                "pcie_floor_ms_per_step": (h2d / pcie[0] + d2h / pcie[1]) / 1e6 if pcie[0] else None}

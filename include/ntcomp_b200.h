@@ -89,6 +89,13 @@ void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]);
  * 0 (default) = chosen per batch; otherwise >= 256, rounded up to a multiple of 4. */
 int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len);
 
+/* Host-buffer entry points: serial == 0 (default) moves results back while the next chunk of input goes up (both PCIe
+ * directions busy); serial != 0 sends all input first and the results afterwards.  Same results either way.  On a host
+ * whose DMA paths share a ceiling, mixing the directions costs more than the overlap gains (8 GPUs copying at once on the
+ * round-2 box: 29.8 GB/s up alone, 14.9 down alone, 19.3 for both together; profiles/r2/e2e_probe_n8.json).
+ * The environment variable NTC_COPY_DIRECTIONS=serial|duplex sets the initial value. */
+int32_t ntc_ctx_set_copy_directions(ntc_ctx* ctx, int32_t serial);
+
 /* ---------------- encode ------------------------------------------------------------------- */
 
 /* flat_map(encode_dictionary . encode_sequence) over a batch of reads: src/main.rs:166,169 with

@@ -167,6 +167,10 @@ class Context:
         """matching-statistics tile length (0 = automatic); results do not depend on it"""
         check(_lib.lib().ntc_ctx_set_tile_len(self._h, int(tile_len)))
 
+    def set_copy_directions(self, serial):
+        """host-buffer API: one PCIe direction at a time (True) or results travelling back while input goes up (False)"""
+        check(_lib.lib().ntc_ctx_set_copy_directions(self._h, int(bool(serial))))
+
     def encode_file(self, fastx_path, out_path, n_threads=0):
         """`ntcomp encode` (src/main.rs:141-181): fastX file -> encoded.dat; returns the stats dict"""
         st = np.zeros(6, dtype=np.uint64)

@@ -351,6 +351,7 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
         unsigned long long v = strtoull(env, nullptr, 10);
         if (v >= 1024) ctx->max_chunk_bases = v;
     }
+    if (const char* env = getenv("NTC_COPY_DIRECTIONS")) ctx->copy_serial = strcmp(env, "serial") == 0;
     if (const char* env = getenv("NTC_MAX_CHUNK_RECORDS")) {
         unsigned long long v = strtoull(env, nullptr, 10);
         if (v >= 16) ctx->max_chunk_records = v;
@@ -442,6 +443,7 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
         for (DevBuf* b : lb) release(b);
     }
     free_column_work(ctx);
+    release(&ctx->hold); release(&ctx->hold2);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
     for (auto ev : ctx->event_pool) cudaEventDestroy(ev);
     cudaFree(ctx->d_rank); cudaFree(ctx->d_lcs); cudaFree(ctx->d_jump); cudaFree(ctx->d_pfx);
@@ -466,6 +468,12 @@ int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len) {
     if (tile_len && tile_len < kTileMin) { set_error("tile length must be 0 (automatic) or >= 256"); return NTC_ERR_INVALID_ARG; }
     if (tile_len > (1u << 22)) tile_len = 1u << 22;
     ctx->tile_len = (tile_len + 3u) & ~3u;
+    return NTC_OK;
+}
+
+int32_t ntc_ctx_set_copy_directions(ntc_ctx* ctx, int32_t serial) {
+    if (!ctx) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    ctx->copy_serial = serial != 0;
     return NTC_OK;
 }
 

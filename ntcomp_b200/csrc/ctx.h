@@ -56,6 +56,12 @@ struct ntc_ctx {
     ntc::Lane lanes[2];             // lanes[0] also serves the device-resident API (on the caller's stream)
     uint64_t max_chunk_records = 4ull << 20;  // host-buffer decode: records per chunk (NTC_MAX_CHUNK_RECORDS overrides)
     cudaStream_t stream = nullptr;  // == lanes[0].stream
+    // Host-buffer API: 0 = both PCIe directions at once (results travel back while the next chunk's input goes up),
+    // 1 = one direction at a time (all input first, results afterwards).  On a host whose copy engines share a ceiling
+    // -- 8 GPUs copying on the round-2 box: 29.8 GB/s up alone, 14.9 down alone, 19.3 for BOTH together -- mixing the
+    // directions costs more than the overlap gains (profiles/r2/e2e_probe_n8.json).  NTC_COPY_DIRECTIONS=serial|duplex.
+    int copy_serial = 0;
+    ntc::DevBuf hold, hold2;        // copy_serial: records / offsets of a whole call parked in HBM
     void* colwork = nullptr;        // workspaces + pinned landing buffers of the GPU column codec, both directions (api_columns.inc)
 
     // optional per-kernel-class timing with CUDA events on the launching stream (bench.py roofline)

@@ -117,7 +117,8 @@ def test_one_direction_contexts_and_pinned_buffers():
     rec, roff = full.encode_batch(bases, off)
     rec_e, roff_e = enc.encode_batch(bases, off)
     assert (rec == rec_e).all() and (roff == roff_e).all()
-    assert enc.index_bytes()["jump"] > 0 and dec.index_bytes()["rank"] > 0      # sizes are reported either way ...
+    assert enc.index_bytes()["jump"] == 0 and enc.index_bytes()["rank"] > 0      # only the arrays of one direction are resident
+    assert dec.index_bytes()["rank"] == 0 and dec.index_bytes()["lcs"] == 0 and dec.index_bytes()["jump"] > 0
     text, n = dec.decode_fasta(rec, 1)
     assert (text, n) == full.decode_fasta(rec, 1)
     with pytest.raises(nt.NtcError) as e:

@@ -300,6 +300,24 @@ def test_chunked_host_path_matches_unchunked(monkeypatch, small_cases):
     assert e.value.code == 5
     rec3, roff3 = ctx2.encode_batch(bases, off)
     assert (rec3 == rec).all() and (roff3 == roff).all()
+    # one PCIe direction at a time (ntc_ctx_set_copy_directions): records parked in HBM until the input is up, all records
+    # up before any text comes down -- same results, chunked and unchunked, including the capacity error
+    for c in (ctx2, case0.ctx):
+        c.set_copy_directions(True)
+        try:
+            rec4, roff4 = c.encode_batch(bases, off)
+            assert (rec4 == rec).all() and (roff4 == roff).all()
+            tri4, _ = c.encode_sequence_batch(bases, off)
+            assert (tri4 == tri).all()
+            db4, doff4 = c.decode_batch(rec4)
+            assert (db4 == bases).all() and (doff4 == off).all()
+            text, n = c.decode_fasta(rec4, 9995)
+            assert text == helpers.fasta_text(reads, 9995) and n == len(reads)
+            with pytest.raises(nt.NtcError) as e:
+                _decode_with_cap(c, rec4, len(bases) - 5)
+            assert e.value.code == 3
+        finally:
+            c.set_copy_directions(False)
 
 
 @pytest.mark.parametrize("cfg", ["C2-small", "C3-small", "C5-small"])
