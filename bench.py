@@ -291,10 +291,10 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
     t_index = time.time() - t0
     t0 = time.time()
     ctx = nt.Context(index, R.local_rank)
-    # host-buffer leg: with four or more ranks copying on one host the two PCIe directions are not additive on this pool's boxes
-    # (profiles/r2/e2e_probe_n8.json: 29.8 GB/s up alone, 14.9 down alone, 19.3 for both together per GPU), so results travel
-    # after the input instead of beside it; NTC_COPY_DIRECTIONS overrides
-    copy_serial = os.environ.get("NTC_COPY_DIRECTIONS", "serial" if world >= 4 else "duplex") == "serial"
+    # host-buffer leg: both PCIe directions at once by default.  The one-direction-at-a-time mode (NTC_COPY_DIRECTIONS=serial) was
+    # built for hosts where mixed traffic is slower than either direction alone (8 GPUs on this pool's boxes) and measured no
+    # better there -- ranks drift out of phase, so the host sees mixed traffic anyway (profiles/r2/ab_copy_directions.txt)
+    copy_serial = os.environ.get("NTC_COPY_DIRECTIONS", "duplex") == "serial"
     ctx.set_copy_directions(copy_serial)
     out["setup_s"] = {"index_build_or_load": t_index, "ctx_create": time.time() - t0}
     out["index_bytes"] = ctx.index_bytes()
