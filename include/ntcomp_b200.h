@@ -90,10 +90,10 @@ void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]);
 int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len);
 
 /* Host-buffer entry points: serial == 0 (default) moves results back while the next chunk of input goes up (both PCIe
- * directions busy); serial != 0 sends all input first and the results afterwards.  Same results either way.  On a host
- * whose DMA paths share a ceiling, mixing the directions costs more than the overlap gains (8 GPUs copying at once on the
- * round-2 box: 29.8 GB/s up alone, 14.9 down alone, 19.3 for both together; profiles/r2/e2e_probe_n8.json).
- * The environment variable NTC_COPY_DIRECTIONS=serial|duplex sets the initial value. */
+ * directions busy); serial != 0 sends all input first and the results afterwards.  Same results either way.  Meant for hosts
+ * where mixed-direction DMA is slower than either direction alone (8 GPUs copying at once on the round-2 box: 29.8 GB/s up
+ * alone, 14.9 down alone, 19.3 for both together); measured there it gains nothing because the ranks are out of phase
+ * (profiles/r2/ab_copy_directions.txt), so the default is duplex.  NTC_COPY_DIRECTIONS=serial|duplex sets the initial value. */
 int32_t ntc_ctx_set_copy_directions(ntc_ctx* ctx, int32_t serial);
 
 /* ---------------- encode ------------------------------------------------------------------- */

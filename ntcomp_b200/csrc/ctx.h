@@ -59,7 +59,8 @@ struct ntc_ctx {
     // Host-buffer API: 0 = both PCIe directions at once (results travel back while the next chunk's input goes up),
     // 1 = one direction at a time (all input first, results afterwards).  On a host whose copy engines share a ceiling
     // -- 8 GPUs copying on the round-2 box: 29.8 GB/s up alone, 14.9 down alone, 19.3 for BOTH together -- mixing the
-    // directions costs more than the overlap gains (profiles/r2/e2e_probe_n8.json).  NTC_COPY_DIRECTIONS=serial|duplex.
+    // directions looked costlier than the overlap gains (profiles/r2/e2e_probe_n8.json); measured, serial gains nothing there
+    // (ranks out of phase: profiles/r2/ab_copy_directions.txt), so the default is 0.  NTC_COPY_DIRECTIONS=serial|duplex.
     int copy_serial = 0;
     ntc::DevBuf hold, hold2;        // copy_serial: records / offsets of a whole call parked in HBM
     void* colwork = nullptr;        // workspaces + pinned landing buffers of the GPU column codec, both directions (api_columns.inc)
