@@ -436,7 +436,7 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
 def measure_columns(ctx, h_bases, h_off, n_reads, read_len, lo, hbm_peak):
     """Row f1: the fused column codec (ntc_encode_columns / ntc_decode_columns_fasta) on the first blocks of the batch.
     Kernel time = CUDA events around the column kernels on the launching stream (classes column_encode / column_decode)."""
-    n = min(n_reads, 16 * BLOCK_READS)
+    n = min(n_reads, 16 * BLOCK_READS, max(1, (192 << 20) // read_len))          # 16 blocks of short reads, ~200 MB of long ones
     if n < 1:
         return None
     bases = h_bases[: n * read_len].numpy()

@@ -291,7 +291,8 @@ class Context:
         check(_lib.lib().ntc_decode_columns_fasta(self._h, C.cast(arr, C.c_void_p), len(blocks), _ptr(words) if len(words) else None, len(words),
                                                   first_seq_number, 1 if full_last_literal_word else 0, C.byref(tp), C.byref(nb), C.byref(ns),
                                                   C.byref(nr)))
-        text = C.string_at(tp, nb.value) if nb.value else b""
+        # (C.string_at takes a C int: texts of 2 GiB and more need the array route)
+        text = memoryview((C.c_ubyte * nb.value).from_address(tp.value)).tobytes() if nb.value else b""
         return text, ns.value, nr.value
 
     # ---- device-resident API (raw device pointers as ints, e.g. torch.Tensor.data_ptr()) ----
