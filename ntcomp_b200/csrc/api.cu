@@ -247,6 +247,20 @@ int32_t decode_walk(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint64_
         // (a two-pass variant -- walk to 2-bit slots per record, then one thread per sequence formatting header + bases
         // left to right -- measured slower on B200: 3.31 vs 2.56 ms on C3, 9.6 vs 6.0 ms on C5; r1 A/B, profiles/r1)
         Timed t(ctx, KC_WALK, st);
+        // experiment (NTC_WALK_WINDOW=<hit ratio in percent>, with NTC_L2_PERSIST_MB set): persisting access window over the jump table
+        static const int win = [] { const char* e = getenv("NTC_WALK_WINDOW"); return e ? atoi(e) : 0; }();
+        if (win > 0) {
+            cudaStreamAttrValue av;
+            memset(&av, 0, sizeof av);
+            int maxw = 0;
+            cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, ctx->device);
+            av.accessPolicyWindow.base_ptr = ctx->d_jump;
+            av.accessPolicyWindow.num_bytes = std::min<size_t>(ctx->index_bytes[2], (size_t)maxw);
+            av.accessPolicyWindow.hitRatio = win / 100.0f;
+            av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+            av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av);
+        }
         walk_kernel<<<blocks_for(n_rec, kWalkThreads), kWalkThreads, 0, st>>>(ctx->dix, d_records, n_rec, (const uint64_t*)lane.base_off.p,
                                                             (const uint64_t*)lane.seq_idx.p, (const uint64_t*)lane.seq_endkey.p,
                                                             (const uint64_t*)lane.dec_small.p, first_no, fasta, d_out, cap, d_counts,
