@@ -53,6 +53,15 @@ const char* ntc_version(void);
 int32_t ntc_index_build(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n_seqs, uint32_t k,
                         int32_t add_revcomp, int32_t n_threads, ntc_index** out);
 
+/* The same construction on the GPU ("next" row f4: `ntcomp build`, src/main.rs:97-140): both strands of all sequences become
+ * one 2-bit text in HBM, the k-mer occurrences are radix-sorted by their k-mer in colex order (4 characters per pass, gathered
+ * from the text -- keys are never materialised), distinct k-mers, sources, '$'-padded dummy nodes, LCS and the subset rows
+ * follow from scans, binary searches and one merge.  Same index, bit for bit, as ntc_index_build.  No CPU fallback.
+ * stats (nullable, 8 doubles): [0] ms until the input is in HBM, [1] ms of device work + download, [2] k-mer occurrences,
+ * [3] distinct k-mers, [4] source k-mers, [5] dummy nodes, [6] radix passes, [7] kernel launches. */
+int32_t ntc_index_build_gpu(int32_t device, const uint8_t* const* seqs, const uint64_t* lens, uint64_t n_seqs, uint32_t k,
+                            int32_t add_revcomp, ntc_index** out, double* stats);
+
 /* Flattened view of an existing SbwtIndex<SubsetMatrix> + LcsArray (what a Rust host passes after
  * kbo::index::load_sbwt, src/main.rs:149,190): 4 subset rows of n_sets bits (LSB-first u64 words,
  * A,C,G,T) and LCS as one byte per node.  C is recomputed from the rows. */

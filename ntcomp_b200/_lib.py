@@ -23,6 +23,7 @@ SIGNATURES = {
     "ntc_last_error": (C.c_char_p, []),
     "ntc_version": (C.c_char_p, []),
     "ntc_index_build": (_i32, [_vp, _vp, _u64, _u32, _i32, _i32, _pp]),
+    "ntc_index_build_gpu": (_i32, [_i32, _vp, _vp, _u64, _u32, _i32, _pp, _vp]),
     "ntc_index_from_arrays": (_i32, [_u32, _u64, _vp, _vp, _vp, _vp, _vp, _pp]),
     "ntc_index_save": (_i32, [_vp, C.c_char_p]),
     "ntc_index_load": (_i32, [C.c_char_p, _pp]),

@@ -77,6 +77,23 @@ class Index:
         return cls(h)
 
     @classmethod
+    def build_gpu(cls, seqs, k, add_revcomp=True, device=0, stats=None):
+        """The same construction on the GPU (ntc_index_build_gpu; `ntcomp build`, src/main.rs:97-140).  `stats`, when a
+        dict, receives the phase times and counts the call reports."""
+        L = _lib.lib()
+        arrs = [_u8(s) for s in seqs]
+        n = len(arrs)
+        ptrs = (C.c_void_p * max(n, 1))(*[a.ctypes.data for a in arrs])
+        lens = np.array([len(a) for a in arrs], dtype=np.uint64)
+        h = C.c_void_p()
+        st = np.zeros(8, dtype=np.float64)
+        check(L.ntc_index_build_gpu(device, C.cast(ptrs, C.c_void_p), _ptr(lens), n, k, int(add_revcomp), C.byref(h), _ptr(st)))
+        if stats is not None:
+            stats.update(upload_ms=float(st[0]), device_ms=float(st[1]), occurrences=int(st[2]), distinct=int(st[3]),
+                         sources=int(st[4]), dummies=int(st[5]), radix_passes=int(st[6]), launches=int(st[7]))
+        return cls(h)
+
+    @classmethod
     def from_arrays(cls, k, n_sets, rows, lcs):
         L = _lib.lib()
         rows = [np.ascontiguousarray(r, dtype=np.uint64) for r in rows]

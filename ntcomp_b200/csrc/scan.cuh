@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(Load load, ui
 // Every thread owns one contiguous run of tiles (serial sum, ONE block-wide scan, serial write-back): the first
 // version scanned 256 tiles per round with three barriers each -- 75 rounds and 82 us for the 19 k tiles of C3's
 // record scan (ncu r1 launch list), as long as the reduce pass that reads all the records.
-__global__ void __launch_bounds__(kScanThreads) scan_tiles_kernel(Pair64* tile_sums, uint64_t n_tiles, const uint64_t* carry_in,
+static __global__ void __launch_bounds__(kScanThreads) scan_tiles_kernel(Pair64* tile_sums, uint64_t n_tiles, const uint64_t* carry_in,
                                                                   uint64_t* totals) {
     const uint64_t per = (n_tiles + kScanThreads - 1) / kScanThreads;
     const uint64_t lo = tmin<uint64_t>(n_tiles, per * threadIdx.x), hi = tmin<uint64_t>(n_tiles, lo + per);

@@ -6,6 +6,7 @@
 #include <cstring>
 #include <vector>
 
+#include "../../ntcomp_b200/csrc/build_pipeline.h"
 #include "../../ntcomp_b200/csrc/column_decode_kernels.cuh"
 #include "../../ntcomp_b200/csrc/column_kernels.cuh"
 #include "../../ntcomp_b200/csrc/column_plan.h"
@@ -258,3 +259,48 @@ int64_t emul_column_decode(const uint64_t* words_be, uint64_t n_words, uint64_t 
 }
 
 }  // extern "C"
+
+// ---- GPU index construction (build_pipeline.h) with loops in place of launches -------------------------------------
+// for_each = one call per element in order, scan = a serial exclusive sum calling the post hook, sort = one stable
+// counting sort per digit with the product's digit functor (what the radix kernels compute, pass for pass).
+namespace {
+struct CpuExec {
+    std::vector<void*> owned;
+    bool failed() const { return false; }
+    template <class T> T* alloc(uint64_t n) { void* p = calloc(n ? n : 1, sizeof(T)); owned.push_back(p); return (T*)p; }
+    void zero(void* p, uint64_t bytes) { memset(p, 0, bytes); }
+    template <class F> void for_each(uint64_t n, F f) { for (uint64_t i = 0; i < n; i++) f(i); }
+    template <class L, class P> uint64_t scan(L load, uint64_t n, P post) {
+        Pair64 run{0, 0};
+        for (uint64_t i = 0; i < n; i++) { const Pair64 v = load(i); post(i, run, v); run = run + v; }
+        return run.a;
+    }
+    template <class D> uint32_t* sort(uint32_t* a, uint32_t* b, uint64_t n, uint32_t n_digits, D digit) {
+        for (uint32_t t = 0; t < n_digits; t++) {
+            uint64_t pos[257] = {0};
+            for (uint64_t i = 0; i < n; i++) pos[digit(a[i], t) + 1]++;
+            for (int d = 0; d < 256; d++) pos[d + 1] += pos[d];
+            for (uint64_t i = 0; i < n; i++) b[pos[digit(a[i], t)]++] = a[i];
+            uint32_t* s2 = a; a = b; b = s2;
+        }
+        return a;
+    }
+    void download(void* host, const void* dev, uint64_t bytes) { memcpy(host, dev, bytes); }
+    ~CpuExec() { for (void* p : owned) free(p); }
+};
+}  // namespace
+
+extern "C" int32_t emul_index_build(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n_seqs, uint32_t k, int32_t add_revcomp,
+                                    ntc_index** out, uint64_t* stats /* [7], nullable */) {
+    *out = nullptr;
+    uint64_t fwd_len = 0;
+    for (uint64_t s2 = 0; s2 < n_seqs; s2++) fwd_len += lens[s2] + 1;
+    std::vector<uint8_t> fwd(fwd_len ? fwd_len : 1);
+    uint64_t o = 0;
+    for (uint64_t s2 = 0; s2 < n_seqs; s2++) { if (lens[s2]) memcpy(fwd.data() + o, seqs[s2], lens[s2]); o += lens[s2]; fwd[o++] = '\n'; }
+    CpuExec x;
+    bld::BuildStats bs;
+    const int32_t rc = bld::sbwt_build(x, fwd.data(), fwd_len, k, add_revcomp != 0, out, &bs);
+    if (stats) { stats[0] = bs.text_chars; stats[1] = bs.occurrences; stats[2] = bs.distinct; stats[3] = bs.sources; stats[4] = bs.dummies; stats[5] = bs.nodes; stats[6] = bs.sort_passes; }
+    return rc;
+}

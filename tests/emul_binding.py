@@ -36,8 +36,26 @@ def lib():
         L.emul_dict_pack.argtypes = [vp, vp, u64, vp]
         L.emul_decode.restype = u32
         L.emul_decode.argtypes = [vp, vp, u64, u64, i32, vp, u64, vp, u64, vp]
+        L.emul_index_build.restype = i32
+        L.emul_index_build.argtypes = [vp, vp, u64, u32, i32, C.POINTER(vp), vp]
         _LIB = L
     return _LIB
+
+
+def index_build(seqs, k, add_revcomp=True, stats=None):
+    """build_pipeline.h (the GPU index construction) run with loops on the CPU -> nt.Index"""
+    arrs = [np.ascontiguousarray(np.frombuffer(bytes(s), dtype=np.uint8) if isinstance(s, (bytes, bytearray)) else s, dtype=np.uint8) for s in seqs]
+    n = len(arrs)
+    ptrs = (C.c_void_p * max(n, 1))(*[a.ctypes.data for a in arrs])
+    lens = np.array([len(a) for a in arrs], dtype=np.uint64)
+    h = C.c_void_p()
+    st = np.zeros(7, dtype=np.uint64)
+    rc = lib().emul_index_build(C.cast(ptrs, C.c_void_p), _ptr(lens), n, k, int(add_revcomp), C.byref(h), _ptr(st))
+    if rc:
+        raise nt.NtcError(rc, "emulated index construction failed")
+    if stats is not None:
+        stats.update(zip(("text_chars", "occurrences", "distinct", "sources", "dummies", "nodes", "sort_passes"), (int(v) for v in st)))
+    return nt.Index(h)
 
 
 def _ptr(a):

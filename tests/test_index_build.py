@@ -76,3 +76,110 @@ def test_synthetic_generator_matches_numpy_restatement():
         assert (got == want).all() and (off == woff).all()
     hit = synth.reads(g, 1, 0, 100, 150, 50_000)[0] != synth.reads(g, 1, 0, 100, 150, 0)[0]
     assert 0.03 < float(hit.mean()) < 0.07                       # substitutions always change the base
+
+
+# ---- row f4: the GPU construction (ntc_index_build_gpu; build_pipeline.h + build_kernels.cuh) ---------------------------
+# "emul" runs the very same functors and order of operations with loops on the CPU (tests/emul, CpuExec: a stable counting
+# sort per digit in place of the radix kernels); "gpu" is the product call.  Both must equal the host builder bit for bit,
+# and (first test) the oracle's independent construction.
+
+def _gpu_builders():
+    return [pytest.param("emul", id="emul"), pytest.param("gpu", id="gpu", marks=pytest.mark.gpu)]
+
+
+def _build_with(backend, seqs, k, rc, stats=None):
+    if backend == "emul":
+        import emul_binding
+        return emul_binding.index_build(seqs, k, rc, stats)
+    return nt.Index.build_gpu(seqs, k, rc, stats=stats)
+
+
+def _same_index(a, b):
+    assert a.n_sets == b.n_sets and a.k == b.k
+    assert (a.C() == b.C()).all()
+    for x, y in zip(a.rows(), b.rows()):
+        assert (x == y).all()
+    assert (a.lcs() == b.lcs()).all()
+
+
+def _as_arrays(seqs):
+    return [np.frombuffer(bytes(s), dtype=np.uint8) if isinstance(s, (bytes, bytearray)) else s for s in seqs]
+
+
+@pytest.mark.parametrize("backend", _gpu_builders())
+@pytest.mark.parametrize("k", [12, 13, 16, 31, 32, 33, 64, 91, 96, 97, 128, 200, 255])
+def test_gpu_construction_matches_host_builder_and_oracle(backend, k):
+    rng = np.random.default_rng(k)
+    seqs = [helpers.random_seq(rng, int(n)) for n in rng.choice([0, 5, k - 1, k, k + 3, 500, 3000], size=4)]
+    seqs.append(np.frombuffer(b"ACGTNNACGT" * 30 + b"N" + b"ACGGT" * 60, dtype=np.uint8))
+    for rc in (True, False):
+        g = _build_with(backend, seqs, k, rc)
+        _same_index(g, nt.Index.build(seqs, k, rc))
+        _same(ob.OracleIndex.build(seqs, k, rc), g)
+
+
+@pytest.mark.parametrize("backend", _gpu_builders())
+def test_gpu_construction_degenerate_and_repetitive_inputs(backend):
+    rep = [b"A" * 300, b"ACACACACAC" * 40, b"ACGT" * 100 + b"T" * 25 + b"ACGT" * 50]
+    for k in (12, 31, 91):
+        for rc in (True, False):
+            _same_index(_build_with(backend, _as_arrays(rep), k, rc), nt.Index.build(_as_arrays(rep), k, rc))
+    # nothing to index (root only), a single k-mer, k + 1 bases, only separators, lower case (not ACGT for the builder)
+    for seqs in ([], [b""], [b"ACGT"], [b"ACGTACGTACGT"], [b"ACGTACGTACGTA"], [b"NNNN"], [b"acgtacgtacgtacgt"]):
+        for rc in (True, False):
+            _same_index(_build_with(backend, _as_arrays(seqs), 12, rc), nt.Index.build(_as_arrays(seqs), 12, rc))
+
+
+@pytest.mark.parametrize("backend", _gpu_builders())
+def test_gpu_construction_predecessor_found_only_by_search(backend):
+    """A k-mer seen only at the start of a sequence is a source unless some other k-mer ENDS with its (k-1)-prefix -- e.g.
+    the last k-mer of another sequence, which is not its neighbour in any text: the binary-search path of PredBySearch."""
+    rng = np.random.default_rng(3)
+    for k in (12, 31, 33, 91):
+        W, y, V = (bytes(helpers.random_seq(rng, n)) for n in (200, k - 1, 150))
+        cases = [[W + y, y + b"C" + V], [W + y, y + b"C" + V, y + b"G" + V[:40]], [W + y + b"N" + y + b"T" + V], [W, W[5:]],
+                 [W, W[5:5 + k]], [y + b"A", b"C" + y]]
+        for seqs in cases:
+            for rc in (True, False):
+                _same_index(_build_with(backend, _as_arrays(seqs), k, rc), nt.Index.build(_as_arrays(seqs), k, rc))
+
+
+@pytest.mark.parametrize("backend", _gpu_builders())
+def test_gpu_construction_many_short_sequences(backend):
+    rng = np.random.default_rng(7)
+    for it in range(24):
+        k = int(rng.integers(12, 80))
+        alpha = list(b"ACGT" if it % 3 else b"AC") + ([ord("N")] if it % 5 == 0 else [])
+        seqs = [bytes(rng.choice(alpha, size=int(rng.integers(0, 3 * k))).astype(np.uint8)) for _ in range(int(rng.integers(1, 40)))]
+        if it % 4 == 0:
+            seqs += seqs[:3]
+        _same_index(_build_with(backend, _as_arrays(seqs), k, bool(it & 1)), nt.Index.build(_as_arrays(seqs), k, bool(it & 1)))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("genome_len,k", [(300_000, 31), (1_000_000, 91), (700_000, 255)])
+def test_gpu_construction_larger_genomes(genome_len, k):
+    """Many radix blocks per pass (the emulation never runs the radix kernels themselves): one random contig plus a copy of a
+    piece of it (duplicate k-mers across sequences) and a few short ones."""
+    from ntcomp_b200 import synth
+    g = synth.genome(genome_len)
+    seqs = [g, g[1000:60_000].copy(), g[:k].copy(), g[5:5 + 2 * k].copy()]
+    st = {}
+    a = nt.Index.build_gpu(seqs, k, True, stats=st)
+    _same_index(a, nt.Index.build(seqs, k, True))
+    assert st["launches"] > 0 and st["occurrences"] >= 2 * (genome_len - k + 1)
+
+
+def test_gpu_construction_needs_a_gpu_or_succeeds():
+    """no CPU fallback: without a device the call fails with NTC_ERR_CUDA"""
+    import torch
+    g = np.frombuffer(b"ACGT" * 100, dtype=np.uint8)
+    if torch.cuda.is_available():
+        assert nt.Index.build_gpu([g], 12).n_sets == nt.Index.build([g], 12).n_sets
+    else:
+        with pytest.raises(nt.NtcError) as e:
+            nt.Index.build_gpu([g], 12)
+        assert e.value.code == 2
+    with pytest.raises(nt.NtcError) as e:
+        nt.Index.build_gpu([g], 11)
+    assert e.value.code == 9
