@@ -140,10 +140,40 @@ int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint
         };
         if (twelve) launch(ms_kernel<12>); else launch(ms_kernel<10>);
     }
+    lane.seg_len = 0;
     if (counts && n_bases > (uint64_t)T) {                            // no read can exceed T otherwise
-        Timed t(ctx, KC_SCAN, st);
-        count_kernel<<<blocks_for(n_reads, 256), 256, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, T, scratch, counts, status,
-                                                               keep_records ? 1 : 0);
+        // One thread per read (count_kernel) walks a read's cover as one chain of dependent loads; the segment path cuts it into
+        // 512-position pieces.  Measured on B200 (profiles/r2/ab_seg_parallel.txt): with enough reads to fill the GPU the two cost
+        // the same (C5, 250 k x 10 kbp: 7.09 vs 7.43 ms for count + emit; both walk every record's entry once or twice out of DRAM),
+        // with few long sequences -- contigs handed in as reads, as the reference's own test does -- the chain's latency is all
+        // there is and the segments win by the number of pieces.  So: segments when the reads cannot fill the machine
+        // (fewer than 148 SMs x 1024 threads).  NTC_SEG_SERIAL=1 / 0 forces either.
+        static const int force_serial = [] { const char* e = getenv("NTC_SEG_SERIAL"); return e ? (atoi(e) != 0 ? 1 : 0) : -1; }();
+        const bool serial = force_serial >= 0 ? force_serial == 1 : n_reads >= 148u * 1024u;
+        if (keep_records && !serial) {
+            // records of reads longer than the tile: speculative walk per 512-position segment, joined per read; seg_emit_kernel
+            // (encode_pipeline) writes the words once the offsets are known
+            static const uint32_t force_S = [] { const char* e = getenv("NTC_SEG_LEN"); return e ? (uint32_t)atoi(e) & ~63u : 0u; }();
+            const uint32_t S = force_S >= 64 ? force_S : seg_len_for(n_bases, n_reads);
+            const uint64_t max_segs = n_bases / S + n_reads;
+            NTC_CUDA_TRY(ensure(&lane.seg_off, (n_reads + 2) * 8 + 16));
+            NTC_CUDA_TRY(ensure(&lane.seg_desc, (max_segs + 1) * 8));
+            NTC_CUDA_TRY(ensure(&lane.seg_bits, (max_segs + 1) * (S / 64) * 8));
+            NTC_CUDA_TRY(ensure(&lane.seg_info, (max_segs + 1) * 16));
+            uint64_t* seg_off = (uint64_t*)lane.seg_off.p;
+            Timed t(ctx, KC_SCAN, st, 5);
+            exclusive_scan_pairs(SegLoad{d_offsets, T, S}, n_reads, (Pair64*)lane.tiles.p, nullptr, seg_off + n_reads + 2, seg_off, nullptr, st,
+                                 TileDescPost{(uint64_t*)lane.seg_desc.p});
+            seg_spec_kernel<<<blocks_for(max_segs, 256), 256, 0, st>>>(ctx->dix, d_offsets, T, S, scratch, (const uint64_t*)lane.seg_desc.p,
+                                                                       seg_off + n_reads, (uint64_t*)lane.seg_bits.p, (uint32_t*)lane.seg_info.p, status);
+            seg_join_kernel<<<blocks_for(n_reads, 256), 256, 0, st>>>(ctx->dix, d_offsets, n_reads, T, S, scratch, seg_off, (const uint64_t*)lane.seg_bits.p,
+                                                                      (uint32_t*)lane.seg_info.p, counts, status);
+            lane.seg_len = S;
+        } else {
+            Timed t(ctx, KC_SCAN, st);
+            count_kernel<<<blocks_for(n_reads, 256), 256, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, T, scratch, counts, status,
+                                                                   keep_records ? 1 : 0);
+        }
     }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
@@ -196,12 +226,19 @@ int32_t encode_pipeline(ntc_ctx* ctx, Lane& lane, int mode, const uint8_t* d_bas
     if (lane.ev_scan) NTC_CUDA_TRY(cudaEventRecord(lane.ev_scan, st));
     {
         Timed t(ctx, KC_EMIT, st);
-        if (mode == 0)
+        if (mode == 0) {
             emit_kernel<0><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                                   rec_off, rel, d_out, cap, ctx->d_status, T);
-        else
+                                                                                   rec_off, rel, d_out, cap, ctx->d_status, T, lane.seg_len ? 1 : 0);
+            if (lane.seg_len) {
+                ctx->launches++; ctx->class_launches[KC_EMIT]++;
+                seg_emit_kernel<<<blocks_for(n_bases / lane.seg_len + n_reads, 256), 256, 0, st>>>(
+                    ctx->dix, packed, d_offsets, T, lane.seg_len, scratch, (const uint64_t*)lane.seg_desc.p, (const uint64_t*)lane.seg_off.p + n_reads,
+                    (const uint32_t*)lane.seg_info.p, counts, rec_off, rel, d_out, cap, ctx->d_status);
+            }
+        } else {
             emit_kernel<1><<<blocks_for(n_reads, kMsThreads), kMsThreads, 0, st>>>(ctx->dix, packed, d_offsets, n_reads, scratch, counts,
-                                                                                   rec_off, rel, d_out, cap, ctx->d_status, T);
+                                                                                   rec_off, rel, d_out, cap, ctx->d_status, T, 0);
+        }
     }
     NTC_CUDA_TRY(cudaGetLastError());
     return NTC_OK;
@@ -453,7 +490,7 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
         if (ln.ev_scan) cudaEventDestroy(ln.ev_scan);
         if (ln.ev_done) cudaEventDestroy(ln.ev_done);
         if (ln.h_land) cudaFreeHost(ln.h_land);
-        DevBuf* lb[] = {&ln.packed, &ln.scratch, &ln.counts, &ln.tiles, &ln.rec_off, &ln.tile_off, &ln.desc, &ln.base_off, &ln.seq_idx, &ln.seq_first, &ln.seq_endkey, &ln.dec_tiles, &ln.dec_small, &ln.st_in, &ln.st_off, &ln.st_out, &ln.st_out2};
+        DevBuf* lb[] = {&ln.packed, &ln.scratch, &ln.counts, &ln.tiles, &ln.rec_off, &ln.tile_off, &ln.desc, &ln.seg_off, &ln.seg_desc, &ln.seg_bits, &ln.seg_info, &ln.base_off, &ln.seq_idx, &ln.seq_first, &ln.seq_endkey, &ln.dec_tiles, &ln.dec_small, &ln.st_in, &ln.st_off, &ln.st_out, &ln.st_out2};
         for (DevBuf* b : lb) release(b);
     }
     free_column_work(ctx);

@@ -26,6 +26,8 @@ struct Lane {
     cudaStream_t stream = nullptr;
     DevBuf packed, scratch, counts, tiles, rec_off;   // encode workspaces
     DevBuf tile_off, desc;                            // tiles per read (scanned) and work-item descriptors of ms_kernel
+    DevBuf seg_off, seg_desc, seg_bits, seg_info;     // long reads: segmentation segments (encode_kernels.cuh, seg_*_thread)
+    uint32_t seg_len = 0;                             // != 0: the last ms_pipeline on this lane took the segment path with this S
     DevBuf st_in, st_off, st_out, st_out2;            // staging for host buffers
     // decode workspaces: base offsets / sequence ids per record, first record and layout word per sequence,
     // scan tiles, and dec_small = [0..1] scan totals (bases, sequences), [2..3] counts (sequences, bytes)

@@ -95,27 +95,39 @@ NTC_HD uint32_t unique_run(const uint64_t* sc, uint32_t q, uint32_t T, uint32_t 
     return tmin(total, limit);
 }
 
+// one record of the greedy cover: the cursor i (exclusive end, > 0) moves to the next record's end.  The step depends on
+// nothing but i and the scratch entries, so two walks that ever share a cursor position coincide from there on.
+// SPEC (the speculative walks of seg_spec_thread): a step whose left extension exceeds kSpecExtCap is not taken -- returns false
+// with i untouched -- so that a walk started in the middle of a very long match costs a bounded number of loads.
+constexpr uint32_t kSpecExtCap = 4096;
+template <bool SPEC = false, typename Sink>
+NTC_HD bool segment_step(const uint64_t* sc, uint32_t& i, uint32_t k, uint32_t T, Sink&& sink) {
+    uint64_t ent = sc[i - 1];
+    uint32_t d = entry_d(ent), v = entry_s(ent);
+    if (d == k && i > k + 1) {                                        // src/lib.rs:180
+        const uint32_t max_ext = i - k - 1;
+        uint32_t ext = unique_run(sc, i - 2, T, SPEC ? tmin(max_ext, kSpecExtCap) : max_ext);   // left_extend_kmer, src/lib.rs:186
+        if (SPEC && ext == kSpecExtCap && max_ext > kSpecExtCap) return false;
+        uint32_t new_len = k + ext, m = new_len, old_i = i;
+        for (;;) {                                                    // hop loop, src/lib.rs:193-203
+            uint32_t dd = entry_d(sc[i - 1]);
+            if (dd < m) { m -= dd; i -= dd; } else break;
+        }
+        uint32_t L = new_len - (m - 1);                               // src/lib.rs:199
+        i -= 1;                                                       // src/lib.rs:213-214
+        sink(L, v, old_i, k);
+    } else {                                                          // src/lib.rs:204-211
+        sink(d, v, i, d);
+        i -= d;
+    }
+    return true;
+}
 template <typename Sink>
 NTC_HD uint32_t segment_read(const uint64_t* sc,   // no __restrict__: CountSink parks records in dead entries
                               uint32_t len, uint32_t k, uint32_t T, Sink&& sink) {
     uint32_t i = len, cnt = 0;
     while (i > 0) {
-        uint64_t ent = sc[i - 1];
-        uint32_t d = entry_d(ent), v = entry_s(ent);
-        if (d == k && i > k + 1) {                                    // src/lib.rs:180
-            uint32_t ext = unique_run(sc, i - 2, T, i - k - 1);       // left_extend_kmer, src/lib.rs:186
-            uint32_t new_len = k + ext, m = new_len, old_i = i;
-            for (;;) {                                                // hop loop, src/lib.rs:193-203
-                uint32_t dd = entry_d(sc[i - 1]);
-                if (dd < m) { m -= dd; i -= dd; } else break;
-            }
-            uint32_t L = new_len - (m - 1);                           // src/lib.rs:199
-            i -= 1;                                                   // src/lib.rs:213-214
-            sink(L, v, old_i, k);
-        } else {                                                      // src/lib.rs:204-211
-            sink(d, v, i, d);
-            i -= d;
-        }
+        segment_step(sc, i, k, T, sink);
         cnt++;
     }
     return cnt;
@@ -379,6 +391,137 @@ NTC_HD void count_thread(const DevIndex& ix, const uint64_t* __restrict__ packed
     if (sink.big) NTC_ATOMIC_OR(status, (uint32_t)ST_LEN24);
 }
 
+// ---- long reads: the segmentation cut into segments ---------------------------------------------------------------
+// count_thread walks a 10 kbp read as ONE chain of ~600 dependent, scattered scratch loads (C5: 5.4 ms for 250 k reads, an eighth
+// of the step).  The cover is a deterministic walk over cursor positions (segment_step), and walks that meet stay together -- they
+// meet at the first mismatch below both, where every match ends -- so the walk is cut into segments of S cursor positions (512 .. 16,384):
+//   A  seg_spec_thread, one thread per segment: a SPECULATIVE walk from the segment's top cursor to its bottom; remembers the
+//      cursors it visited (one bit each), how many records that was and where it left the segment;
+//   B  seg_join_thread, one thread per read: the TRUE walk, top down -- inside a segment it steps until it stands on a cursor the
+//      speculative walk visited (usually within a record or two), then takes that walk's count and exit; notes where the true
+//      walk entered each segment and how many records came before;
+//   C  seg_emit_thread, one thread per segment, after the record offsets are scanned: walks again from the true entry and
+//      writes the record words straight to their final place (these reads park nothing and emit_kernel<0> skips them).
+// Same records as count_thread + emit_kernel<0>, in 20 x as many independent chains.
+// Segment length S: a multiple of 64 (one bitmap word per 64 cursors), chosen per batch (seg_len_for): 512 for reads up to a few
+// 10 kbp; longer for contig-sized sequences, where the per-read join (one step per segment, ~1.2 us each on B200) would
+// otherwise dominate -- 5 Mbp in one read: 12 ms of join at S = 512.
+constexpr uint32_t kSegLenMin = 512, kSegLenMax = 16384;
+inline uint32_t seg_len_for(uint64_t n_bases, uint64_t n_reads) {
+    const uint64_t mean = n_reads ? n_bases / n_reads : 0;
+    uint32_t S = kSegLenMin;
+    while (S < kSegLenMax && (uint64_t)S * S < mean * 32) S *= 2;    // join ~ len / S steps per read, walk ~ S / 32 steps per segment
+    return S;
+}
+struct SegLoad {             // scan input: segments of a read (only reads longer than the tile length take this path)
+    const uint64_t* offsets;
+    uint32_t T, S;
+    NTC_HD Pair64 operator()(uint64_t r) const {
+        const uint64_t len = offsets[r + 1] - offsets[r];
+        return Pair64{len > T && !(len >> 32) ? (len + S - 1) / S : 0, 0};
+    }
+};
+struct NullSink {
+    NTC_HD void operator()(uint32_t, uint32_t, uint32_t, uint32_t) const {}
+};
+// seg_info: 4 x u32 per segment = records of the speculative walk, its exit cursor (below the segment, or the cursor inside it at
+// which the walk gave up: not marked, the true walk steps on from there), the true walk's entry cursor (0: the true walk jumps
+// over this segment), records of the read before that entry
+NTC_HD void seg_spec_thread(const DevIndex& ix, const uint64_t* __restrict__ offsets, uint32_t T, uint32_t S, const uint64_t* __restrict__ scratch,
+                            const uint64_t* __restrict__ desc, uint64_t* __restrict__ seg_bits, uint32_t* __restrict__ seg_info,
+                            const uint32_t* __restrict__ status, uint64_t gi) {
+    const uint64_t r = desc[gi] >> kDescTileBits;
+    const uint32_t g = (uint32_t)desc[gi] & ((1u << kDescTileBits) - 1u);
+    const uint64_t a = offsets[r] - NTC_LDG(offsets);
+    const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
+    const uint64_t* sc = scratch + scratch_base(a, r);
+    const uint32_t lo = g * S, top = tmin(len, lo + S);
+    uint64_t* bits = seg_bits + gi * (S / 64);
+    uint32_t cnt = 0, i = top;
+    if (*status & (ST_BAD_BASE | ST_READ_TOO_LONG)) i = lo;           // some d == 0: the walk would not move (Q3)
+    int w = (int)(S / 64) - 1;                                        // the walk descends: one bitmap word at a time
+    uint64_t cur = 0;
+    while (i > lo) {
+        const uint32_t b = i - lo - 1;
+        while ((int)(b >> 6) < w) { bits[w] = cur; cur = 0; w--; }
+        if (!segment_step<true>(sc, i, ix.k, T, NullSink())) break;   // too long a step to take on speculation: the true walk goes on from here
+        cur |= 1ull << (b & 63);
+        cnt++;
+    }
+    for (; w >= 0; w--) { bits[w] = cur; cur = 0; }
+    seg_info[4 * gi + 0] = cnt;
+    seg_info[4 * gi + 1] = i;
+    seg_info[4 * gi + 2] = 0;
+    seg_info[4 * gi + 3] = 0;
+}
+NTC_HD void seg_join_thread(const DevIndex& ix, const uint64_t* __restrict__ offsets, uint64_t n_reads, uint32_t T, uint32_t S,
+                            const uint64_t* __restrict__ scratch, const uint64_t* __restrict__ seg_off, const uint64_t* __restrict__ seg_bits,
+                            uint32_t* __restrict__ seg_info, uint32_t* __restrict__ counts, uint32_t* __restrict__ status, uint64_t r) {
+    if (r >= n_reads) return;
+    const uint64_t len64 = offsets[r + 1] - offsets[r];
+    const uint32_t len = (uint32_t)len64;
+    if (len64 <= T || (len64 >> 32)) return;
+    if (*status & (ST_BAD_BASE | ST_READ_TOO_LONG)) { counts[r] = 0; return; }
+    const uint64_t a = offsets[r] - NTC_LDG(offsets);
+    const uint64_t* sc = scratch + scratch_base(a, r);
+    const uint64_t s0 = seg_off[r];
+    uint32_t i = len, cnt = 0;
+    while (i > 0) {
+        const uint32_t g = (i - 1) / S, lo = g * S;
+        const uint64_t gi = s0 + g;
+        const uint64_t* bits = seg_bits + gi * (S / 64);
+        seg_info[4 * gi + 2] = i;
+        seg_info[4 * gi + 3] = cnt;
+        while (i > lo) {
+            const uint32_t b = i - lo - 1;
+            if ((bits[b >> 6] >> (b & 63)) & 1ull) {                  // the speculative walk stood here: same walk from now on
+                // records of that walk from here on = all of them minus the cursors it visited above this one; the walks meet
+                // near the top of the segment, so that is a word or two (counting the words below cost 17 us per segment at S = 16,384)
+                uint32_t above = (b & 63) == 63 ? 0u : (uint32_t)NTC_POPCLL(bits[b >> 6] & (~0ull << ((b & 63) + 1)));
+                for (uint32_t w = (b >> 6) + 1; w < S / 64; w++) above += (uint32_t)NTC_POPCLL(bits[w]);
+                cnt += seg_info[4 * gi + 0] - above;
+                i = seg_info[4 * gi + 1];                             // below the segment, or the cursor at which that walk gave up
+                continue;
+            }
+            segment_step(sc, i, ix.k, T, NullSink());
+            cnt++;
+        }
+    }
+    counts[r] = cnt;
+}
+struct SegEmitSink {
+    const uint64_t* __restrict__ packed;
+    uint64_t* __restrict__ out;
+    uint64_t a, first;
+    uint32_t big = 0;
+    NTC_HD void operator()(uint32_t L, uint32_t v, uint32_t end_pos, uint32_t) {
+        big |= (L >= (1u << 24));
+        uint64_t word;
+        if (L > kLiteralMax) word = (uint64_t)v | ((uint64_t)(L & 0xFFFFFFu) << 32) | (first << 56);       // src/encode.rs:146-149
+        else word = packed_slice(packed, a + end_pos - L, L) | (((first + 2) | ((uint64_t)L << 2)) << 56);  // src/encode.rs:150-156
+        *out++ = word;
+        first = 0;
+    }
+};
+NTC_HD void seg_emit_thread(const DevIndex& ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offsets, uint32_t T, uint32_t S,
+                            const uint64_t* __restrict__ scratch, const uint64_t* __restrict__ desc, const uint32_t* __restrict__ seg_info,
+                            const uint32_t* __restrict__ counts, const uint64_t* __restrict__ rec_offsets, const uint64_t* __restrict__ rel,
+                            uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status, uint64_t gi) {
+    uint32_t i = seg_info[4 * gi + 2];
+    if (i == 0) return;                                               // the true walk never stood in this segment
+    const uint64_t r = desc[gi] >> kDescTileBits;
+    const uint32_t g = (uint32_t)desc[gi] & ((1u << kDescTileBits) - 1u);
+    if (counts[r] == 0) return;
+    const uint64_t rel0 = rel ? NTC_LDG(rel) : 0;
+    if (rec_offsets[r + 1] - rel0 > cap) { NTC_ATOMIC_OR(status, (uint32_t)ST_CAPACITY); return; }
+    const uint64_t a = offsets[r] - NTC_LDG(offsets);
+    const uint64_t* sc = scratch + scratch_base(a, r);
+    const uint32_t before = seg_info[4 * gi + 3], lo = g * S;
+    SegEmitSink sink{packed, out + (rec_offsets[r] - rel0) + before, a, before == 0 ? 1ull : 0ull};
+    while (i > lo) segment_step(sc, i, ix.k, T, sink);
+    if (sink.big) NTC_ATOMIC_OR(status, (uint32_t)ST_LEN24);
+}
+
 #if defined(__CUDACC__)
 // 1-D bulk TMA (cp.async.bulk) of `bytes` (multiple of 16) from global to shared memory, completion
 // on an mbarrier; issued by one thread.
@@ -461,6 +604,29 @@ __global__ void __launch_bounds__(256) count_kernel(DevIndex ix, const uint64_t*
     count_thread(ix, packed, offsets, n_reads, T, scratch, counts, status, keep_records != 0, (uint64_t)blockIdx.x * 256 + threadIdx.x);
 }
 
+__global__ void __launch_bounds__(256) seg_spec_kernel(DevIndex ix, const uint64_t* __restrict__ offsets, uint32_t T, uint32_t S,
+                                                       const uint64_t* __restrict__ scratch, const uint64_t* __restrict__ desc,
+                                                       const uint64_t* __restrict__ n_segs, uint64_t* __restrict__ seg_bits,
+                                                       uint32_t* __restrict__ seg_info, const uint32_t* __restrict__ status) {
+    const uint64_t gi = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (gi < *n_segs) seg_spec_thread(ix, offsets, T, S, scratch, desc, seg_bits, seg_info, status, gi);
+}
+__global__ void __launch_bounds__(256) seg_join_kernel(DevIndex ix, const uint64_t* __restrict__ offsets, uint64_t n_reads, uint32_t T, uint32_t S,
+                                                       const uint64_t* __restrict__ scratch, const uint64_t* __restrict__ seg_off,
+                                                       const uint64_t* __restrict__ seg_bits, uint32_t* __restrict__ seg_info,
+                                                       uint32_t* __restrict__ counts, uint32_t* __restrict__ status) {
+    seg_join_thread(ix, offsets, n_reads, T, S, scratch, seg_off, seg_bits, seg_info, counts, status, (uint64_t)blockIdx.x * 256 + threadIdx.x);
+}
+__global__ void __launch_bounds__(256) seg_emit_kernel(DevIndex ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offsets,
+                                                       uint32_t T, uint32_t S, const uint64_t* __restrict__ scratch, const uint64_t* __restrict__ desc,
+                                                       const uint64_t* __restrict__ n_segs, const uint32_t* __restrict__ seg_info,
+                                                       const uint32_t* __restrict__ counts, const uint64_t* __restrict__ rec_offsets,
+                                                       const uint64_t* __restrict__ rel, uint64_t* __restrict__ out, uint64_t cap,
+                                                       uint32_t* __restrict__ status) {
+    const uint64_t gi = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (gi < *n_segs) seg_emit_thread(ix, packed, offsets, T, S, scratch, desc, seg_info, counts, rec_offsets, rel, out, cap, status, gi);
+}
+
 // ------------------------------------------------------------------------------------------
 // emit: MODE 0 = packed u64 records (encode_dictionary . encode_sequence),
 //       MODE 1 = (len, start, end) triples (encode_sequence alone)
@@ -495,7 +661,7 @@ template <int MODE>
 NTC_HD void emit_thread(const DevIndex& ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offsets, uint64_t n_reads,
                         const uint64_t* __restrict__ scratch, const uint32_t* __restrict__ counts, const uint64_t* __restrict__ rec_offsets,
                         const uint64_t* __restrict__ rel, uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status, uint32_t T,
-                        uint64_t r) {
+                        uint64_t r, bool segs = false) {
     // rec_offsets are absolute (a carry from earlier chunks is folded in); `out` is this chunk's
     // buffer, so positions are taken relative to *rel (the number of records before the chunk)
     if (r >= n_reads) return;
@@ -504,6 +670,7 @@ NTC_HD void emit_thread(const DevIndex& ix, const uint64_t* __restrict__ packed,
     const uint64_t base0 = NTC_LDG(offsets);
     const uint64_t a = offsets[r] - base0;
     const uint32_t len = (uint32_t)(offsets[r + 1] - offsets[r]);
+    if (MODE == 0 && segs && len > T) return;                         // written by seg_emit_kernel, nothing parked
     if (rec_offsets[r + 1] - rel0 > cap) { NTC_ATOMIC_OR(status, (uint32_t)ST_CAPACITY); return; }
     const uint64_t* sc = scratch + scratch_base(a, r);
     if (MODE == 0) {
@@ -523,9 +690,10 @@ __global__ void __launch_bounds__(kMsThreads) emit_kernel(DevIndex ix, const uin
                                                           const uint64_t* __restrict__ offsets, uint64_t n_reads,
                                                           const uint64_t* __restrict__ scratch, const uint32_t* __restrict__ counts,
                                                           const uint64_t* __restrict__ rec_offsets, const uint64_t* __restrict__ rel,
-                                                          uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status, uint32_t T) {
+                                                          uint64_t* __restrict__ out, uint64_t cap, uint32_t* __restrict__ status, uint32_t T,
+                                                          int segs) {
     emit_thread<MODE>(ix, packed, offsets, n_reads, scratch, counts, rec_offsets, rel, out, cap, status, T,
-                      (uint64_t)blockIdx.x * kMsThreads + threadIdx.x);
+                      (uint64_t)blockIdx.x * kMsThreads + threadIdx.x, segs != 0);
 }
 
 // encode_dictionary alone (src/encode.rs:129-166): triples -> record words, literal bases from the

@@ -58,6 +58,9 @@ extern "C" {
     // ---- index (host) ----
     pub fn ntc_index_build(seqs: *const *const u8, lens: *const u64, n_seqs: u64, k: u32, add_revcomp: i32, n_threads: i32,
                            out: *mut *mut ntc_index) -> i32;
+    /// `ntcomp build` on the GPU (row f4): same index as ntc_index_build; stats = 8 f64 or null
+    pub fn ntc_index_build_gpu(device: i32, seqs: *const *const u8, lens: *const u64, n_seqs: u64, k: u32, add_revcomp: i32,
+                               out: *mut *mut ntc_index, stats: *mut f64) -> i32;
     pub fn ntc_index_from_arrays(k: u32, n_sets: u64, row_a: *const u64, row_c: *const u64, row_g: *const u64, row_t: *const u64,
                                  lcs: *const u8, out: *mut *mut ntc_index) -> i32;
     pub fn ntc_index_save(idx: *const ntc_index, path: *const c_char) -> i32;

@@ -49,8 +49,17 @@ void* emul_index_create(const ntc_index* idx) {
 void emul_index_free(void* p) { delete (EmulIndex*)p; }
 void emul_set_tile_len(void* p, uint32_t T) { ((EmulIndex*)p)->tile_len = T ? (T + 3u) & ~3u : 1u << 22; }
 
+// state of the segment path (long reads in record mode; api.cu: ms_pipeline / encode_pipeline)
+struct EmulSegs {
+    bool live = false;
+    uint32_t S = 0;
+    std::vector<uint64_t> off, desc, bits;
+    std::vector<uint32_t> info;
+};
+
 static void run_ms(const EmulIndex* e, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads, std::vector<uint64_t>* packed,
-                   std::vector<uint64_t>* scratch, uint64_t** scratch_aligned, uint32_t* counts, uint32_t* status, bool keep_records = false) {
+                   std::vector<uint64_t>* scratch, uint64_t** scratch_aligned, uint32_t* counts, uint32_t* status, bool keep_records = false,
+                   EmulSegs* segs = nullptr) {
     uint64_t nb = offsets[n_reads] - offsets[0];
     packed->assign(nb / 32 + 6, 0);
     scratch->assign(scratch_entries(nb, n_reads) + 4, 0);
@@ -69,7 +78,26 @@ static void run_ms(const EmulIndex* e, const uint8_t* bases, const uint64_t* off
     uint64_t stage[4];
     // items in reverse order: tiles of a read must not depend on the order in which they run
     for (uint64_t i = tile_off[n_reads]; i-- > 0;) ms_thread(e->dix, packed->data(), offsets, desc[i], T, sc, counts, status, stage, 1, keep_records);
-    if (counts) for (uint64_t r = 0; r < n_reads; r++) count_thread(e->dix, packed->data(), offsets, n_reads, T, sc, counts, status, keep_records, r);
+    if (!counts) return;
+    if (keep_records && segs && nb > T && !getenv("NTC_SEG_SERIAL")) {
+        const char* fs = getenv("NTC_SEG_LEN");
+        const uint32_t S = fs ? (uint32_t)atoi(fs) & ~63u : seg_len_for(nb, n_reads);
+        segs->S = S;
+        SegLoad sl{offsets, T, S};
+        segs->off.assign(n_reads + 1, 0);
+        for (uint64_t r = 0; r < n_reads; r++) segs->off[r + 1] = segs->off[r] + sl(r).a;
+        const uint64_t n_segs = segs->off[n_reads];
+        segs->desc.assign(n_segs + 1, ~0ull);
+        TileDescPost spost{segs->desc.data()};
+        for (uint64_t r = 0; r < n_reads; r++) spost(r, Pair64{segs->off[r], 0}, sl(r));
+        segs->bits.assign((n_segs + 1) * (S / 64), ~0ull);          // garbage, as fresh device memory would be
+        segs->info.assign((n_segs + 1) * 4, 0xDEADBEEFu);
+        for (uint64_t gi = n_segs; gi-- > 0;) seg_spec_thread(e->dix, offsets, T, S, sc, segs->desc.data(), segs->bits.data(), segs->info.data(), status, gi);
+        for (uint64_t r = 0; r < n_reads; r++) seg_join_thread(e->dix, offsets, n_reads, T, S, sc, segs->off.data(), segs->bits.data(), segs->info.data(), counts, status, r);
+        segs->live = true;
+        return;
+    }
+    for (uint64_t r = 0; r < n_reads; r++) count_thread(e->dix, packed->data(), offsets, n_reads, T, sc, counts, status, keep_records, r);
 }
 
 // mode 0 records, 1 triples.  Returns the accumulated status bits.
@@ -80,13 +108,17 @@ uint32_t emul_encode(void* ep, const uint8_t* bases, const uint64_t* offsets, ui
     std::vector<uint64_t> packed, scratch;
     std::vector<uint32_t> counts(n_reads + 1, 0);
     uint64_t* sc = nullptr;
-    run_ms(e, bases, offsets, n_reads, &packed, &scratch, &sc, counts.data(), &status, mode == 0);
+    EmulSegs segs;
+    run_ms(e, bases, offsets, n_reads, &packed, &scratch, &sc, counts.data(), &status, mode == 0, &segs);
     std::vector<uint64_t> roff(n_reads + 1, 0);
     for (uint64_t r = 0; r < n_reads; r++) roff[r + 1] = roff[r] + counts[r];   // exclusive scan (scan.cuh on the GPU)
     for (uint64_t r = 0; r < n_reads; r++) {
-        if (mode == 0) emit_thread<0>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), nullptr, out, cap, &status, e->tile_len, r);
+        if (mode == 0) emit_thread<0>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), nullptr, out, cap, &status, e->tile_len, r, segs.live);
         else emit_thread<1>(e->dix, packed.data(), offsets, n_reads, sc, counts.data(), roff.data(), nullptr, out, cap, &status, e->tile_len, r);
     }
+    if (mode == 0 && segs.live)
+        for (uint64_t gi = 0; gi < segs.off[n_reads]; gi++)
+            seg_emit_thread(e->dix, packed.data(), offsets, e->tile_len, segs.S, sc, segs.desc.data(), segs.info.data(), counts.data(), roff.data(), nullptr, out, cap, &status, gi);
     *n_records = roff[n_reads];
     if (rec_offsets) memcpy(rec_offsets, roff.data(), (n_reads + 1) * 8);
     return status;

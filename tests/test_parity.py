@@ -88,6 +88,37 @@ def test_encode_records_parity_literal_oracle(small_cases):
         assert (rec == orec).all(), case.k
 
 
+def test_long_read_segment_path(backend):
+    """Reads longer than the tile length are segmented in 512-position segments (seg_spec / seg_join / seg_emit in
+    encode_kernels.cuh): speculative walks per segment joined by the true walk.  Noisy long reads (walks merge at every
+    mismatch), error-free copies of a 30 kbp contig (one record spanning many segments: the speculative walks give up at
+    kSpecExtCap = 4096 and the true walk takes the long step), a long match broken once, read lengths around multiples of 512,
+    short reads in the same batch (the one-item path), capacity errors."""
+    rng = np.random.default_rng(77)
+    g = helpers.random_seq(rng, 30000)
+    case = Case(backend, [g, helpers.random_seq(rng, 700)], 31)
+    reads = helpers.sample_reads(rng, [g], 40, lengths=[511, 512, 513, 1023, 1024, 1025, 1536, 4096, 4097, 4608, 9000, 150, 40],
+                                 error_rates=[0, 0.002, 0.01, 0.05, 0.2], k=31)
+    broken = g[2000:22000].copy()
+    broken[10000] = ord("A") if broken[10000] != ord("A") else ord("C")
+    reads += [g.copy(), g[100:9000].copy(), g[5:4700].copy(), broken, helpers.random_seq(rng, 3000), g[:600].copy()]
+    bases, off = nt.concat_reads(reads)
+    for T in (256, 512, 1000, 0):
+        case.ctx.set_tile_len(T)
+        rec, roff = case.ctx.encode_batch(bases, off)
+        orec, oroff = case.oracle.encode_reads(bases, off, fast=True, threads=8)
+        assert (roff == oroff).all() and (rec == orec).all(), T
+        db, doff = case.ctx.decode_batch(rec)
+        assert (doff == off).all() and (db == bases).all()
+    case.ctx.set_tile_len(256)
+    lrec, _ = case.oracle.encode_reads(bases, off, fast=False, threads=8)
+    assert (lrec == rec).all()
+    with pytest.raises(nt.NtcError) as e:
+        case.ctx.encode_batch(bases, off, cap=len(rec) - 1)
+    assert e.value.code == 3
+    case.ctx.set_tile_len(0)
+
+
 def test_tile_length_invariance(small_cases):
     """Long reads are cut into tiles with a k-1 base warm-up (ms_thread); matching statistics, record
     streams and round trips must not depend on the tile length.  Reads of exactly T, T+1, 2T-1, 2T, ...
