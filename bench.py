@@ -281,7 +281,24 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
     path = "/tmp/ntc_bench_%s_%d_%d.idx" % (cfg["name"], cfg["genome"], cfg["k"])
     index = None
     if rank == 0:
-        index = nt.Index.build([g], cfg["k"])
+        # `ntcomp build` on the GPU (row f4, ntc_index_build_gpu); at N = 1 with a CPU budget the host builder runs beside it
+        # (all host threads) and the two indexes are compared bit for bit
+        bstats = {}
+        nt.Index.build_gpu([g[:100_000]], cfg["k"], device=R.local_rank)     # CUDA context + module load outside the timing
+        tb = time.time()
+        index = nt.Index.build_gpu([g], cfg["k"], device=R.local_rank, stats=bstats)
+        out["index_build"] = {"impl": "ntc_index_build_gpu", "wall_ms": (time.time() - tb) * 1e3, "device_ms": bstats["device_ms"],
+                              "upload_ms": bstats["upload_ms"], "n_sets": index.n_sets, "kmer_occurrences": bstats["occurrences"],
+                              "radix_passes": bstats["radix_passes"], "launches": bstats["launches"]}
+        if world == 1 and args.cpu_budget > 0:
+            tb = time.time()
+            host = nt.Index.build([g], cfg["k"])
+            host_s = time.time() - tb
+            same = host.n_sets == index.n_sets and (host.lcs() == index.lcs()).all() and all((a == b).all() for a, b in zip(host.rows(), index.rows()))
+            if not same:
+                raise SystemExit("bench.py: ntc_index_build_gpu and ntc_index_build disagree")
+            out["index_build"].update({"host_builder_s": host_s, "host_threads": os.cpu_count(), "identical_to_host_builder": True})
+            del host
         if world > 1:
             index.save(path)
     if world > 1:
@@ -651,7 +668,7 @@ def main():
         "e2e": m["e2e"],
         "host_binding": ("NUMA-local CPUs of each GPU (%d CPUs on rank 0)" % len(cpus)) if cpus else "none",
         "gpu_launches": m["gpu_launches"], "roofline": roofline, "cpu_baseline": cpu, "setup_s": m["setup_s"],
-        "index_bytes": m["index_bytes"], "columns": m.get("columns"),
+        "index_bytes": m["index_bytes"], "index_build": m.get("index_build"), "columns": m.get("columns"),
     }
     line.update(extras)
     emit(line)

@@ -151,6 +151,28 @@ struct RankPost {            // distinct rank of every occurrence; first occurre
         if (v.a) uniq[r] = sorted[i];
     }
 };
+// The occurrences are first sorted by their LAST characters only (the most significant radix digits); occurrences whose
+// neighbour agrees on all of those characters are "tied" and get a full-key sort among themselves afterwards.
+struct TieFlag {
+    const uint64_t* packed; const uint32_t* sorted; uint32_t k; uint32_t top_chars; uint64_t m; uint8_t* tie;
+    NTC_HD void operator()(uint64_t i) const {
+        const uint32_t b = sorted[i];
+        bool t = false;
+        if (i > 0) { const uint32_t a = sorted[i - 1]; t = common_suffix(packed, k, a, a, b, b) >= top_chars; }
+        if (!t && i + 1 < m) { const uint32_t c = sorted[i + 1]; t = common_suffix(packed, k, b, b, c, c) >= top_chars; }
+        tie[i] = t ? 1 : 0;
+    }
+};
+struct TiePost {             // slots and values of the tied occurrences, in slot order
+    const uint32_t* sorted; uint32_t* tslot; uint32_t* tval;
+    NTC_HD void operator()(uint64_t i, const Pair64& pre, const Pair64& v) const {
+        if (v.a) { tslot[pre.a] = (uint32_t)i; tval[pre.a] = sorted[i]; }
+    }
+};
+struct TieScatter {          // tied slots, ascending, receive the tied occurrences in full-key order
+    const uint32_t* tslot; const uint32_t* tval; uint32_t* sorted;
+    NTC_HD void operator()(uint64_t j) const { sorted[tslot[j]] = tval[j]; }
+};
 // ---- 3. predecessors and sources -------------------------------------------------------------------------
 // An occurrence at p whose left neighbour p-1 starts a k-mer too: that k-mer's (k-1)-suffix is this k-mer's (k-1)-prefix,
 // so its node is in the predecessor group.  (Several occurrences may write; any of them names the same group.)
@@ -313,15 +335,19 @@ __global__ void __launch_bounds__(256) for_each_kernel(F f, uint64_t n) {
 
 // LSD radix sort of u32 elements, 8-bit digits supplied by a functor (digit(elem, t), t = 0 least significant): the keys
 // (k-mers of up to 255 characters) are never materialised -- a pass gathers 4 characters per element from the 2-bit text,
-// which is a few MB and stays in L2, and moves 4 bytes per element.  Three launches per pass: per-block digit histogram,
-// scan over blocks per digit, stable scatter.
+// which is a few MB and stays in L2, and moves 4 bytes per element.  Three launches per pass: per-block digit histogram
+// (which also leaves every element's digit in a byte array, so the scatter does not gather again), scan over blocks per
+// digit, stable scatter.  What bounds a pass is random 32-byte sectors through L1TEX (one per gathered digit, one per
+// scattered store), the same roofline as ms_kernel: the scatter therefore orders its tile in shared memory first and writes
+// runs of equal digits, ~2 sectors per 16 elements instead of one each (first version: 211 us per pass over 10 M elements,
+// profiles/r2/launches_index_build_gpu.txt).
 constexpr int kSortThreads = 256;
 constexpr int kSortRounds = 16;
 constexpr int kSortTile = kSortThreads * kSortRounds;      // 4096 elements per block, 512 per warp
 
 template <typename D>
 __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const uint32_t* __restrict__ in, uint64_t n, uint32_t t, D digit,
-                                                                  uint32_t* __restrict__ block_hist, uint32_t n_blocks) {
+                                                                  uint8_t* __restrict__ dig, uint32_t* __restrict__ block_hist, uint32_t n_blocks) {
     __shared__ uint32_t h[256];
     h[threadIdx.x] = 0;
     __syncthreads();
@@ -329,7 +355,11 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const uint32_t
 #pragma unroll 4
     for (int r = 0; r < kSortRounds; r++) {
         const uint64_t i = base + (uint64_t)r * kSortThreads + threadIdx.x;
-        if (i < n) atomicAdd(&h[digit(in[i], t)], 1u);
+        if (i < n) {
+            const uint32_t d = digit(in[i], t);
+            dig[i] = (uint8_t)d;
+            atomicAdd(&h[d], 1u);
+        }
     }
     __syncthreads();
     block_hist[(uint64_t)threadIdx.x * n_blocks + blockIdx.x] = h[threadIdx.x];
@@ -370,49 +400,75 @@ static __global__ void __launch_bounds__(kSortThreads) radix_scan_kernel(uint32_
     for (uint32_t i = lo; i < hi; i++) { const uint32_t v = row[i]; row[i] = run; run += v; }
     if (threadIdx.x == 0) totals[blockIdx.x] = total;
 }
-// stable scatter: a warp owns 512 consecutive elements and ranks them 32 at a time (match.any groups equal digits, the
-// lowest lane of a group bumps the warp's counter), then the per-warp counters become absolute output positions
-template <typename D>
-__global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t n,
-                                                                     uint32_t t, D digit, const uint32_t* __restrict__ block_hist,
+// stable scatter: a warp owns 512 consecutive elements and ranks them 32 at a time (lanes with equal digits form a group, the
+// lowest lane of a group bumps the warp's counter -- the groups come from eight ballots); the per-warp counters become positions in the block's tile ordered
+// by digit, the tile is put in that order in shared memory, and thread j writes tile element j: neighbours with the same
+// digit go to neighbouring addresses
+__global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(const uint32_t* __restrict__ in, const uint8_t* __restrict__ dig,
+                                                                     uint32_t* __restrict__ out, uint64_t n, const uint32_t* __restrict__ block_hist,
                                                                      uint32_t n_blocks, const uint32_t* __restrict__ totals) {
     __shared__ uint32_t cnt[kSortThreads / 32][256];
-    __shared__ uint32_t dbase[256];
+    __shared__ uint32_t gbase[256];          // first output position of the block's run of digit d, minus the run's position in the tile
+    __shared__ uint32_t s_val[kSortTile];
+    __shared__ uint8_t s_dig[kSortTile];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int w = 0; w < kSortThreads / 32; w++) cnt[w][threadIdx.x] = 0;
     uint32_t total;
-    const uint32_t before = block_exclusive_u32(totals[threadIdx.x], &total);       // elements with a smaller digit
-    dbase[threadIdx.x] = before + block_hist[(uint64_t)threadIdx.x * n_blocks + blockIdx.x];
-    __syncthreads();
-    const uint64_t wbase = (uint64_t)blockIdx.x * kSortTile + (uint64_t)warp * (kSortRounds * 32);
+    const uint32_t before = block_exclusive_u32(totals[threadIdx.x], &total);       // elements with a smaller digit, all blocks
+    const uint32_t first_out = before + block_hist[(uint64_t)threadIdx.x * n_blocks + blockIdx.x];
+    const uint64_t tbase = (uint64_t)blockIdx.x * kSortTile;
+    const uint64_t wbase = tbase + (uint64_t)warp * (kSortRounds * 32);
     uint32_t val[kSortRounds], key[kSortRounds];                     // key = digit << 16 | rank inside the warp's digit group
     const uint32_t lt = (1u << lane) - 1u;
+    // all 16 loads of the thread first: the ranking rounds below are separated by warp barriers, which the loads may not cross
 #pragma unroll
     for (int r = 0; r < kSortRounds; r++) {
         const uint64_t i = wbase + (uint64_t)r * 32 + lane;
         const bool ok = i < n;
-        const uint32_t v = ok ? in[i] : 0u;
-        const uint32_t d = ok ? digit(v, t) : 0x100u + (uint32_t)lane;       // idle lanes: one group each, never counted
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        val[r] = ok ? in[i] : 0u;
+        key[r] = ok ? (uint32_t)dig[i] : 0xFFFFFFFFu;
+    }
+#pragma unroll
+    for (int r = 0; r < kSortRounds; r++) {
+        const bool ok = key[r] != 0xFFFFFFFFu;
+        const uint32_t d = ok ? key[r] : 0u;
+        // lanes holding the same digit: eight ballots, one per bit (match.any measured the same)
+        uint32_t peers = __ballot_sync(0xffffffffu, ok);
+#pragma unroll
+        for (int bit = 0; bit < 8; bit++) {
+            const uint32_t has = __ballot_sync(0xffffffffu, (d >> bit) & 1u);
+            peers &= ((d >> bit) & 1u) ? has : ~has;
+        }
         uint32_t rank = 0;
         if (ok) rank = cnt[warp][d] + (uint32_t)__popc(peers & lt);
         __syncwarp();
         if (ok && (peers & lt) == 0) cnt[warp][d] += (uint32_t)__popc(peers);
         __syncwarp();
-        val[r] = v;
-        key[r] = ok ? (d << 16 | rank) : 0xFFFFFFFFu;
+        if (ok) key[r] = d << 16 | rank;
     }
     __syncthreads();
     {
-        uint32_t run = dbase[threadIdx.x];
+        uint32_t mine = 0;                                            // elements of digit threadIdx.x in this tile
+#pragma unroll
+        for (int w = 0; w < kSortThreads / 32; w++) mine += cnt[w][threadIdx.x];
+        uint32_t run = block_exclusive_u32(mine, &total);             // the digit's position in the tile
+        gbase[threadIdx.x] = first_out - run;
 #pragma unroll
         for (int w = 0; w < kSortThreads / 32; w++) { const uint32_t c = cnt[w][threadIdx.x]; cnt[w][threadIdx.x] = run; run += c; }
     }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < kSortRounds; r++)
-        if (key[r] != 0xFFFFFFFFu) out[cnt[warp][key[r] >> 16] + (key[r] & 0xFFFFu)] = val[r];
+        if (key[r] != 0xFFFFFFFFu) {
+            const uint32_t p = cnt[warp][key[r] >> 16] + (key[r] & 0xFFFFu);
+            s_val[p] = val[r];
+            s_dig[p] = (uint8_t)(key[r] >> 16);
+        }
+    __syncthreads();
+    const uint32_t in_tile = (uint32_t)tmin<uint64_t>(kSortTile, n - tbase);
+#pragma unroll 4
+    for (uint32_t j = threadIdx.x; j < in_tile; j += kSortThreads) out[gbase[s_dig[j]] + j] = s_val[j];
 }
 #endif  // __CUDACC__
 

@@ -12,8 +12,10 @@
 namespace ntc {
 namespace bld {
 
+constexpr uint32_t kTopDigits = 8;       // radix digits (4 characters each) of the first, partial-key sort
+
 struct BuildStats {
-    uint64_t text_chars = 0, occurrences = 0, distinct = 0, sources = 0, dummies = 0, nodes = 0, sort_passes = 0;
+    uint64_t text_chars = 0, occurrences = 0, distinct = 0, sources = 0, dummies = 0, nodes = 0, sort_passes = 0, tied = 0;
 };
 
 // X provides:
@@ -21,7 +23,8 @@ struct BuildStats {
 //   void zero(void* p, uint64_t bytes)
 //   template <class F> void for_each(uint64_t n, F f)
 //   template <class L, class P> uint64_t scan(L load, uint64_t n, P post)      exclusive sum of load(i).a; returns the total
-//   template <class D> uint32_t* sort(uint32_t* a, uint32_t* b, uint64_t n, uint32_t n_digits, D digit)   returns a or b
+//   template <class D> uint32_t* sort(uint32_t* a, uint32_t* b, uint64_t n, uint32_t t_lo, uint32_t t_hi, D digit)
+//                                                          stable LSD passes over digits t_lo .. t_hi-1; returns a or b
 //   void download(void* host, const void* dev, uint64_t bytes)
 //   bool failed()
 template <class X>
@@ -45,9 +48,33 @@ int32_t sbwt_build(X& x, const uint8_t* d_fwd, uint64_t fwd_len, uint32_t k, boo
     if (x.failed()) return 2;
     const uint64_t m = x.scan(FlagLoad{vstart}, n_chars, CompactPos{occ_a});
 
-    // 2. sort the occurrences by k-mer (colex), distinct k-mers
-    uint32_t* sorted = m > 1 ? x.sort(occ_a, occ_b, m, n_digits, RealDigit{packed, k}) : occ_a;
+    // 2. sort the occurrences by k-mer (colex), distinct k-mers.  k > 32: the 8 most significant digits first (the last
+    //    29..32 characters, which tell almost all k-mers of a genome apart), then a full-key sort of the few occurrences that
+    //    still tie with a neighbour, written back into the slots they came from -- 8 passes over everything instead of ceil(k/4).
+    //    Stable passes both times, so the result is the full LSD sort's, order of equal k-mers included.
     uint8_t* head = x.template alloc<uint8_t>(n_chars);
+    if (x.failed()) return 2;
+    uint32_t* sorted = occ_a;
+    uint64_t n_tied = 0, passes = 0;
+    if (m > 1) {
+        const uint32_t t_lo = n_digits > kTopDigits ? n_digits - kTopDigits : 0;
+        sorted = x.sort(occ_a, occ_b, m, t_lo, n_digits, RealDigit{packed, k});
+        passes += n_digits - t_lo;
+        if (t_lo > 0) {
+            uint32_t* spare = sorted == occ_a ? occ_b : occ_a;       // values of the tied occurrences
+            x.for_each(m, TieFlag{packed, sorted, k, k - 4 * t_lo, m, head});
+            n_tied = x.scan(FlagLoad{head}, m, NoPost());           // count first: the slot list is sized to it
+            if (n_tied) {
+                uint32_t* tslot = x.template alloc<uint32_t>(n_tied);
+                uint32_t* ttmp = x.template alloc<uint32_t>(n_tied);
+                if (x.failed()) return 2;
+                x.scan(FlagLoad{head}, m, TiePost{sorted, tslot, spare});
+                uint32_t* tv = x.sort(spare, ttmp, n_tied, 0, n_digits, RealDigit{packed, k});
+                passes += n_digits;
+                x.for_each(n_tied, TieScatter{tslot, tv, sorted});
+            }
+        }
+    }
     uint32_t* rank_of_pos = x.template alloc<uint32_t>(n_chars);
     uint32_t* uniq = x.template alloc<uint32_t>(m + 1);
     if (x.failed()) return 2;
@@ -76,7 +103,8 @@ int32_t sbwt_build(X& x, const uint8_t* d_fwd, uint64_t fwd_len, uint32_t k, boo
     uint32_t* dn_id = x.template alloc<uint32_t>(m0);
     if (x.failed()) return 2;
     x.for_each(m0, Iota32{did_a});
-    uint32_t* dsorted = m0 > 1 ? x.sort(did_a, did_b, m0, n_digits, DummyDigit{packed, dd}) : did_a;
+    uint32_t* dsorted = m0 > 1 ? x.sort(did_a, did_b, m0, 0, n_digits, DummyDigit{packed, dd}) : did_a;
+    if (m0 > 1) passes += n_digits;
     x.for_each(m0, AdjDummy{packed, dsorted, dd, dhead});
     const uint64_t nd = x.scan(FlagLoad{dhead}, m0, DummyPost{dsorted, dslot, dn_id});
 
@@ -117,7 +145,7 @@ int32_t sbwt_build(X& x, const uint8_t* d_fwd, uint64_t fwd_len, uint32_t k, boo
     if (rc) { delete idx; return rc; }
     if (stats) {
         stats->text_chars = n_chars; stats->occurrences = m; stats->distinct = nr; stats->sources = nsrc;
-        stats->dummies = nd; stats->nodes = n; stats->sort_passes = (uint64_t)n_digits * ((m > 1) + (m0 > 1));
+        stats->dummies = nd; stats->nodes = n; stats->sort_passes = passes; stats->tied = n_tied;
     }
     *out = idx;
     return 0;

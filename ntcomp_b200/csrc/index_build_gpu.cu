@@ -3,6 +3,7 @@
 // functors and the radix sort are build_kernels.cuh; this file is the CUDA executor (launches, scans, buffers) and the
 // C entry point.  Same index, bit for bit, as the host builder (index_build.cpp) -- tests/test_index_build.py.
 // No CPU fallback: without a device the call fails with NTC_ERR_CUDA.
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 #include <string>
@@ -18,24 +19,37 @@ using namespace ntc;
 
 namespace {
 
+// Device memory comes from one arena (a single cudaMalloc sized from the text length, a second chunk only if the dummy nodes
+// outgrow it): the first version made ~25 cudaMalloc / cudaFree calls of 40-100 MB, more wall time than all kernels together.
 struct GpuExec {
     cudaStream_t st = nullptr;
-    std::vector<void*> owned;
+    struct Chunk { char* p; uint64_t cap, used; };
+    std::vector<Chunk> chunks;
+    uint64_t first_chunk = 256ull << 20;
     cudaError_t err = cudaSuccess;
     uint64_t launches = 0;
     Pair64* tile_sums = nullptr; uint64_t tile_cap = 0;
     uint64_t* d_totals = nullptr;
     uint32_t* block_hist = nullptr; uint64_t hist_cap = 0;
     uint32_t* digit_totals = nullptr;
+    uint8_t* dig = nullptr; uint64_t dig_cap = 0;
 
     bool failed() const { return err != cudaSuccess; }
     void note(cudaError_t e) { if (err == cudaSuccess && e != cudaSuccess) err = e; }
     void* raw_alloc(uint64_t bytes) {
         if (failed()) return nullptr;
-        void* p = nullptr;
-        note(cudaMalloc(&p, bytes ? bytes : 1));
-        if (p) owned.push_back(p);
-        return p;
+        bytes = (bytes + 255) & ~255ull;
+        if (chunks.empty() || chunks.back().used + bytes > chunks.back().cap) {
+            const uint64_t cap = std::max<uint64_t>(bytes, chunks.empty() ? first_chunk : 256ull << 20);
+            void* p = nullptr;
+            note(cudaMalloc(&p, cap));
+            if (!p) return nullptr;
+            chunks.push_back(Chunk{(char*)p, cap, 0});
+        }
+        Chunk& c = chunks.back();
+        void* r = c.p + c.used;
+        c.used += bytes;
+        return r;
     }
     template <class T> T* alloc(uint64_t n) { return (T*)raw_alloc((n ? n : 1) * sizeof(T)); }
     void zero(void* p, uint64_t bytes) { if (!failed() && bytes) note(cudaMemsetAsync(p, 0, bytes, st)); }
@@ -56,16 +70,17 @@ struct GpuExec {
         note(cudaStreamSynchronize(st));
         return failed() ? 0 : h[0];
     }
-    template <class D> uint32_t* sort(uint32_t* a, uint32_t* b, uint64_t n, uint32_t n_digits, D digit) {
-        if (failed()) return a;
+    template <class D> uint32_t* sort(uint32_t* a, uint32_t* b, uint64_t n, uint32_t t_lo, uint32_t t_hi, D digit) {
+        if (failed() || n < 2) return a;
         const uint32_t n_blocks = (uint32_t)((n + bld::kSortTile - 1) / bld::kSortTile);
         if ((uint64_t)n_blocks * 256 > hist_cap) { block_hist = (uint32_t*)raw_alloc((uint64_t)n_blocks * 256 * 4); hist_cap = (uint64_t)n_blocks * 256; }
+        if (n > dig_cap) { dig = (uint8_t*)raw_alloc(n); dig_cap = n; }
         if (!digit_totals) digit_totals = (uint32_t*)raw_alloc(256 * 4);
         if (failed()) return a;
-        for (uint32_t t = 0; t < n_digits; t++) {
-            bld::radix_hist_kernel<D><<<n_blocks, bld::kSortThreads, 0, st>>>(a, n, t, digit, block_hist, n_blocks);
+        for (uint32_t t = t_lo; t < t_hi; t++) {
+            bld::radix_hist_kernel<D><<<n_blocks, bld::kSortThreads, 0, st>>>(a, n, t, digit, dig, block_hist, n_blocks);
             bld::radix_scan_kernel<<<256, bld::kSortThreads, 0, st>>>(block_hist, n_blocks, digit_totals);
-            bld::radix_scatter_kernel<D><<<n_blocks, bld::kSortThreads, 0, st>>>(a, b, n, t, digit, block_hist, n_blocks, digit_totals);
+            bld::radix_scatter_kernel<<<n_blocks, bld::kSortThreads, 0, st>>>(a, dig, b, n, block_hist, n_blocks, digit_totals);
             launches += 3;
             uint32_t* s = a; a = b; b = s;
         }
@@ -77,7 +92,7 @@ struct GpuExec {
         note(cudaStreamSynchronize(st));
     }
     ~GpuExec() {
-        for (void* p : owned) cudaFree(p);
+        for (Chunk& c : chunks) cudaFree(c.p);
         if (st) cudaStreamDestroy(st);
     }
 };
@@ -114,6 +129,8 @@ extern "C" int32_t ntc_index_build_gpu(int32_t device, const uint8_t* const* seq
             }
         }
         GpuExec x;
+        // work arrays: ~45 bytes per text character (two strands + padding) when the dummy nodes are few, as in any genome
+        x.first_chunk = ((uint64_t)(add_revcomp ? 2 : 1) * fwd_len + bld::kPad + bld::kTail + 64) * 48 + fwd_len + (32ull << 20);
         NTC_CUDA_TRY(cudaStreamCreateWithFlags(&x.st, cudaStreamNonBlocking));
         uint8_t* d_fwd = x.alloc<uint8_t>(fwd_len);
         if (x.failed()) { set_error(std::string("cudaMalloc: ") + cudaGetErrorString(x.err)); return NTC_ERR_CUDA; }
@@ -142,7 +159,7 @@ extern "C" int32_t ntc_index_build_gpu(int32_t device, const uint8_t* const* seq
             stats[3] = (double)bs.distinct;
             stats[4] = (double)bs.sources;
             stats[5] = (double)bs.dummies;
-            stats[6] = (double)bs.sort_passes;
+            stats[6] = (double)bs.sort_passes;   // radix passes run (over all occurrences, over the tied ones, over the dummy candidates)
             stats[7] = (double)x.launches;
         }
         return NTC_OK;

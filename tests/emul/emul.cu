@@ -307,8 +307,8 @@ struct CpuExec {
         for (uint64_t i = 0; i < n; i++) { const Pair64 v = load(i); post(i, run, v); run = run + v; }
         return run.a;
     }
-    template <class D> uint32_t* sort(uint32_t* a, uint32_t* b, uint64_t n, uint32_t n_digits, D digit) {
-        for (uint32_t t = 0; t < n_digits; t++) {
+    template <class D> uint32_t* sort(uint32_t* a, uint32_t* b, uint64_t n, uint32_t t_lo, uint32_t t_hi, D digit) {
+        for (uint32_t t = t_lo; t < t_hi; t++) {
             uint64_t pos[257] = {0};
             for (uint64_t i = 0; i < n; i++) pos[digit(a[i], t) + 1]++;
             for (int d = 0; d < 256; d++) pos[d + 1] += pos[d];
