@@ -238,6 +238,9 @@ void ntc_free(void* p);
 /* `ntcomp build` front end (src/main.rs:97-134): every fastX record of every file is one input sequence */
 int32_t ntc_index_build_from_files(const char* const* paths, uint64_t n_paths, uint32_t k, int32_t add_revcomp,
                                    int32_t n_threads, ntc_index** out);
+/* the same with the construction on GPU `device` (ntc_index_build_gpu); n_threads parse the files */
+int32_t ntc_index_build_from_files_gpu(int32_t device, const char* const* paths, uint64_t n_paths, uint32_t k, int32_t add_revcomp,
+                                       int32_t n_threads, ntc_index** out);
 
 /* ---------------- device-resident variants (buffers already in HBM, stream-ordered) ----------
  * Same semantics; all pointers are device pointers on ctx's GPU, `stream` is a cudaStream_t (0 =

@@ -68,6 +68,7 @@ SIGNATURES = {
     "ntc_fastx_load": (_i32, [C.c_char_p, _i32, _vp, _vp, _vp, _vp]),
     "ntc_free": (None, [_vp]),
     "ntc_index_build_from_files": (_i32, [_vp, _u64, _u32, _i32, _i32, _pp]),
+    "ntc_index_build_from_files_gpu": (_i32, [_i32, _vp, _u64, _u32, _i32, _i32, _pp]),
     "ntc_ctx_set_tile_len": (_i32, [_vp, _u32]),
     "ntc_ctx_set_copy_directions": (_i32, [_vp, _i32]),
     "ntc_ctx_kernel_times": (_i32, [_vp, _vp, _vp, _i32]),

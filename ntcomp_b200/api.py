@@ -103,11 +103,15 @@ class Index:
         return cls(h)
 
     @classmethod
-    def build_from_files(cls, paths, k, add_revcomp=True, n_threads=0):
-        """`ntcomp build` front end (src/main.rs:97-134): every fastX record of every file is one input sequence"""
+    def build_from_files(cls, paths, k, add_revcomp=True, n_threads=0, gpu=None):
+        """`ntcomp build` front end (src/main.rs:97-134): every fastX record of every file is one input sequence; gpu = a device
+        ordinal runs the construction there (ntc_index_build_gpu)"""
         arr = (C.c_char_p * len(paths))(*[str(p).encode() for p in paths])
         h = C.c_void_p()
-        check(_lib.lib().ntc_index_build_from_files(arr, len(paths), k, int(add_revcomp), n_threads, C.byref(h)))
+        if gpu is None:
+            check(_lib.lib().ntc_index_build_from_files(arr, len(paths), k, int(add_revcomp), n_threads, C.byref(h)))
+        else:
+            check(_lib.lib().ntc_index_build_from_files_gpu(int(gpu), arr, len(paths), k, int(add_revcomp), n_threads, C.byref(h)))
         return cls(h)
 
     @classmethod

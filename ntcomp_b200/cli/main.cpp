@@ -1,6 +1,6 @@
 // ntcomp-b200 -- command-line front end over the C ABI (include/ntcomp_b200.h), mirroring the
 // reference's three subcommands (src/cli.rs:26-93, src/main.rs:91-214):
-//   ntcomp-b200 build  -o <prefix> [-k 31] [-t threads] [-l list] <fastX>...     ->  <prefix>.ntcidx
+//   ntcomp-b200 build  -o <prefix> [-k 31] [-t threads] [-l list] [--gpu [--device N]] <fastX>...     ->  <prefix>.ntcidx
 //   ntcomp-b200 encode -i <prefix> <reads.fastX[.gz]>   > encoded.dat
 //   ntcomp-b200 decode -i <prefix> <encoded.dat>        > decoded.fasta
 // encoded.dat is the reference's format.  The index file is this library's own flat
@@ -19,7 +19,7 @@
 
 static int usage() {
     fprintf(stderr,
-            "usage: ntcomp-b200 build  -o <prefix> [-k 31] [-t threads] [-l input-list] <fastX>...\n"
+            "usage: ntcomp-b200 build  -o <prefix> [-k 31] [-t threads] [-l input-list] [--gpu [--device N]] <fastX>...\n"
             "       ntcomp-b200 encode -i <prefix> [-t threads] [--device N] [-o out] <reads.fastX>\n"
             "       ntcomp-b200 decode -i <prefix> [-t threads] [--device N] [-o out] <encoded.dat>\n");
     return 2;
@@ -37,6 +37,7 @@ int main(int argc, char** argv) {
     std::vector<std::string> inputs;
     uint32_t k = 31;                    // src/cli.rs:43
     int threads = 0, device = 0;
+    bool gpu_build = false;
     for (int i = 2; i < argc; i++) {
         std::string a = argv[i];
         auto val = [&]() -> const char* { if (i + 1 >= argc) { usage(); exit(2); } return argv[++i]; };
@@ -46,6 +47,7 @@ int main(int argc, char** argv) {
         else if (a == "-t" || a == "--threads") threads = atoi(val());
         else if (a == "-l" || a == "--input-list") list = val();
         else if (a == "--device") device = atoi(val());
+        else if (a == "--gpu") gpu_build = true;
         else if (a == "-p" || a == "--prefix-precalc" || a == "-m" || a == "--mem-gb" || a == "--temp-dir") (void)val();  // kbo build knobs: accepted, unused
         else if (a == "-d" || a == "--dedup-batches" || a == "--verbose") {}
         else if (a == "-h" || a == "--help") return usage();
@@ -71,7 +73,8 @@ int main(int argc, char** argv) {
         for (auto& s : inputs) paths.push_back(s.c_str());
         ntc_index* idx = nullptr;
         fprintf(stderr, "Building SBWT index from %zu files...\n", inputs.size());
-        int32_t rc = ntc_index_build_from_files(paths.data(), paths.size(), k, /*add_revcomp=*/1, threads, &idx);   // src/main.rs:118
+        int32_t rc = gpu_build ? ntc_index_build_from_files_gpu(device, paths.data(), paths.size(), k, /*add_revcomp=*/1, threads, &idx)
+                               : ntc_index_build_from_files(paths.data(), paths.size(), k, /*add_revcomp=*/1, threads, &idx);   // src/main.rs:118
         if (rc) return fail("build", rc);
         fprintf(stderr, "Serializing index (k = %u, %llu nodes) to %s ...\n", ntc_index_k(idx), (unsigned long long)ntc_index_n_sets(idx),
                 idx_path.c_str());

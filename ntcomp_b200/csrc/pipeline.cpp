@@ -951,8 +951,20 @@ void ntc_free(void* p) { free(p); }
 
 // `ntcomp build` front end (src/main.rs:97-134): every record of every fastX file is one input sequence of
 // kbo::build (add_revcomp = true there).  Construction itself is ntc_index_build (host, offline).
+static int32_t build_from_files(const char* const* paths, uint64_t n_paths, uint32_t k, int32_t add_revcomp, int32_t n_threads, int32_t device,
+                                ntc_index** out);
 int32_t ntc_index_build_from_files(const char* const* paths, uint64_t n_paths, uint32_t k, int32_t add_revcomp, int32_t n_threads,
                                    ntc_index** out) {
+    return build_from_files(paths, n_paths, k, add_revcomp, n_threads, -1, out);
+}
+// the same with the construction on GPU `device` (ntc_index_build_gpu): what `ntcomp-b200 build --gpu` runs
+int32_t ntc_index_build_from_files_gpu(int32_t device, const char* const* paths, uint64_t n_paths, uint32_t k, int32_t add_revcomp,
+                                       int32_t n_threads, ntc_index** out) {
+    if (device < 0) { set_error("device ordinal out of range"); return NTC_ERR_INVALID_ARG; }
+    return build_from_files(paths, n_paths, k, add_revcomp, n_threads, device, out);
+}
+static int32_t build_from_files(const char* const* paths, uint64_t n_paths, uint32_t k, int32_t add_revcomp, int32_t n_threads, int32_t device,
+                                ntc_index** out) {
     if (!out || (n_paths && !paths)) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
     std::vector<uint8_t*> fb(n_paths, nullptr);
     std::vector<uint64_t*> fo(n_paths, nullptr);
@@ -964,7 +976,8 @@ int32_t ntc_index_build_from_files(const char* const* paths, uint64_t n_paths, u
         std::vector<uint64_t> lens;
         for (uint64_t f = 0; f < n_paths; f++)
             for (uint64_t i = 0; i < fn[f]; i++) { ptrs.push_back(fb[f] + fo[f][i]); lens.push_back(fo[f][i + 1] - fo[f][i]); }
-        rc = ntc_index_build(ptrs.data(), lens.data(), ptrs.size(), k, add_revcomp, n_threads, out);
+        rc = device >= 0 ? ntc_index_build_gpu(device, ptrs.data(), lens.data(), ptrs.size(), k, add_revcomp, out, nullptr)
+                         : ntc_index_build(ptrs.data(), lens.data(), ptrs.size(), k, add_revcomp, n_threads, out);
     }
     for (uint64_t f = 0; f < n_paths; f++) { free(fb[f]); free(fo[f]); }
     return rc;

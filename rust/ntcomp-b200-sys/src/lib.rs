@@ -131,6 +131,8 @@ extern "C" {
     pub fn ntc_free(p: *mut c_void);
     pub fn ntc_index_build_from_files(paths: *const *const c_char, n_paths: u64, k: u32, add_revcomp: i32, n_threads: i32,
                                       out: *mut *mut ntc_index) -> i32;
+    pub fn ntc_index_build_from_files_gpu(device: i32, paths: *const *const c_char, n_paths: u64, k: u32, add_revcomp: i32, n_threads: i32,
+                                          out: *mut *mut ntc_index) -> i32;
 
     // ---- device-resident variants (device pointers, cudaStream_t) ----
     pub fn ntc_encode_device(ctx: *mut ntc_ctx, d_bases: *const u8, d_offsets: *const u64, n_reads: u64, n_bases: u64,

@@ -144,6 +144,11 @@ def test_cli_round_trip_and_block_parity(tmp_path, genome_and_reads, monkeypatch
     _write_fastq(fq, reads, opener=lambda p, m: gzip.open(p, m, compresslevel=1))
     prefix = str(tmp_path / "idx")
     subprocess.run([CLI, "build", "-k", "31", "-o", prefix, str(fa)], check=True, capture_output=True)
+    # `build --gpu` (ntc_index_build_gpu behind the same front end) writes the same file, byte for byte
+    subprocess.run([CLI, "build", "--gpu", "-k", "31", "-o", prefix + "_gpu", str(fa)], check=True, capture_output=True)
+    with open(prefix + ".ntcidx", "rb") as fh, open(prefix + "_gpu.ntcidx", "rb") as fg:
+        assert fh.read() == fg.read()
+    assert (nt.Index.build_from_files([fa], 31, gpu=0).lcs() == nt.Index.load(prefix + ".ntcidx").lcs()).all()
     enc, dec = tmp_path / "encoded.dat", tmp_path / "decoded.fasta"
     with open(enc, "wb") as f:
         r = subprocess.run([CLI, "encode", "-i", prefix, str(fq)], stdout=f, stderr=subprocess.PIPE)
