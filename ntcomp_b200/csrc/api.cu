@@ -138,7 +138,8 @@ int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint
                                                                                 tile_off + n_reads, T, scratch, counts, status, keep_records ? 1 : 0,
                                                                                 stage_words);
         };
-        if (twelve) launch(ms_kernel<12>); else launch(ms_kernel<10>);
+        if (ctx->dix.rank_nodes == 64) { if (twelve) launch(ms_kernel<12, 64>); else launch(ms_kernel<10, 64>); }
+        else { if (twelve) launch(ms_kernel<12, 32>); else launch(ms_kernel<10, 32>); }
     }
     lane.seg_len = 0;
     if (counts && n_bases > (uint64_t)T) {                            // no read can exceed T otherwise
@@ -367,6 +368,7 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
     std::vector<ntc_lcsx_t> lcs;
     std::vector<uint64_t> jump;
     uint32_t c_start[4] = {0, 0, 0, 0};
+    const uint32_t rank_nodes = rank_nodes_for(idx->n);
     const bool use_pfx = idx->k >= 10 && !getenv("NTC_NO_PREFIX_TABLE");   // a tile's warm-up (k-1 bases) must cover the 8 bases
     double t_rank = 0, t_lcs = 0, t_jump = 0;
     std::exception_ptr build_err;
@@ -375,8 +377,8 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
         try {
             if (uses & NTC_USE_ENCODE) lcs_thread = std::thread([&]() { build_lcs_words(*idx, &lcs); t_lcs = since(); });   // serial stack pass
             if (uses & NTC_USE_ENCODE) {
-                build_rank_blocks(*idx, &rank, std::max(1, threads - 1));
-                if (use_pfx) build_prefix_table(rank, idx->n, &pfx, c_start);
+                build_rank_blocks(*idx, &rank, std::max(1, threads - 1), rank_nodes);
+                if (use_pfx) build_prefix_table(rank, idx->n, &pfx, c_start, rank_nodes);
                 t_rank = since();
             }
             if (uses & NTC_USE_DECODE) { build_jump_table(*idx, &jump, std::max(1, threads - 1)); t_jump = since(); }
@@ -446,6 +448,7 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
     ctx->dix.pfx = (const uint4*)ctx->d_pfx;
     ctx->dix.n = (uint32_t)idx->n;
     ctx->dix.k = idx->k;
+    ctx->dix.rank_nodes = rank_nodes;
     spec_window(idx->n, &ctx->dix.spec_lo, &ctx->dix.spec_span);
     {
         // L2 cache-hint descriptors, made once on the device and handed to every kernel as (uniform) parameters

@@ -36,8 +36,8 @@ enum : uint32_t {
 // Index as the kernels see it.  All arrays are L2-resident at the BASELINE configs
 // (5 Mbp / k=91: rank 13.4 MB, LCS 10 MB, jump 80 MB).
 struct DevIndex {
-    const uint4* rank;     // [(n/32+1) * 4] entries, c = entry index & 3: {C[c] + ones of row c before the block,
-                           //   row bits, Q bits, 0}
+    const uint4* rank;     // rank blocks, 64 bytes each (layout.h): rank_nodes == 32: [(n/32+1) * 4] entries, c = entry index & 3:
+                           //   {C[c] + ones of row c before the block, row bits, Q bits, 0}; rank_nodes == 64: two sectors per block
     const ntc_lcsx_t* lcsx;  // [n + 1] LCS side array (layout.h)
     const uint64_t* jump;  // [n] pred^16 | chars16 << 32
     const uint4* pfx;      // [4^8 * 2] prefix table (host_index.h), null when k < 10
@@ -47,6 +47,7 @@ struct DevIndex {
     uint32_t spec_lo, spec_span;  // ms_kernel speculates LCS loads while spec_lo <= d < spec_lo + spec_span
     uint64_t pol_keep, pol_stream;  // L2 cache-hint descriptors (createpolicy, made once by policy_kernel at context
                                     // creation): kernel parameters are uniform, so a hinted load needs no R2UR pair
+    uint32_t rank_nodes;   // 32 or 64: layout of `rank` (layout.h); read by the host side only (kernels are instantiated per layout)
 };
 
 // scratch entry written by the matching-statistics pass, one per base:
@@ -65,14 +66,6 @@ NTC_HD uint32_t entry_urun(uint64_t e) { return (uint32_t)(e >> 40); }
 #else
 #define NTC_POPC(x) __builtin_popcount(x)
 #endif
-NTC_HD uint32_t rank_block(uint32_t v) { return v >> 5; }
-NTC_HD uint32_t rank_offset(uint32_t v, uint32_t) { return v & 31u; }
-NTC_HD uint32_t entry_rank(const uint4& e, uint32_t off) {            // off in [0, 32)
-    return e.x + (uint32_t)NTC_POPC(e.y & ((1u << off) - 1u));
-}
-NTC_HD uint32_t entry_bit(const uint4& e, uint32_t off) { return (e.y >> off) & 1u; }
-NTC_HD uint32_t entry_qbit(const uint4& e, uint32_t off) { return (e.z >> off) & 1u; }
-
 // 2-bit base at chunk-relative position p of a packed stream (32 bases per u64, LSB first)
 NTC_HD uint32_t packed_base(const uint64_t* __restrict__ packed, uint64_t p) {
     return (uint32_t)(NTC_LDG(packed + (p >> 5)) >> ((p & 31) * 2)) & 3u;
@@ -167,14 +160,75 @@ NTC_HD uint2 ld8x2_keep_if(const uint4* ptr, uint64_t pol, bool on) {   // first
     return on ? uint2{ptr->x, ptr->y} : uint2{0u, 0u};
 #endif
 }
-// the part of a rank entry that a rank needs (count + row bits), loaded only when `on`; and the rank of offset `off`
-// in that entry when `on`, else in `va`
-typedef uint2 RankPart;
-NTC_HD RankPart ld_rank_part_if(const uint4* ptr, uint64_t pol, bool on) { return ld8x2_keep_if(ptr, pol, on); }
-NTC_HD uint32_t entry_rank_sel(const uint4& va, const RankPart& vb, bool on, uint32_t off) {
-    const uint32_t cnt = on ? vb.x : va.x, bits = on ? vb.y : va.y;
-    return cnt + (uint32_t)NTC_POPC(bits & ((1u << off) - 1u));
+NTC_HD uint64_t ld8_keep_if(const uint64_t* ptr, uint64_t pol, bool on) {
+#if defined(__CUDA_ARCH__)
+    uint64_t v;
+    asm volatile(
+        "{\n .reg .pred p;\n setp.ne.u32 p, %3, 0;\n mov.u64 %0, 0;\n"
+        " @p ld.global.nc.L2::cache_hint.u64 %0, [%1], %2;\n}"
+        : "=&l"(v) : "l"(ptr), "l"(pol), "r"((uint32_t)on));
+    return v;
+#else
+    (void)pol;
+    return on ? *ptr : 0ull;
+#endif
 }
+// Rank blocks (layout.h).  RankL<NODES>: block / offset of node v; ld_ent = everything a step reads of (block, base c) -- count, row
+// bits, Q bits -- in ONE load of one sector; ld_part_if = the part a rank needs (count + row bits), loaded only when `on`;
+// rank = ones of the entry's row in block-relative positions [0, off) + the count; rank_sel = the same in `vb` when `on`, else in `va`.
+template <int NODES> struct RankL;
+template <> struct RankL<32> {
+    typedef uint4 Ent;                                                // {count, row bits, Q bits, spare}
+    typedef uint2 Part;
+    static NTC_HD uint32_t block(uint32_t v) { return v >> 5; }
+    static NTC_HD uint32_t offset(uint32_t v) { return v & 31u; }
+    static NTC_HD Ent ld_ent(const uint4* rank, uint32_t blk, uint32_t c, uint64_t pol) { return ld16_keep(rank + (blk * 4u + c), pol); }   // 32-bit entry index: n / 8 < 2^29
+    static NTC_HD Part ld_part_if(const uint4* rank, uint32_t blk, uint32_t c, uint64_t pol, bool on) { return ld8x2_keep_if(rank + (blk * 4u + c), pol, on); }
+    static NTC_HD uint32_t rank(const Ent& e, uint32_t off) { return e.x + (uint32_t)NTC_POPC(e.y & ((1u << off) - 1u)); }   // off in [0, 32)
+    static NTC_HD uint32_t bit(const Ent& e, uint32_t off) { return (e.y >> off) & 1u; }
+    static NTC_HD uint32_t qbit(const Ent& e, uint32_t off) { return (e.z >> off) & 1u; }
+    static NTC_HD uint32_t rank_sel(const Ent& va, const Part& vb, bool on, uint32_t off) {
+        const uint32_t cnt = on ? vb.x : va.x, bits = on ? vb.y : va.y;
+        return cnt + (uint32_t)NTC_POPC(bits & ((1u << off) - 1u));
+    }
+};
+template <> struct RankL<64> {
+    struct Ent { uint32_t cnt; uint64_t bits, q; };
+    struct Part { uint32_t cnt; uint64_t bits; };
+    static NTC_HD uint32_t block(uint32_t v) { return v >> 6; }
+    static NTC_HD uint32_t offset(uint32_t v) { return v & 63u; }
+    static NTC_HD Ent ld_ent(const uint4* rank, uint32_t blk, uint32_t c, uint64_t pol) {
+        const uint4* p = rank + (blk * 4u + (c >> 1) * 2u);          // the sector of bases {A,C} or {G,T}
+        uint64_t w0, w1, w2, w3;
+#if defined(__CUDA_ARCH__)
+        asm volatile("ld.global.nc.L2::cache_hint.v4.u64 {%0,%1,%2,%3}, [%4], %5;" : "=l"(w0), "=l"(w1), "=l"(w2), "=l"(w3) : "l"(p), "l"(pol));
+#else
+        (void)pol;
+        const uint64_t* q = (const uint64_t*)p;
+        w0 = q[0]; w1 = q[1]; w2 = q[2]; w3 = q[3];
+#endif
+        Ent e;
+        e.cnt = (c & 1u) ? (uint32_t)(w0 >> 32) : (uint32_t)w0;
+        e.bits = (c & 1u) ? w2 : w1;
+        e.q = w3;
+        return e;
+    }
+    static NTC_HD Part ld_part_if(const uint4* rank, uint32_t blk, uint32_t c, uint64_t pol, bool on) {
+        const uint4* p = rank + (blk * 4u + (c >> 1) * 2u);
+        Part r;
+        r.cnt = ld4_keep_if((const uint32_t*)p + (c & 1u), pol, on);
+        r.bits = ld8_keep_if((const uint64_t*)p + 1u + (c & 1u), pol, on);
+        return r;
+    }
+    static NTC_HD uint32_t rank(const Ent& e, uint32_t off) { return e.cnt + (uint32_t)NTC_POPCLL(e.bits & ((1ull << off) - 1ull)); }   // off in [0, 64)
+    static NTC_HD uint32_t bit(const Ent& e, uint32_t off) { return (uint32_t)(e.bits >> off) & 1u; }
+    static NTC_HD uint32_t qbit(const Ent& e, uint32_t off) { return (uint32_t)(e.q >> off) & 1u; }
+    static NTC_HD uint32_t rank_sel(const Ent& va, const Part& vb, bool on, uint32_t off) {
+        const uint32_t cnt = on ? vb.cnt : va.cnt;
+        const uint64_t bits = on ? vb.bits : va.bits;
+        return cnt + (uint32_t)NTC_POPCLL(bits & ((1ull << off) - 1ull));
+    }
+};
 NTC_HD uint64_t ld8_keep(const uint64_t* ptr, uint64_t pol) {
 #if defined(__CUDA_ARCH__)
     uint64_t v;

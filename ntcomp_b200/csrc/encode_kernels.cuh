@@ -213,6 +213,7 @@ struct TileDescPost {
 
 // `stage` = 4 x blockDim u64 staging slots of this thread's block (shared memory on the GPU),
 // indexed [slot * stride + lane]
+template <int NODES>
 NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t* __restrict__ offsets, uint64_t item_desc, uint32_t T,
                       uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts, uint32_t* __restrict__ status,
                       uint64_t* stage, uint32_t stride, bool keep_records) {
@@ -272,8 +273,9 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         // a singleton interval [s, s+1) -- the common case once the match is longer than ~log4(n) -- needs one
         // entry only, also when s is the last node of its block: rank(s+1) = rank(s) + row bit of s
         const bool single = e == s + 1u;
-        const uint32_t bs = rank_block(s), os = rank_offset(s, bs);
-        const uint32_t be = rank_block(e), oe = rank_offset(e, be);
+        typedef RankL<NODES> RL;
+        const uint32_t bs = RL::block(s), os = RL::offset(s);
+        const uint32_t be = RL::block(e), oe = RL::offset(e);
         const bool other = !single && be != bs;                       // the interval end lies in another block
         // LCS words of the interval ends: loaded speculatively only while d is in the window where
         // extensions of chance matches fail (around log4(n_sets), set by the host), on demand otherwise
@@ -281,8 +283,8 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         // all load sectors on it)
         const bool spec = force || (d - ix.spec_lo < ix.spec_span);   // unsigned: spec_lo <= d < spec_lo + spec_span
         // all loads of the iteration issue back to back, before any of their results is used
-        const uint4 va = ld16_keep(ix.rank + (bs * 4u + c), keep);             // 32-bit entry index: n / 8 < 2^29
-        const RankPart vb = ld_rank_part_if(ix.rank + (be * 4u + c), keep, other);
+        const typename RL::Ent va = RL::ld_ent(ix.rank, bs, c, keep);
+        const typename RL::Part vb = RL::ld_part_if(ix.rank, be, c, keep, other);
 #if NTC_LCS16
         const uint32_t xs = ld2_keep_if(ix.lcsx + s, keep, spec);     // node s: LCS[s], distance to the previous smaller value
         const uint32_t xe = ld2_keep_if(ix.lcsx + e, keep, spec);     // node e (<= n: the array has n + 1 entries): LCS[e], distance to the next smaller
@@ -291,13 +293,13 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         uint32_t xe = ld4_keep_if(ix.lcsx + (e - 1u), keep, spec && !single);
         xe = single ? xs : xe;
 #endif
-        const uint32_t s2 = entry_rank(va, os);
-        const uint32_t e2 = single ? s2 + entry_bit(va, os) : entry_rank_sel(va, vb, other, oe);
+        const uint32_t s2 = RL::rank(va, os);
+        const uint32_t e2 = single ? s2 + RL::bit(va, os) : RL::rank_sel(va, vb, other, oe);
         if (fresh) {
             // the block of the interval start (unchanged since the last successful step) also holds its Q bit:
             // finish entry j-1, whose (start, d) are still in s and d
             if (j > p0) {
-                urun = (d == k && entry_qbit(va, os)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
+                urun = (d == k && RL::qbit(va, os)) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
                 const uint32_t slot = (j - 1u) & 3u;
                 stage[slot * stride] = make_entry(s, d, urun);
                 if (slot == 3u) {                                     // one full 32-byte sector
@@ -358,9 +360,8 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         for (uint32_t q = first_unflushed; q + 1 < p1; q++) sc[q] = stage[(q & 3u) * stride];
         uint32_t last_run = 0;                                         // urun of a read's last position is never read (ext looks at i-2)
         if (p1 < len) {                                                // ... but the next tile's runs may continue this one
-            const uint32_t bq = rank_block(s);
-            const uint4 vq = ld16_keep(ix.rank + (size_t)bq * 4, keep);
-            last_run = (d == k && entry_qbit(vq, rank_offset(s, bq))) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
+            const typename RankL<NODES>::Ent vq = RankL<NODES>::ld_ent(ix.rank, RankL<NODES>::block(s), 0u, keep);
+            last_run = (d == k && RankL<NODES>::qbit(vq, RankL<NODES>::offset(s))) ? tmin(urun + 1u, 0xFFFFFFu) : 0u;
         }
         sc[p1 - 1] = make_entry(s, d, last_run);
     }
@@ -560,7 +561,7 @@ constexpr uint32_t kMsStageWordsMax = 1024;  // at most 8 KB of packed reads per
 // 9.8 KB per block twelve blocks fit one SM beside a 124 KB L1 -- the kernel needs ~100 KB of L1 (profiles/r2/ab_ms_scratch_on_chip.txt)
 // -- and twelve blocks of 40 registers measure 11.49 against 11.69 ms for ten of 48 (profiles/r2/ab_ms_blocks.txt).  Batches of longer
 // reads take the ten-block instantiation: twelve blocks with an 8 KB stage each would push the L1 below that size (12.55 ms, r1).
-template <int MIN_BLOCKS>
+template <int MIN_BLOCKS, int NODES>
 __global__ void __launch_bounds__(kMsThreads, MIN_BLOCKS) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
                                                         const uint64_t* __restrict__ offsets, const uint64_t* __restrict__ desc,
                                                         const uint64_t* __restrict__ n_items, uint32_t T,
@@ -595,7 +596,7 @@ __global__ void __launch_bounds__(kMsThreads, MIN_BLOCKS) ms_kernel(DevIndex ix,
     const uint64_t* pk = staged ? (s_packed - w_lo) : packed;                // generic pointer: shared or global
     const uint64_t i = i0 + threadIdx.x;
     if (i >= i1) return;
-    ms_thread(ix, pk, offsets, desc[i], T, scratch, counts, status, s_stage + threadIdx.x, kMsThreads, keep_records != 0);
+    ms_thread<NODES>(ix, pk, offsets, desc[i], T, scratch, counts, status, s_stage + threadIdx.x, kMsThreads, keep_records != 0);
 }
 
 __global__ void __launch_bounds__(256) count_kernel(DevIndex ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offsets,

@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cstdio>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -56,12 +57,23 @@ int32_t finalize_index(ntc_index* idx) {
     return NTC_OK;
 }
 
-void build_prefix_table(const std::vector<uint32_t>& rb, uint64_t n, std::vector<uint32_t>* out, uint32_t c_start[4]) {
+uint32_t rank_nodes_for(uint64_t n_sets) {
+    if (const char* env = getenv("NTC_RANK_NODES")) { const int v = atoi(env); if (v == 32 || v == 64) return (uint32_t)v; }
+    return n_sets >= NTC_RANK64_MIN_NODES ? 64u : 32u;
+}
+
+void build_prefix_table(const std::vector<uint32_t>& rb, uint64_t n, std::vector<uint32_t>* out, uint32_t c_start[4], uint32_t kBlockNodes) {
     // the same arithmetic as the device's extend_right: entry count + popcount of the row bits below the offset
     auto rank = [&](uint32_t c, uint64_t i) -> uint32_t {
-        const uint32_t* e = rb.data() + (i / kBlockNodes) * 16 + c * 4;
         const uint32_t off = (uint32_t)(i % kBlockNodes);
-        return e[0] + (uint32_t)__builtin_popcount(e[1] & ((1u << off) - 1u));
+        if (kBlockNodes == 32) {
+            const uint32_t* e = rb.data() + (i / kBlockNodes) * 16 + c * 4;
+            return e[0] + (uint32_t)__builtin_popcount(e[1] & ((1u << off) - 1u));
+        }
+        const uint32_t* e = rb.data() + (i / kBlockNodes) * 16 + (c >> 1) * 8;      // the sector of bases {A,C} or {G,T}
+        uint64_t bits;
+        memcpy(&bits, e + 2 + 2 * (c & 1), 8);
+        return e[c & 1] + (uint32_t)__builtin_popcountll(bits & ((1ull << off) - 1ull));
     };
     const uint32_t n_entries = 1u << (2 * kPrefixBases);
     out->assign((size_t)n_entries * 8, 0);
@@ -82,7 +94,7 @@ void build_prefix_table(const std::vector<uint32_t>& rb, uint64_t n, std::vector
     }
 }
 
-void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out, int n_threads) {
+void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out, int n_threads, uint32_t kBlockNodes) {
     const uint64_t n = idx.n;
     const uint32_t k = idx.k;
     const uint64_t n_blocks = n / kBlockNodes + 1;  // position n (interval end) must be addressable
@@ -116,11 +128,19 @@ void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out, int n_t
             for (int c = 0; c < 4; c++) {
                 uint64_t bits = 0;
                 for (uint32_t i = 0; i < kBlockNodes && base + i < n; i++) bits |= (uint64_t)row_bit(idx, c, base + i) << i;
-                uint32_t* e = out->data() + b * 16 + c * 4;
-                e[0] = (uint32_t)idx.C[c] + rank(c, base);  // C[c] folded in: extend_right is entry count + popcount
-                e[1] = (uint32_t)bits;
-                e[2] = (uint32_t)q;
-                e[3] = 0;
+                const uint32_t cnt = (uint32_t)idx.C[c] + rank(c, base);  // C[c] folded in: extend_right is entry count + popcount
+                if (kBlockNodes == 32) {
+                    uint32_t* e = out->data() + b * 16 + c * 4;
+                    e[0] = cnt;
+                    e[1] = (uint32_t)bits;
+                    e[2] = (uint32_t)q;
+                    e[3] = 0;
+                } else {
+                    uint32_t* e = out->data() + b * 16 + (c >> 1) * 8;    // {count, count, bits, bits, Q} per pair of bases (layout.h)
+                    e[c & 1] = cnt;
+                    memcpy(e + 2 + 2 * (c & 1), &bits, 8);
+                    memcpy(e + 6, &q, 8);
+                }
             }
         }
     });

@@ -19,7 +19,8 @@ namespace ntc {
 constexpr uint32_t kMinK = 12;   // len <= 11 literals index kmer[k-len..k) (src/encode.rs:152): needs k >= 11;
                                  // the decode jump table packs 16 bases, the bucketed builder uses 8
 constexpr uint32_t kMaxK = 255;  // d and LCS are stored in one byte
-constexpr uint32_t kBlockNodes = NTC_RANK_NODES;  // nodes per 64-byte rank block (layout.h)
+// nodes per 64-byte rank block (layout.h): 64 for indexes of NTC_RANK64_MIN_NODES nodes or more, else 32; NTC_RANK_NODES=32|64 overrides
+uint32_t rank_nodes_for(uint64_t n_sets);
 
 void set_error(const std::string& msg);
 
@@ -31,11 +32,11 @@ int32_t build_index(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n
 
 // ---- derived device layouts (built on the host, uploaded by ntc_ctx_create) ----
 
-// Rank blocks: 64 bytes per kBlockNodes nodes = 4 x 16-byte entries (A,C,G,T), entry =
-//   u32 C[c] + ones of this row before the block | 32 row bits | 32 Q bits | spare word
+// Rank blocks, 64 bytes each.  nodes == 32: 4 x 16-byte entries (A,C,G,T), entry =
+//   u32 C[c] + ones of this row before the block | 32 row bits | 32 Q bits | spare word;  nodes == 64: two sectors (layout.h)
 // Q[v] = node v is alone in its (k-1)-suffix group  <=>  LCS[v] < k-1 and (v+1 == n or LCS[v+1] < k-1).
 // One rank probe = one aligned 16-byte load = one 32-byte L2 sector.
-void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out /* 16 u32 per block */, int n_threads);
+void build_rank_blocks(const ntc_index& idx, std::vector<uint32_t>* out /* 16 u32 per block */, int n_threads, uint32_t nodes = 32);
 
 // LCS words for O(1) contract_left: u32 word i = LCS[i] | min(255, i - PSV(i)) << 8 | LCS[i+1] << 16 |
 // min(255, NSV(i+1) - (i+1)) << 24, PSV / NSV = nearest position left / right with a strictly smaller
@@ -49,7 +50,7 @@ void spec_window(uint64_t n_sets, uint32_t* lo, uint32_t* span);
 // zero when some prefix of x is absent from the index (the kernel then takes the ordinary path).
 // c_start[c] = interval start after the single base c.
 constexpr uint32_t kPrefixBases = 8;
-void build_prefix_table(const std::vector<uint32_t>& rank_blocks, uint64_t n, std::vector<uint32_t>* out, uint32_t c_start[4]);
+void build_prefix_table(const std::vector<uint32_t>& rank_blocks, uint64_t n, std::vector<uint32_t>* out, uint32_t c_start[4], uint32_t nodes = 32);
 
 // Decode jump table: one u64 per node = pred^16(v) (low 32 bits) | last 16 bases of node v's k-mer
 // (high 32 bits, base at string position k-16+i in bits 2i..2i+1).  Root and '$' positions code 0.

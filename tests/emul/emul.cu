@@ -30,7 +30,9 @@ extern "C" {
 
 void* emul_index_create(const ntc_index* idx) {
     EmulIndex* e = new EmulIndex();
-    build_rank_blocks(*idx, &e->rank, 2);
+    const uint32_t nodes = rank_nodes_for(idx->n);                   // as ntc_ctx_create; NTC_RANK_NODES=64 runs the 64-node layout on small cases
+    build_rank_blocks(*idx, &e->rank, 2, nodes);
+    e->dix.rank_nodes = nodes;
     build_jump_table(*idx, &e->jump, 2);
     build_lcs_words(*idx, &e->lcs);
     e->dix.rank = (const uint4*)e->rank.data();
@@ -38,7 +40,7 @@ void* emul_index_create(const ntc_index* idx) {
     e->dix.jump = e->jump.data();
     e->dix.pfx = nullptr;
     if (idx->k >= 10) {                                              // as ntc_ctx_create
-        build_prefix_table(e->rank, idx->n, &e->pfx, e->dix.c_start);
+        build_prefix_table(e->rank, idx->n, &e->pfx, e->dix.c_start, nodes);
         e->dix.pfx = (const uint4*)e->pfx.data();
     }
     e->dix.n = (uint32_t)idx->n;
@@ -77,7 +79,10 @@ static void run_ms(const EmulIndex* e, const uint8_t* bases, const uint64_t* off
     for (uint64_t r = 0; r < n_reads; r++) tpost(r, Pair64{tile_off[r], 0}, tl(r));
     uint64_t stage[4];
     // items in reverse order: tiles of a read must not depend on the order in which they run
-    for (uint64_t i = tile_off[n_reads]; i-- > 0;) ms_thread(e->dix, packed->data(), offsets, desc[i], T, sc, counts, status, stage, 1, keep_records);
+    for (uint64_t i = tile_off[n_reads]; i-- > 0;) {
+        if (e->dix.rank_nodes == 64) ms_thread<64>(e->dix, packed->data(), offsets, desc[i], T, sc, counts, status, stage, 1, keep_records);
+        else ms_thread<32>(e->dix, packed->data(), offsets, desc[i], T, sc, counts, status, stage, 1, keep_records);
+    }
     if (!counts) return;
     if (keep_records && segs && nb > T && !getenv("NTC_SEG_SERIAL")) {
         const char* fs = getenv("NTC_SEG_LEN");

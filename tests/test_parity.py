@@ -88,6 +88,31 @@ def test_encode_records_parity_literal_oracle(small_cases):
         assert (rec == orec).all(), case.k
 
 
+def test_rank_blocks_of_64_nodes(backend, monkeypatch):
+    """Indexes of 20 M nodes or more keep their rank blocks as 64 nodes per 64 bytes (layout.h: one 256-bit load per probe, half the
+    bytes); NTC_RANK_NODES=64 selects that layout for small indexes.  Same matching statistics, records and round trips as the
+    oracle: reads across block borders, intervals whose ends lie in different blocks, the prefix table built from these blocks."""
+    monkeypatch.setenv("NTC_RANK_NODES", "64")
+    rng = np.random.default_rng(64)
+    for k, sizes in [(12, [700, 90]), (31, [20000, 500]), (91, [30000]), (255, [1500, 900])]:
+        case = Case(backend, [helpers.random_seq(rng, n) for n in sizes], k)
+        reads = _reads_for(rng, case, 60)
+        bases, off = nt.concat_reads(reads)
+        d, s = case.ctx.matching_statistics(bases, off)
+        for i, r in enumerate(reads[:25]):
+            od, os_, _ = case.oracle.matching_statistics(r)
+            lo, hi = int(off[i]), int(off[i + 1])
+            assert (d[lo:hi] == od).all() and (s[lo:hi] == os_).all(), (k, i)
+        for T in (0, 256):
+            case.ctx.set_tile_len(T)
+            rec, roff = case.ctx.encode_batch(bases, off)
+            orec, oroff = case.oracle.encode_reads(bases, off, fast=True, threads=8)
+            assert (roff == oroff).all() and (rec == orec).all(), (k, T)
+        case.ctx.set_tile_len(0)
+        db, doff = case.ctx.decode_batch(rec)
+        assert (doff == off).all() and (db == bases).all()
+
+
 def test_long_read_segment_path(backend):
     """Reads longer than the tile length are segmented in 512-position segments (seg_spec / seg_join / seg_emit in
     encode_kernels.cuh): speculative walks per segment joined by the true walk.  Noisy long reads (walks merge at every
