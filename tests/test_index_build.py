@@ -170,6 +170,28 @@ def test_gpu_construction_larger_genomes(genome_len, k):
     assert st["launches"] > 0 and st["occurrences"] >= 2 * (genome_len - k + 1)
 
 
+@pytest.mark.gpu
+def test_gpu_construction_many_sequences_at_scale():
+    """20,000 sequences of 60..900 bases (a fragmented assembly): tens of thousands of source k-mers, more than a million dummy
+    candidates to sort, de-duplicate and merge; a quarter of the sequences are copies or substrings of others (sources that
+    have a predecessor elsewhere), some hold non-ACGT bytes."""
+    rng = np.random.default_rng(2024)
+    g = helpers.random_seq(rng, 20_000_000)
+    seqs = []
+    for i in range(20_000):
+        a = int(rng.integers(0, len(g) - 1000))
+        s = g[a:a + int(rng.integers(60, 900))].copy()
+        if i % 50 == 7:
+            s[len(s) // 2] = ord("N")
+        seqs.append(s)
+    seqs += [s[10:].copy() for s in seqs[:2500]] + [s.copy() for s in seqs[2500:5000]]
+    for k in (31, 91):
+        st = {}
+        a = nt.Index.build_gpu(seqs, k, True, stats=st)
+        _same_index(a, nt.Index.build(seqs, k, True))
+        assert st["sources"] > 5_000 and st["dummies"] > 100_000
+
+
 def test_gpu_construction_needs_a_gpu_or_succeeds():
     """no CPU fallback: without a device the call fails with NTC_ERR_CUDA"""
     import torch
