@@ -394,6 +394,10 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
         L = _lib.lib()
         n_rec_c, n_bytes_c, n_seqs_c = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
         split = [0.0, 0.0]
+        # encode: this rank's share of the host's threads packs the reads to 2 bits per base before they cross PCIe
+        # (ntc_ctx_set_host_threads; NTC_HOST_THREADS=0 leaves the packing to the GPU and sends ASCII)
+        host_threads = int(os.environ.get("NTC_HOST_THREADS", "0"))
+        ctx.set_host_threads(host_threads)
 
         def e2e_step():
             ta = time.perf_counter()
@@ -432,10 +436,11 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
             e2e_step()
         torch.cuda.synchronize()
         t_e2e = R.reduce([time.perf_counter() - t0])[0]
-        h2d = nbe + (ne + 1) * 8 + n_rec_e * 8
+        h2d = (((nbe + 31) // 32 + 4) * 8 if host_threads > 0 else nbe) + (ne + 1) * 8 + n_rec_e * 8
         d2h = n_rec_e * 8 + int(n_bytes_c.value)
         e2e = {"value": nbe * world * e2e_steps / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "steps": e2e_steps, "api": "ntc_encode_batch + ntc_decode_fasta, pinned host buffers", "reads_per_gpu": ne,
+               "host_pack_threads": host_threads,   # > 0: reads cross PCIe as 0.25 B/base, packed by that many host threads per GPU inside ntc_encode_batch
                "copy_directions": "serial (all input up, then results down)" if copy_serial else "duplex (results travel back while the next chunk goes up)",
                "encode_ms_per_step": 1e3 * split[0] / e2e_steps, "decode_ms_per_step": 1e3 * split[1] / e2e_steps,
                "pcie_h2d_gbs": pcie[0], "pcie_d2h_gbs": pcie[1],   # per GPU, all ranks copying at once (min over ranks)

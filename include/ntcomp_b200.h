@@ -105,6 +105,15 @@ int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len);
  * (profiles/r2/ab_copy_directions.txt), so the default is duplex.  NTC_COPY_DIRECTIONS=serial|duplex sets the initial value. */
 int32_t ntc_ctx_set_copy_directions(ntc_ctx* ctx, int32_t serial);
 
+/* Host-buffer encode: n_threads > 0 = that many host threads turn the reads into the 2-bit stream while the GPU works on the chunk
+ * before (AVX2, ~8 GB/s per thread alone), so 0.25 B per base cross PCIe instead of 1; 0 (the default) = the ASCII bytes are copied up
+ * and packed on the GPU; < 0 = this GPU's share of the host's threads, at most 16, off below 4.  Same results either way (a non-ACGT
+ * byte is NTC_ERR_BAD_BASE from whichever side packs).  Measured on the B200 boxes it does not beat page-locked copies over Gen5 x16
+ * (N = 1, 16 threads: encode 32.8-36.7 vs 32.0 ms per 1.5 G bases; N = 8, 4 threads per GPU: round trip 44.0 vs 50.1 Gbases/s;
+ * profiles/r2/ab_host_pack.txt), hence off by default -- for pageable `bases` buffers or slower links.  NTC_HOST_THREADS sets the
+ * initial value. */
+int32_t ntc_ctx_set_host_threads(ntc_ctx* ctx, int32_t n_threads);
+
 /* ---------------- encode ------------------------------------------------------------------- */
 
 /* flat_map(encode_dictionary . encode_sequence) over a batch of reads: src/main.rs:166,169 with

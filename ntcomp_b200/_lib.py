@@ -71,6 +71,7 @@ SIGNATURES = {
     "ntc_index_build_from_files_gpu": (_i32, [_i32, _vp, _u64, _u32, _i32, _i32, _pp]),
     "ntc_ctx_set_tile_len": (_i32, [_vp, _u32]),
     "ntc_ctx_set_copy_directions": (_i32, [_vp, _i32]),
+    "ntc_ctx_set_host_threads": (_i32, [_vp, _i32]),
     "ntc_ctx_kernel_times": (_i32, [_vp, _vp, _vp, _i32]),
     "ntc_l2_random_bench": (_i32, [_vp, _u64, _u32, _i32, _u32, _vp]),
     "ntc_matching_statistics": (_i32, [_vp, _vp, _vp, _u64, _vp, _vp]),

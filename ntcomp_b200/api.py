@@ -192,6 +192,10 @@ class Context:
         """host-buffer API: one PCIe direction at a time (True) or results travelling back while input goes up (False)"""
         check(_lib.lib().ntc_ctx_set_copy_directions(self._h, int(bool(serial))))
 
+    def set_host_threads(self, n_threads=-1):
+        """host-buffer encode: host threads that pack the reads to 2 bits per base before they cross PCIe (0 = off, < 0 = auto)"""
+        check(_lib.lib().ntc_ctx_set_host_threads(self._h, int(n_threads)))
+
     def encode_file(self, fastx_path, out_path, n_threads=0):
         """`ntcomp encode` (src/main.rs:141-181): fastX file -> encoded.dat; returns the stats dict"""
         st = np.zeros(6, dtype=np.uint64)

@@ -187,6 +187,7 @@ int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint
 // records are written at out[offset - *rel] (chunked host path: out is the chunk's staging buffer).
 // wait_scan: an event the scan must wait for (the previous chunk's scan on the other lane).
 // ------------------------------------------------------------------------------------------
+// d_bases == nullptr: lane.packed already holds the batch's 2-bit stream (packed on the host, api_host.inc).
 int32_t encode_pipeline(ntc_ctx* ctx, Lane& lane, int mode, const uint8_t* d_bases, const uint64_t* d_offsets, uint64_t n_reads,
                         uint64_t n_bases, uint64_t* d_out, uint64_t cap, uint64_t* d_rec_offsets, const uint64_t* carry,
                         uint64_t* totals_out, const uint64_t* rel, cudaEvent_t wait_scan, cudaStream_t st) {
@@ -211,7 +212,7 @@ int32_t encode_pipeline(ntc_ctx* ctx, Lane& lane, int mode, const uint8_t* d_bas
     uint64_t* scratch = (uint64_t*)lane.scratch.p;
     uint32_t* counts = (uint32_t*)lane.counts.p;
 
-    if (n_bases) {
+    if (n_bases && d_bases) {
         Timed t(ctx, KC_PACK, st);
         pack2bit_kernel<<<blocks_for((n_bases + 31) / 32, kPackThreads), kPackThreads, 0, st>>>(d_bases, d_offsets, n_bases, packed,
                                                                                                 ctx->d_status);
@@ -474,6 +475,7 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
             }
         }
     }
+    ntc_ctx_set_host_threads(ctx, getenv("NTC_HOST_THREADS") ? atoi(getenv("NTC_HOST_THREADS")) : 0);   // off by default: measured no faster than the link (api_host.inc)
     if (const char* env = getenv("NTC_TILE_LEN")) ntc_ctx_set_tile_len(ctx, (uint32_t)strtoul(env, nullptr, 10));
     if (const char* env = getenv("NTC_SPEC_LO")) ctx->dix.spec_lo = (uint32_t)strtoul(env, nullptr, 10);      // tuning knobs
     if (const char* env = getenv("NTC_SPEC_SPAN")) ctx->dix.spec_span = (uint32_t)strtoul(env, nullptr, 10);
@@ -498,6 +500,8 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
     }
     free_column_work(ctx);
     release(&ctx->hold); release(&ctx->hold2);
+    delete ctx->pool;
+    for (void* p : ctx->h_pack) if (p) cudaFreeHost(p);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
     for (auto ev : ctx->event_pool) cudaEventDestroy(ev);
     cudaFree(ctx->d_rank); cudaFree(ctx->d_lcs); cudaFree(ctx->d_jump); cudaFree(ctx->d_pfx);
@@ -522,6 +526,20 @@ int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len) {
     if (tile_len && tile_len < kTileMin) { set_error("tile length must be 0 (automatic) or >= 256"); return NTC_ERR_INVALID_ARG; }
     if (tile_len > (1u << 22)) tile_len = 1u << 22;
     ctx->tile_len = (tile_len + 3u) & ~3u;
+    return NTC_OK;
+}
+
+int32_t ntc_ctx_set_host_threads(ntc_ctx* ctx, int32_t n_threads) {
+    if (!ctx) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    if (n_threads < 0) {                                              // auto: this GPU's share of the host's threads, when that is enough to beat the link
+        int n_dev = 1;
+        cudaGetDeviceCount(&n_dev);
+        const int share = (int)std::thread::hardware_concurrency() / std::max(1, n_dev);
+        n_threads = share >= 4 ? std::min(share, 16) : 0;
+    }
+    n_threads = std::min(n_threads, 64);
+    if (ctx->pool && ctx->pool->threads() != n_threads) { delete ctx->pool; ctx->pool = nullptr; }
+    ctx->host_threads = n_threads;
     return NTC_OK;
 }
 

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "device_common.cuh"
+#include "host_pack.h"
 #include "scan.cuh"
 
 namespace ntc {
@@ -65,6 +66,13 @@ struct ntc_ctx {
     // (ranks out of phase: profiles/r2/ab_copy_directions.txt), so the default is 0.  NTC_COPY_DIRECTIONS=serial|duplex.
     int copy_serial = 0;
     ntc::DevBuf hold, hold2;        // copy_serial: records / offsets of a whole call parked in HBM
+    // Host-buffer encode: host_threads > 0 = that many host threads turn each chunk of ASCII reads into the 2-bit stream (host_pack.cpp) in
+    // page-locked staging, so 0.25 B per base cross PCIe and pack2bit_kernel is skipped; 0 (default) = the ASCII bytes are copied up and packed on
+    // the GPU.  Measured no faster than page-locked copies over Gen5 x16 at N = 1 and slower at N = 8 (profiles/r2/ab_host_pack.txt).
+    int host_threads = 0;
+    ntc::HostPool* pool = nullptr;  // created on first use
+    void* h_pack[2] = {nullptr, nullptr};
+    size_t h_pack_cap[2] = {0, 0};
     void* colwork = nullptr;        // workspaces + pinned landing buffers of the GPU column codec, both directions (api_columns.inc)
 
     // optional per-kernel-class timing with CUDA events on the launching stream (bench.py roofline)

@@ -79,6 +79,7 @@ extern "C" {
     pub fn ntc_ctx_index_bytes(ctx: *const ntc_ctx, out: *mut u64);
     pub fn ntc_ctx_set_tile_len(ctx: *mut ntc_ctx, tile_len: u32) -> i32;
     pub fn ntc_ctx_set_copy_directions(ctx: *mut ntc_ctx, serial: i32) -> i32;
+    pub fn ntc_ctx_set_host_threads(ctx: *mut ntc_ctx, n_threads: i32) -> i32;
 
     // ---- encode ----
     pub fn ntc_encode_batch(ctx: *mut ntc_ctx, bases: *const u8, offsets: *const u64, n_reads: u64, records: *mut u64, cap: u64,

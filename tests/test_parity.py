@@ -374,6 +374,22 @@ def test_chunked_host_path_matches_unchunked(monkeypatch, small_cases):
             assert e.value.code == 3
         finally:
             c.set_copy_directions(False)
+    # who packs the reads to 2 bits (ntc_ctx_set_host_threads): host threads before the copy (1, 3 and 16 of them; partial last words,
+    # chunks of a few thousand bases) or pack2bit_kernel after it -- same records, the same error for a non-ACGT byte
+    for c in (ctx2, case0.ctx):
+        for threads in (0, 1, 3, 16):
+            c.set_host_threads(threads)
+            rec5, roff5 = c.encode_batch(bases, off)
+            assert (rec5 == rec).all() and (roff5 == roff).all(), threads
+            tri5, _ = c.encode_sequence_batch(bases, off)
+            assert (tri5 == tri).all()
+            for bad in (b"ACGTNNNN", b"ACGTacgt", b"ACGU" * 20):
+                with pytest.raises(nt.NtcError) as e:
+                    c.encode_batch(*nt.concat_reads(reads[:200] + [bad] + reads[200:]))
+                assert e.value.code == 5, (threads, bad)
+            rec5, roff5 = c.encode_batch(bases, off)
+            assert (rec5 == rec).all() and (roff5 == roff).all(), threads
+        c.set_host_threads(-1)
 
 
 @pytest.mark.parametrize("cfg", ["C2-small", "C3-small", "C5-small"])
