@@ -13,6 +13,7 @@
 extern "C" {
 void* emul_index_create(const ntc_index* idx);
 void emul_index_free(void* p);
+void emul_set_tile_len(void* p, uint32_t T);
 uint32_t emul_encode(void* ep, const uint8_t* bases, const uint64_t* offsets, uint64_t n_reads, int mode, uint64_t* out, uint64_t cap,
                      uint64_t* n_records, uint64_t* rec_offsets);
 uint32_t emul_decode(void* ep, const uint64_t* rec, uint64_t n_rec, uint64_t first_no, int fasta, uint8_t* out, uint64_t cap,
@@ -23,9 +24,50 @@ int emul_columns_decode(const uint64_t* cols_in, uint32_t n_blocks, const uint64
                         uint64_t* rec, uint64_t cap, uint64_t* n_rec_out, uint32_t* detail);
 }
 
+extern "C" int32_t emul_index_build(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n_seqs, uint32_t k, int32_t add_revcomp,
+                                    ntc_index** out, uint64_t* stats);
+
+// the GPU index construction (build_pipeline.h) with exactly-sized work arrays: many short sequences, separators, k up to 255
+static int check_builder(std::mt19937_64& rng) {
+    const char* alpha = "ACGTN";
+    for (uint32_t k : {12u, 31u, 33u, 91u, 255u}) {
+        std::vector<std::vector<uint8_t>> store;
+        for (int i = 0; i < 12; i++) {
+            std::vector<uint8_t> s(rng() % (3 * k + 40));
+            for (auto& b : s) b = (uint8_t)alpha[rng() % (i % 4 == 0 ? 5 : 4)];
+            store.push_back(s);
+        }
+        store.push_back(store[1]);
+        std::vector<const uint8_t*> ptrs;
+        std::vector<uint64_t> lens;
+        for (auto& s : store) { ptrs.push_back(s.data()); lens.push_back(s.size()); }
+        for (int rc = 0; rc < 2; rc++) {
+            ntc_index *a = nullptr, *b = nullptr;
+            if (emul_index_build(ptrs.data(), lens.data(), ptrs.size(), k, rc, &a, nullptr)) return 20;
+            if (ntc_index_build(ptrs.data(), lens.data(), ptrs.size(), k, rc, 2, &b)) return 21;
+            const uint64_t n = ntc_index_n_sets(a);
+            if (n != ntc_index_n_sets(b)) return 22;
+            std::vector<uint8_t> la(n), lb(n);
+            ntc_index_get_lcs(a, la.data());
+            ntc_index_get_lcs(b, lb.data());
+            if (la != lb) return 23;
+            std::vector<uint64_t> ra((n + 63) / 64), rb((n + 63) / 64);
+            for (int c = 0; c < 4; c++) {
+                ntc_index_get_row(a, c, ra.data());
+                ntc_index_get_row(b, c, rb.data());
+                if (ra != rb) return 24;
+            }
+            ntc_index_free(a);
+            ntc_index_free(b);
+        }
+    }
+    return 0;
+}
+
 int main() {
     std::mt19937_64 rng(7);
     const char* alpha = "ACGT";
+    if (int rc = check_builder(rng)) { fprintf(stderr, "index construction check failed: %d\n", rc); return rc; }
     for (int round = 0; round < 6; round++) {
         const uint32_t k = round % 3 == 0 ? 12 : (round % 3 == 1 ? 31 : 91);
         std::vector<uint8_t> g(3000 + 2000 * round);
@@ -35,6 +77,7 @@ int main() {
         ntc_index* idx = nullptr;
         if (ntc_index_build(seqs, lens, 1, k, 1, 2, &idx)) { fprintf(stderr, "build failed: %s\n", ntc_last_error()); return 2; }
         void* e = emul_index_create(idx);
+        if (round & 1) emul_set_tile_len(e, 256);                     // reads of up to 700 bases become several tiles: the segment path (seg_*_thread)
         std::vector<uint8_t> bases;
         std::vector<uint64_t> off(1, 0);
         for (int r = 0; r < 300; r++) {
