@@ -92,6 +92,11 @@ void ntc_ctx_destroy(ntc_ctx* ctx);
 /* bytes of HBM held by the re-laid-out index: [0]=rank blocks, [1]=LCS, [2]=decode jump table */
 void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]);
 
+/* Copy of one derived device array as the kernels see it (which: 0 rank blocks, 1 LCS words, 2 decode jump table, 3 prefix table;
+ * *n_bytes = its size, 0 when this context does not hold it; out may be NULL to ask for the size).  Diagnostic: the tests compare the
+ * arrays built by kernels at context creation with the host builders' (NTC_HOST_LAYOUTS=1 makes ntc_ctx_create use those). */
+int32_t ntc_ctx_layout_read(ntc_ctx* ctx, int32_t which, void* out, uint64_t cap, uint64_t* n_bytes);
+
 /* Matching-statistics tile length.  A read longer than the tile is processed as independent tiles of
  * that many positions, each warmed up on the k-1 bases before it (long reads, BASELINE config C5: a
  * 10 kbp read is ~20 chains instead of one); the output is identical for every tile length.

@@ -39,6 +39,7 @@ SIGNATURES = {
     "ntc_pinned_free": (None, [_vp]),
     "ntc_ctx_destroy": (None, [_vp]),
     "ntc_ctx_index_bytes": (None, [_vp, _vp]),
+    "ntc_ctx_layout_read": (_i32, [_vp, _i32, _vp, _u64, _vp]),
     "ntc_encode_batch": (_i32, [_vp, _vp, _vp, _u64, _vp, _u64, _vp, _vp]),
     "ntc_encode_sequence_batch": (_i32, [_vp, _vp, _vp, _u64, _vp, _u64, _vp, _vp]),
     "ntc_encode_dictionary": (_i32, [_vp, _vp, _u64, _vp]),

@@ -182,6 +182,15 @@ class Context:
         _lib.lib().ntc_ctx_index_bytes(self._h, _ptr(out))
         return {"rank": int(out[0]), "lcs": int(out[1]), "jump": int(out[2])}
 
+    def layout(self, which):
+        """derived device array `which` (0 rank blocks, 1 LCS words, 2 jump table, 3 prefix table) as bytes -- diagnostic"""
+        n = C.c_uint64(0)
+        check(_lib.lib().ntc_ctx_layout_read(self._h, which, None, 0, C.byref(n)))
+        out = np.zeros(n.value, dtype=np.uint8)
+        if n.value:
+            check(_lib.lib().ntc_ctx_layout_read(self._h, which, _ptr(out), n.value, C.byref(n)))
+        return out
+
     KERNEL_CLASSES = ["pack2bit", "ms", "scan", "emit", "decode_scan", "seq_offsets", "walk", "misc", "column_encode", "column_decode"]
 
     def set_tile_len(self, tile_len=0):

@@ -18,6 +18,7 @@
 #include "decode_kernels.cuh"
 #include "encode_kernels.cuh"
 #include "host_index.h"
+#include "layout_kernels.cuh"
 #include "synth_common.h"
 
 using namespace ntc;
@@ -350,9 +351,11 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
     const bool trace = getenv("NTC_TRACE") != nullptr;
     const auto t0 = std::chrono::steady_clock::now();
     auto since = [&]() { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); };
-    // The derived HBM layouts are built on the host cores WHILE the CUDA context comes up on another thread (the
-    // driver's start-up is the longer of the two on a cold process); an encode-only / decode-only context (the CLI)
-    // builds and uploads only the arrays its path reads.
+    // The derived HBM layouts (rank blocks, LCS words, jump and prefix tables) are built by kernels from the canonical arrays
+    // (layout_kernels.cuh): 1.5 B per node go up instead of 14.  NTC_HOST_LAYOUTS=1 (and builds with 16-bit LCS words) take the
+    // first version's route: host threads build them WHILE the CUDA context comes up on another thread, then they are uploaded.
+    // An encode-only / decode-only context (the CLI) holds only the arrays its path reads.
+    const bool host_layouts = NTC_LCS16 != 0 || (getenv("NTC_HOST_LAYOUTS") && atoi(getenv("NTC_HOST_LAYOUTS")) != 0);
     int n_dev = 0;
     cudaError_t e_init = cudaSuccess;
     double t_cuda = 0;
@@ -373,7 +376,7 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
     const bool use_pfx = idx->k >= 10 && !getenv("NTC_NO_PREFIX_TABLE");   // a tile's warm-up (k-1 bases) must cover the 8 bases
     double t_rank = 0, t_lcs = 0, t_jump = 0;
     std::exception_ptr build_err;
-    {
+    if (host_layouts) {
         std::thread lcs_thread;
         try {
             if (uses & NTC_USE_ENCODE) lcs_thread = std::thread([&]() { build_lcs_words(*idx, &lcs); t_lcs = since(); });   // serial stack pass
@@ -385,6 +388,8 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
             if (uses & NTC_USE_DECODE) { build_jump_table(*idx, &jump, std::max(1, threads - 1)); t_jump = since(); }
         } catch (...) { build_err = std::current_exception(); }
         if (lcs_thread.joinable()) lcs_thread.join();
+    } else {
+        for (int c = 0; c < 4; c++) c_start[c] = (uint32_t)idx->C[c];   // interval start after the single base c = rank_c(0) + C[c]
     }
     cuda_up.join();
     if (build_err) { set_error("out of host memory while deriving the index layouts"); return NTC_ERR_INVALID_ARG; }
@@ -415,22 +420,76 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
         ntc_ctx_destroy(ctx);
         return NTC_ERR_CUDA;
     };
-    ctx->index_bytes[0] = rank.size() * 4;
-    ctx->index_bytes[1] = lcs.size() * sizeof(ntc_lcsx_t);
-    ctx->index_bytes[2] = jump.size() * 8;
+    const uint64_t n = idx->n;
+    const uint64_t n_rank_blocks = n / rank_nodes + 1;                 // position n (interval end) must be addressable
+    ctx->index_bytes[0] = (uses & NTC_USE_ENCODE) ? n_rank_blocks * 64 : 0;
+    ctx->index_bytes[1] = (uses & NTC_USE_ENCODE) ? (n + 1) * sizeof(ntc_lcsx_t) : 0;
+    ctx->index_bytes[2] = (uses & NTC_USE_DECODE) ? n * 8 : 0;
+    const size_t pfx_bytes = (size_t)(1u << (2 * kPrefixBases)) * 8 * 4;
     if (uses & NTC_USE_ENCODE) {
         if ((e = cudaMalloc(&ctx->d_rank, ctx->index_bytes[0])) != cudaSuccess) return fail("cudaMalloc rank", e);
         if ((e = cudaMalloc(&ctx->d_lcs, ctx->index_bytes[1])) != cudaSuccess) return fail("cudaMalloc lcs", e);
-        if ((e = cudaMemcpy(ctx->d_rank, rank.data(), ctx->index_bytes[0], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload rank", e);
-        if ((e = cudaMemcpy(ctx->d_lcs, lcs.data(), ctx->index_bytes[1], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload lcs", e);
+        if (use_pfx && (e = cudaMalloc(&ctx->d_pfx, pfx_bytes)) != cudaSuccess) return fail("cudaMalloc prefix table", e);
     }
-    if (uses & NTC_USE_DECODE) {
-        if ((e = cudaMalloc(&ctx->d_jump, ctx->index_bytes[2])) != cudaSuccess) return fail("cudaMalloc jump", e);
-        if ((e = cudaMemcpy(ctx->d_jump, jump.data(), ctx->index_bytes[2], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload jump", e);
-    }
-    if (use_pfx && (uses & NTC_USE_ENCODE)) {
-        if ((e = cudaMalloc(&ctx->d_pfx, pfx.size() * 4)) != cudaSuccess) return fail("cudaMalloc prefix table", e);
-        if ((e = cudaMemcpy(ctx->d_pfx, pfx.data(), pfx.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload prefix table", e);
+    if ((uses & NTC_USE_DECODE) && (e = cudaMalloc(&ctx->d_jump, ctx->index_bytes[2])) != cudaSuccess) return fail("cudaMalloc jump", e);
+    if (host_layouts) {
+        if (uses & NTC_USE_ENCODE) {
+            if ((e = cudaMemcpy(ctx->d_rank, rank.data(), ctx->index_bytes[0], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload rank", e);
+            if ((e = cudaMemcpy(ctx->d_lcs, lcs.data(), ctx->index_bytes[1], cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload lcs", e);
+            if (use_pfx && (e = cudaMemcpy(ctx->d_pfx, pfx.data(), pfx_bytes, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("upload prefix table", e);
+        }
+        if ((uses & NTC_USE_DECODE) && (e = cudaMemcpy(ctx->d_jump, jump.data(), ctx->index_bytes[2], cudaMemcpyHostToDevice)) != cudaSuccess)
+            return fail("upload jump", e);
+    } else {
+        // canonical arrays up (4 rows + LCS bytes), ones-before-word of every row by two scans, then one kernel per layout
+        const uint64_t row_words = (n + 63) / 64;
+        uint64_t *d_rows = nullptr, *d_pre = nullptr, *d_tmp = nullptr, *d_tot = nullptr;
+        uint8_t* d_lcs8 = nullptr;
+        Pair64* d_tiles = nullptr;
+        auto cleanup = [&]() { cudaFree(d_rows); cudaFree(d_pre); cudaFree(d_tmp); cudaFree(d_tot); cudaFree(d_lcs8); cudaFree(d_tiles); };
+        auto fail2 = [&](const char* what, cudaError_t err) { cleanup(); return fail(what, err); };
+        if ((e = cudaMalloc(&d_rows, 4 * row_words * 8)) != cudaSuccess) return fail2("cudaMalloc rows", e);
+        if ((e = cudaMalloc(&d_pre, 4 * (row_words + 1) * 8)) != cudaSuccess) return fail2("cudaMalloc row prefixes", e);
+        if ((e = cudaMalloc(&d_lcs8, n + 1)) != cudaSuccess) return fail2("cudaMalloc lcs bytes", e);
+        if ((e = cudaMalloc(&d_tiles, scan_num_tiles(row_words) * sizeof(Pair64))) != cudaSuccess) return fail2("cudaMalloc scan tiles", e);
+        if ((e = cudaMalloc(&d_tot, 16)) != cudaSuccess) return fail2("cudaMalloc scan totals", e);
+        for (int c = 0; c < 4; c++)
+            if ((e = cudaMemcpy(d_rows + c * row_words, idx->rows[c].data(), row_words * 8, cudaMemcpyHostToDevice)) != cudaSuccess) return fail2("upload rows", e);
+        if ((e = cudaMemcpy(d_lcs8, idx->lcs.data(), n, cudaMemcpyHostToDevice)) != cudaSuccess) return fail2("upload lcs bytes", e);
+        lay::Rows rows;
+        rows.row_words = row_words;
+        for (int c = 0; c < 4; c++) { rows.row[c] = d_rows + c * row_words; rows.pre[c] = d_pre + c * (row_words + 1); }
+        for (int c = 0; c < 5; c++) rows.C[c] = idx->C[c];
+        for (int c = 0; c < 4; c += 2)
+            ctx->launches += exclusive_scan_pairs(lay::RowPopLoad{rows.row[c], rows.row[c + 1]}, row_words, d_tiles, nullptr, d_tot,
+                                                  d_pre + c * (row_words + 1), d_pre + (c + 1) * (row_words + 1), 0);
+        if (uses & NTC_USE_ENCODE) {
+            if (rank_nodes == 64) lay::rank_blocks_kernel<64><<<blocks_for(n_rank_blocks, 256), 256>>>(rows, d_lcs8, n, idx->k, (uint32_t*)ctx->d_rank, n_rank_blocks);
+            else lay::rank_blocks_kernel<32><<<blocks_for(n_rank_blocks, 256), 256>>>(rows, d_lcs8, n, idx->k, (uint32_t*)ctx->d_rank, n_rank_blocks);
+            lay::lcs_words_kernel<<<blocks_for(n + 1, 256), 256>>>(d_lcs8, n, (uint32_t*)ctx->d_lcs);
+            if (use_pfx) {
+                if (rank_nodes == 64) lay::prefix_table_kernel<64><<<256, 256>>>((const uint32_t*)ctx->d_rank, n, (uint32_t*)ctx->d_pfx);
+                else lay::prefix_table_kernel<32><<<256, 256>>>((const uint32_t*)ctx->d_rank, n, (uint32_t*)ctx->d_pfx);
+            }
+            ctx->launches += use_pfx ? 3 : 2;
+        }
+        if (uses & NTC_USE_DECODE) {
+            if ((e = cudaMalloc(&d_tmp, n * 8)) != cudaSuccess) return fail2("cudaMalloc jump scratch", e);
+            // four doubling rounds ping-pong between the scratch and the table: start in the table so that the last round lands in it
+            uint64_t* a = (uint64_t*)ctx->d_jump;
+            uint64_t* b = d_tmp;
+            lay::pred_init_kernel<<<blocks_for(row_words * 4, 256), 256>>>(rows, a);
+            for (uint32_t t = 1; t < 16; t *= 2) {
+                lay::pred_double_kernel<<<blocks_for(n, 256), 256>>>(a, b, t, n);
+                std::swap(a, b);
+            }
+            ctx->launches += 5;                                        // a == d_jump again after four swaps
+        }
+        e = cudaDeviceSynchronize();
+        if (e == cudaSuccess) e = cudaGetLastError();
+        cleanup();
+        if (e != cudaSuccess) return fail("deriving the index layouts on the device", e);
+        t_rank = t_lcs = t_jump = since();
     }
     if ((e = cudaMalloc((void**)&ctx->d_status, 16)) != cudaSuccess) return fail("cudaMalloc status", e);
     if ((e = cudaMalloc((void**)&ctx->d_totals, 64)) != cudaSuccess) return fail("cudaMalloc totals", e);
@@ -479,9 +538,12 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
     if (const char* env = getenv("NTC_TILE_LEN")) ntc_ctx_set_tile_len(ctx, (uint32_t)strtoul(env, nullptr, 10));
     if (const char* env = getenv("NTC_SPEC_LO")) ctx->dix.spec_lo = (uint32_t)strtoul(env, nullptr, 10);      // tuning knobs
     if (const char* env = getenv("NTC_SPEC_SPAN")) ctx->dix.spec_span = (uint32_t)strtoul(env, nullptr, 10);
-    if (trace)
+    if (trace && host_layouts)
         fprintf(stderr, "[ntc trace] ctx_create %.3f s: CUDA context up at %.3f (own thread) | host layouts: rank+prefix done at %.3f, lcs at %.3f, "
                 "jump at %.3f | uploads + policies %.3f\n", since(), t_cuda, t_rank, t_lcs, t_jump, since() - std::max(std::max(t_cuda, t_jump), std::max(t_rank, t_lcs)));
+    else if (trace)
+        fprintf(stderr, "[ntc trace] ctx_create %.3f s: CUDA context up at %.3f | canonical arrays up + layouts by kernels done at %.3f | policies %.3f\n",
+                since(), t_cuda, t_rank, since() - t_rank);
     *out = ctx;
     return NTC_OK;
 }
@@ -519,6 +581,18 @@ int32_t ntc_pinned_alloc(uint64_t bytes, void** out) {
 void ntc_pinned_free(void* p) { if (p) cudaFreeHost(p); }
 
 void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]) { memcpy(out, ctx->index_bytes, 24); }
+
+int32_t ntc_ctx_layout_read(ntc_ctx* ctx, int32_t which, void* out, uint64_t cap, uint64_t* n_bytes) {
+    if (!ctx || !n_bytes || which < 0 || which > 3) { set_error("invalid argument"); return NTC_ERR_INVALID_ARG; }
+    const void* src[4] = {ctx->d_rank, ctx->d_lcs, ctx->d_jump, ctx->d_pfx};
+    const uint64_t size[4] = {ctx->index_bytes[0], ctx->index_bytes[1], ctx->index_bytes[2], ctx->d_pfx ? (uint64_t)(1u << (2 * kPrefixBases)) * 32 : 0};
+    *n_bytes = src[which] ? size[which] : 0;
+    if (!out || *n_bytes == 0) return NTC_OK;
+    if (cap < *n_bytes) { set_error("output buffer too small"); return NTC_ERR_CAPACITY; }
+    NTC_CUDA_TRY(cudaSetDevice(ctx->device));
+    NTC_CUDA_TRY(cudaMemcpy(out, src[which], *n_bytes, cudaMemcpyDeviceToHost));
+    return NTC_OK;
+}
 uint64_t ntc_ctx_launch_count(const ntc_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
 int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len) {

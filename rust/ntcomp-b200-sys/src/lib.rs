@@ -77,6 +77,7 @@ extern "C" {
     pub fn ntc_ctx_create_for(device: i32, idx: *const ntc_index, uses: u32, out: *mut *mut ntc_ctx) -> i32;
     pub fn ntc_ctx_destroy(ctx: *mut ntc_ctx);
     pub fn ntc_ctx_index_bytes(ctx: *const ntc_ctx, out: *mut u64);
+    pub fn ntc_ctx_layout_read(ctx: *mut ntc_ctx, which: i32, out: *mut c_void, cap: u64, n_bytes: *mut u64) -> i32;
     pub fn ntc_ctx_set_tile_len(ctx: *mut ntc_ctx, tile_len: u32) -> i32;
     pub fn ntc_ctx_set_copy_directions(ctx: *mut ntc_ctx, serial: i32) -> i32;
     pub fn ntc_ctx_set_host_threads(ctx: *mut ntc_ctx, n_threads: i32) -> i32;

@@ -14,6 +14,7 @@
 #include "../../ntcomp_b200/csrc/decode_kernels.cuh"
 #include "../../ntcomp_b200/csrc/encode_kernels.cuh"
 #include "../../ntcomp_b200/csrc/host_index.h"
+#include "../../ntcomp_b200/csrc/layout_kernels.cuh"
 
 using namespace ntc;
 
@@ -340,4 +341,59 @@ extern "C" int32_t emul_index_build(const uint8_t* const* seqs, const uint64_t* 
     const int32_t rc = bld::sbwt_build(x, fwd.data(), fwd_len, k, add_revcomp != 0, out, &bs);
     if (stats) { stats[0] = bs.text_chars; stats[1] = bs.occurrences; stats[2] = bs.distinct; stats[3] = bs.sources; stats[4] = bs.dummies; stats[5] = bs.nodes; stats[6] = bs.sort_passes; }
     return rc;
+}
+
+// ---- derived layouts: the kernels' per-element bodies (layout_kernels.cuh) in loops against the host builders (host_index.cpp) ----
+// returns 0 when all four arrays are identical for both rank-block layouts, else a code naming the first difference
+extern "C" int32_t emul_layouts_check(const ntc_index* idx) {
+    const uint64_t n = idx->n, row_words = (n + 63) / 64;
+    std::vector<uint64_t> pre[4];
+    lay::Rows rows;
+    rows.row_words = row_words;
+    for (int c = 0; c < 4; c++) {
+        pre[c].assign(row_words + 1, 0);
+        for (uint64_t w = 0; w < row_words; w++) pre[c][w + 1] = pre[c][w] + (uint64_t)__builtin_popcountll(idx->rows[c][w]);   // the scan
+        rows.row[c] = idx->rows[c].data();
+        rows.pre[c] = pre[c].data();
+    }
+    for (int c = 0; c < 5; c++) rows.C[c] = idx->C[c];
+    for (uint32_t nodes : {32u, 64u}) {
+        std::vector<uint32_t> want, got, want_pfx, got_pfx((size_t)(1u << 16) * 8, 0xDEADBEEFu);
+        uint32_t c_start[4];
+        build_rank_blocks(*idx, &want, 2, nodes);
+        const uint64_t n_blocks = n / nodes + 1;
+        got.assign(n_blocks * 16, 0xDEADBEEFu);
+        for (uint64_t b = 0; b < n_blocks; b++) {
+            if (nodes == 32) lay::rank_block_thread<32>(rows, idx->lcs.data(), n, idx->k, got.data(), b);
+            else lay::rank_block_thread<64>(rows, idx->lcs.data(), n, idx->k, got.data(), b);
+        }
+        if (got != want) return 10 + (int32_t)nodes;
+        build_prefix_table(want, n, &want_pfx, c_start, nodes);
+        for (uint64_t x = 0; x < (1u << 16); x++) {
+            if (nodes == 32) lay::prefix_entry_thread<32>(got.data(), n, got_pfx.data(), x);
+            else lay::prefix_entry_thread<64>(got.data(), n, got_pfx.data(), x);
+        }
+        if (got_pfx != want_pfx) return 20 + (int32_t)nodes;
+        for (int c = 0; c < 4; c++) if (c_start[c] != (uint32_t)idx->C[c]) return 30;
+    }
+#if !NTC_LCS16
+    {
+        std::vector<ntc_lcsx_t> want;
+        build_lcs_words(*idx, &want);
+        std::vector<uint32_t> got(n + 1, 0xDEADBEEFu);
+        for (uint64_t i = 0; i <= n; i++) lay::lcs_word_thread(idx->lcs.data(), n, got.data(), i);
+        if (want.size() != got.size() || memcmp(want.data(), got.data(), got.size() * 4) != 0) return 40;
+    }
+#endif
+    {
+        std::vector<uint64_t> want, a(n, ~0ull), b(n, ~0ull);
+        build_jump_table(*idx, &want, 2);
+        for (uint64_t e = 0; e < row_words * 4; e++) lay::pred_init_thread(rows, a.data(), e);
+        for (uint32_t t = 1; t < 16; t *= 2) {
+            for (uint64_t v = 0; v < n; v++) lay::pred_double_thread(a.data(), b.data(), t, v);
+            a.swap(b);
+        }
+        if (a != want) return 50;
+    }
+    return 0;
 }

@@ -36,10 +36,18 @@ def lib():
         L.emul_dict_pack.argtypes = [vp, vp, u64, vp]
         L.emul_decode.restype = u32
         L.emul_decode.argtypes = [vp, vp, u64, u64, i32, vp, u64, vp, u64, vp]
+        L.emul_layouts_check.restype = i32
+        L.emul_layouts_check.argtypes = [vp]
         L.emul_index_build.restype = i32
         L.emul_index_build.argtypes = [vp, vp, u64, u32, i32, C.POINTER(vp), vp]
         _LIB = L
     return _LIB
+
+
+def layouts_check(index):
+    """layout_kernels.cuh bodies in loops against the host builders: 0 = rank blocks (both layouts), prefix table, LCS words and jump
+    table identical"""
+    return int(lib().emul_layouts_check(index._h))
 
 
 def index_build(seqs, k, add_revcomp=True, stats=None):

@@ -205,3 +205,49 @@ def test_gpu_construction_needs_a_gpu_or_succeeds():
     with pytest.raises(nt.NtcError) as e:
         nt.Index.build_gpu([g], 11)
     assert e.value.code == 9
+
+
+# ---- derived device layouts built by kernels at context creation (layout_kernels.cuh) ---------------------------------------
+def _layout_cases():
+    rng = np.random.default_rng(5)
+    yield [helpers.random_seq(rng, 700), helpers.random_seq(rng, 90)], 12
+    yield [helpers.random_seq(rng, 20000), helpers.random_seq(rng, 500), np.frombuffer(b"ACGTNNACGT" * 30, dtype=np.uint8)], 31
+    yield [helpers.random_seq(rng, 9000)], 91
+    yield [helpers.random_seq(rng, 1500), helpers.random_seq(rng, 900)], 255
+    yield [np.frombuffer(b"A" * 2000 + b"ACACACACAC" * 300, dtype=np.uint8)], 16        # LCS runs longer than 255 nodes: saturated distances
+    g = helpers.ALPHA[rng.integers(0, 3, size=30000)]
+    g[[5000, 12000, 12001, 20000, 29000]] = ord("T")
+    yield [g], 16                                                                        # skewed: almost no T
+
+
+def test_layout_kernel_bodies_match_host_builders():
+    import emul_binding
+    for seqs, k in _layout_cases():
+        for rc in (True, False):
+            assert emul_binding.layouts_check(nt.Index.build(seqs, k, rc)) == 0, k
+
+
+@pytest.mark.gpu
+def test_device_built_layouts_match_host_built_ones(monkeypatch):
+    """ntc_ctx_create derives rank blocks, LCS words, jump and prefix tables with kernels; NTC_HOST_LAYOUTS=1 takes the host builders
+    (the arrays every parity test of rounds 1-2 ran on).  Byte for byte the same, for both rank-block layouts and for
+    encode-only / decode-only contexts."""
+    from ntcomp_b200 import synth
+    cases = list(_layout_cases()) + [([synth.genome(1_500_000)], 91)]
+    for seqs, k in cases:
+        index = nt.Index.build(seqs, k)
+        for nodes in ("32", "64"):
+            monkeypatch.setenv("NTC_RANK_NODES", nodes)
+            monkeypatch.delenv("NTC_HOST_LAYOUTS", raising=False)
+            dev = nt.Context(index, 0)
+            monkeypatch.setenv("NTC_HOST_LAYOUTS", "1")
+            host = nt.Context(index, 0)
+            for which in range(4):
+                a, b = dev.layout(which), host.layout(which)
+                assert len(a) == len(b) and len(a) > 0 and (a == b).all(), (k, nodes, which)
+            del dev, host
+    monkeypatch.delenv("NTC_HOST_LAYOUTS", raising=False)
+    monkeypatch.delenv("NTC_RANK_NODES", raising=False)
+    enc = nt.Context(index, 0, uses=1) if "uses" in nt.Context.__init__.__code__.co_varnames else None
+    if enc is not None:
+        assert len(enc.layout(0)) > 0 and len(enc.layout(2)) == 0
