@@ -19,7 +19,10 @@
 namespace ntc {
 
 constexpr int kPackThreads = 256;
-constexpr int kMsThreads = 128;
+#ifndef NTC_MS_THREADS
+#define NTC_MS_THREADS 128          // threads per ms_kernel block; 64 (twice the resident blocks) measured in profiles/r2/ab_ms_threads.txt
+#endif
+constexpr int kMsThreads = NTC_MS_THREADS;
 constexpr uint32_t kLiteralMax = 11;  // bitnuc_threshold, src/encode.rs:137
 
 // ------------------------------------------------------------------------------------------
@@ -562,7 +565,7 @@ constexpr uint32_t kMsStageWordsMax = 1024;  // at most 8 KB of packed reads per
 // -- and twelve blocks of 40 registers measure 11.49 against 11.69 ms for ten of 48 (profiles/r2/ab_ms_blocks.txt).  Batches of longer
 // reads take the ten-block instantiation: twelve blocks with an 8 KB stage each would push the L1 below that size (12.55 ms, r1).
 template <int MIN_BLOCKS, int NODES>
-__global__ void __launch_bounds__(kMsThreads, MIN_BLOCKS) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
+__global__ void __launch_bounds__(kMsThreads, MIN_BLOCKS * (128 / kMsThreads)) ms_kernel(DevIndex ix, const uint64_t* __restrict__ packed,
                                                         const uint64_t* __restrict__ offsets, const uint64_t* __restrict__ desc,
                                                         const uint64_t* __restrict__ n_items, uint32_t T,
                                                         uint64_t* __restrict__ scratch, uint32_t* __restrict__ counts,
