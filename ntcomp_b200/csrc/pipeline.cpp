@@ -41,7 +41,8 @@ using ntc::set_error;
 namespace {
 
 constexpr uint64_t kBlockReads = 65536;            // src/main.rs:152
-constexpr uint64_t kBatchBlocksDefault = 4;        // blocks handed to the GPU per call (stage overlap granularity)
+constexpr uint64_t kBatchBlocksDefault = 2;        // blocks handed to the GPU per call (stage overlap granularity); with the gzip tasks of several
+                                                   // batches in flight: 2 -> 0.22 s, 4 -> 0.25 s, 8 -> 0.34 s per 600 Mbases (profiles/r2/cli_c3_inflight_*.json)
 constexpr uint64_t kBatchBases = 768ull << 20;     // ... or this many bases, whichever comes first
 
 uint64_t batch_blocks() {                          // NTC_PIPELINE_BATCH_BLOCKS overrides (tests: several groups from small files)
@@ -645,19 +646,32 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
         batches.finish();
     }, [&] { batches.finish(); }); });
 
-    // stage 4: gzip + headers per block on the pool (this thread only dispatches and collects, in order)
+    // stage 4: gzip + headers per SUB-block on the pool.  4a dispatches a batch's tasks and moves on -- the tasks of several batches are in flight
+    // at once, so the one big task of a block (the colex column, ~0.8 MB of coded words = ~25 ms of DEFLATE at the reference's level 6) no longer
+    // holds up the pool: the first version waited for each batch of 16 tasks before dispatching the next (0.38 s per 600 Mbases on 16 threads for
+    // 2.2 CPU-seconds of work).  4b collects the batches in order.
+    struct Latch { std::mutex m; std::condition_variable cv; size_t done = 0; };
+    struct InFlight {
+        std::shared_ptr<BytesBatch> out;
+        std::shared_ptr<std::vector<int32_t>> brc;
+        std::shared_ptr<Latch> latch;
+        size_t n_blocks = 0;
+    };
+    Channel<InFlight> flying(4);
     std::thread t_code([&] { stage_guard(&fatal, [&] {
         CodedBatch cb;
         while (coded.pop(&cb)) {
-            const double t0 = now_s();
-            const size_t n_blocks = cb.blocks.size();
-            auto out = std::make_shared<BytesBatch>();
-            out->parts.resize(n_blocks * 4);                           // one gzip task per sub-block: 4 x finer than per block
-            auto brc = std::make_shared<std::vector<int32_t>>(n_blocks * 4, NTC_OK);
+            InFlight f;
+            f.n_blocks = cb.blocks.size();
+            f.out = std::make_shared<BytesBatch>();
+            f.out->parts.resize(f.n_blocks * 4);                       // one gzip task per sub-block: 4 x finer than per block
+            f.brc = std::make_shared<std::vector<int32_t>>(f.n_blocks * 4, NTC_OK);
+            f.latch = std::make_shared<Latch>();
             auto shared = std::make_shared<CodedBatch>(std::move(cb));
-            struct Latch { std::mutex m; std::condition_variable cv; size_t done = 0; };
-            auto latch = std::make_shared<Latch>();
-            for (size_t j = 0; j < n_blocks * 4; j++)
+            auto out = f.out;
+            auto brc = f.brc;
+            auto latch = f.latch;
+            for (size_t j = 0; j < f.n_blocks * 4; j++)
                 pool.submit([j, out, brc, shared, latch, &gzip_us] {
                     const double g0 = now_s();
                     const ntc_coded_block& blk = shared->blocks[j / 4];
@@ -676,22 +690,30 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
                     latch->done++;
                     latch->cv.notify_all();
                 });
-            { std::unique_lock<std::mutex> lk(latch->m); latch->cv.wait(lk, [&] { return latch->done == n_blocks * 4; }); }
-            for (size_t j = 0; j < n_blocks; j++) {
+            if (!flying.push(std::move(f))) { coded.close(); return; }
+        }
+        flying.finish();
+    }, [&] { coded.close(); flying.finish(); }); });
+    std::thread t_collect([&] { stage_guard(&fatal, [&] {
+        InFlight f;
+        while (flying.pop(&f)) {
+            const double t0 = now_s();
+            { std::unique_lock<std::mutex> lk(f.latch->m); f.latch->cv.wait(lk, [&] { return f.latch->done == f.n_blocks * 4; }); }
+            for (size_t j = 0; j < f.n_blocks; j++) {
                 int32_t r = NTC_OK;
-                for (int q = 0; q < 4; q++) if ((*brc)[j * 4 + q] != NTC_OK) r = (*brc)[j * 4 + q];
+                for (int q = 0; q < 4; q++) if ((*f.brc)[j * 4 + q] != NTC_OK) r = (*f.brc)[j * 4 + q];
                 if (r == NTC_OK) st[4]++;
                 else {
-                    for (int q = 0; q < 4; q++) out->parts[j * 4 + q].clear();
+                    for (int q = 0; q < 4; q++) f.out->parts[j * 4 + q].clear();
                     if (r == NTC_ERR_EMPTY_COLUMN) st[5]++;            // dropped, as the reference does (Q4)
-                    else { out->rc = r; out->msg = "block container failed"; }
+                    else { f.out->rc = r; f.out->msg = "block container failed"; }
                 }
             }
             t_stage[3] += now_s() - t0;
-            if (!bytes.push(std::move(*out))) { coded.close(); return; }
+            if (!bytes.push(std::move(*f.out))) { flying.close(); return; }
         }
         bytes.finish();
-    }, [&] { coded.close(); bytes.finish(); }); });
+    }, [&] { flying.close(); bytes.finish(); }); });
 
     // stage 5: write in order
     int32_t w_rc = NTC_OK;
@@ -742,6 +764,7 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
     coded.finish();
     t_batch.join();
     t_code.join();
+    t_collect.join();
     t_write.join();
     if (pool.failed()) fatal = true;
     if (rc == NTC_OK && w_rc != NTC_OK) { rc = w_rc; msg = w_msg; }
@@ -749,7 +772,7 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
     in.close();
     sink.close();
     if (getenv("NTC_TRACE"))
-        fprintf(stderr, "[ntc trace] encode_file busy seconds: cut %.3f, place %.3f, gpu %.3f, gzip (wall, dispatch + wait) %.3f, write %.3f | pool work: "
+        fprintf(stderr, "[ntc trace] encode_file busy seconds: cut %.3f, place %.3f, gpu %.3f, gzip (collector waiting, in order) %.3f, write %.3f | pool work: "
                 "copy into batch %.3f, headers + gzip %.3f\n", t_stage[0], t_stage[1], t_stage[2], t_stage[3], t_stage[4], copy_us.load() * 1e-6,
                 gzip_us.load() * 1e-6);
     if (stats) memcpy(stats, st, sizeof(st));
