@@ -236,7 +236,7 @@ using namespace ntc;
 extern "C" {
 
 const char* ntc_last_error(void) { return ntc::last_error(); }
-const char* ntc_version(void) { return "ntcomp_b200 0.1 (sm_100a)"; }
+const char* ntc_version(void) { return "ntcomp_b200 0.2 (sm_100a)"; }
 
 int32_t ntc_index_build(const uint8_t* const* seqs, const uint64_t* lens, uint64_t n_seqs, uint32_t k, int32_t add_revcomp,
                         int32_t n_threads, ntc_index** out) {
