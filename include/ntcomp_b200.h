@@ -110,13 +110,14 @@ int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len);
  * (profiles/r2/ab_copy_directions.txt), so the default is duplex.  NTC_COPY_DIRECTIONS=serial|duplex sets the initial value. */
 int32_t ntc_ctx_set_copy_directions(ntc_ctx* ctx, int32_t serial);
 
-/* Host-buffer encode: n_threads > 0 = that many host threads turn the reads into the 2-bit stream while the GPU works on the chunk
- * before (AVX2, ~8 GB/s per thread alone), so 0.25 B per base cross PCIe instead of 1; 0 (the default) = the ASCII bytes are copied up
- * and packed on the GPU; < 0 = this GPU's share of the host's threads, at most 16, off below 4.  Same results either way (a non-ACGT
- * byte is NTC_ERR_BAD_BASE from whichever side packs).  Measured on the B200 boxes it does not beat page-locked copies over Gen5 x16
- * (N = 1, 16 threads: encode 32.8-36.7 vs 32.0 ms per 1.5 G bases; N = 8, 4 threads per GPU: round trip 44.0 vs 50.1 Gbases/s;
- * profiles/r2/ab_host_pack.txt), hence off by default -- for pageable `bases` buffers or slower links.  NTC_HOST_THREADS sets the
- * initial value. */
+/* Host threads of the host-buffer entry points.  PAGEABLE caller buffers (a Rust Vec, a numpy array) are moved through page-locked
+ * staging owned by the context, filled and emptied by a pool of host threads: the reads are packed to 2 bits per base on the way up,
+ * records, offsets and text are copied.  A pageable cudaMemcpy runs at 7.5 GB/s up and 14 GB/s down on the B200 boxes; with the staging,
+ * 1.5 G bases encode in 41 instead of 167-200 ms and decode to FASTA in 46 instead of 109-119 ms (16 threads; page-locked buffers: 32 + 31 ms;
+ * profiles/r2/pageable_probe*.json).  Page-locked caller buffers (ntc_pinned_alloc, cudaHostAlloc, cudaHostRegister) are copied by the DMA
+ * engines directly.  n_threads < 0 (the default) = the above with this GPU's share of the host's threads (at most 16, off below 2);
+ * 0 = never use host threads; n > 0 = n threads, and reads in page-locked buffers are packed on the host too (measured no faster there:
+ * profiles/r2/ab_host_pack.txt).  Same results in every mode.  NTC_HOST_THREADS sets the initial value. */
 int32_t ntc_ctx_set_host_threads(ntc_ctx* ctx, int32_t n_threads);
 
 /* ---------------- encode ------------------------------------------------------------------- */

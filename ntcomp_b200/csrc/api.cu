@@ -323,6 +323,37 @@ int32_t decode_pipeline(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_rec,
     return decode_walk(ctx, lane, d_records, n_rec, first_no, fasta, d_out, cap, d_counts, st);
 }
 
+// ---- page-locked staging for pageable caller buffers (ctx.h) ---------------------------------------------------------------
+bool is_pageable(const void* p) {
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+// the pool, if host threads may be used on this context (created on first use)
+HostPool* host_pool(ntc_ctx* ctx) {
+    const int n = ctx->host_threads > 0 ? ctx->host_threads : (ctx->host_threads < 0 ? ctx->auto_threads : 0);
+    if (n <= 0) return nullptr;
+    if (!ctx->pool) ctx->pool = new HostPool(n);
+    return ctx->pool;
+}
+cudaError_t ensure_pinned(ntc_ctx::Pinned* h, size_t bytes) {
+    if (bytes <= h->cap) return cudaSuccess;
+    if (h->p) cudaFreeHost(h->p);
+    h->p = nullptr; h->cap = 0;
+    const size_t want = bytes + bytes / 8 + 4096;
+    cudaError_t e = cudaHostAlloc(&h->p, want, cudaHostAllocPortable);
+    if (e == cudaSuccess) h->cap = want;
+    return e;
+}
+void pool_memcpy(HostPool& pool, void* dst, const void* src, size_t bytes) {
+    const size_t piece = 2u << 20;
+    pool.run((bytes + piece - 1) / piece, [&](uint64_t i) {
+        const size_t a = (size_t)i * piece, n = std::min(piece, bytes - a);
+        memcpy((uint8_t*)dst + a, (const uint8_t*)src + a, n);
+    });
+}
+
 int32_t read_status(ntc_ctx* ctx, cudaStream_t st) {
     uint32_t h = 0;
     NTC_CUDA_TRY(cudaMemcpyAsync(&h, ctx->d_status, 4, cudaMemcpyDeviceToHost, st));
@@ -501,6 +532,8 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
         if ((e = cudaEventCreateWithFlags(&ln.ev_done, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
         if ((e = cudaHostAlloc((void**)&ln.h_land, 64, cudaHostAllocMapped)) != cudaSuccess) return fail("cudaHostAlloc", e);
     }
+    for (cudaEvent_t& ev : ctx->ev_out)
+        if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
     ctx->stream = ctx->lanes[0].stream;
     ctx->dix.rank = (const uint4*)ctx->d_rank;
     ctx->dix.lcsx = (const ntc_lcsx_t*)ctx->d_lcs;
@@ -534,7 +567,7 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
             }
         }
     }
-    ntc_ctx_set_host_threads(ctx, getenv("NTC_HOST_THREADS") ? atoi(getenv("NTC_HOST_THREADS")) : 0);   // off by default: measured no faster than the link (api_host.inc)
+    ntc_ctx_set_host_threads(ctx, getenv("NTC_HOST_THREADS") ? atoi(getenv("NTC_HOST_THREADS")) : -1);   // default: staging for pageable caller buffers only
     if (const char* env = getenv("NTC_TILE_LEN")) ntc_ctx_set_tile_len(ctx, (uint32_t)strtoul(env, nullptr, 10));
     if (const char* env = getenv("NTC_SPEC_LO")) ctx->dix.spec_lo = (uint32_t)strtoul(env, nullptr, 10);      // tuning knobs
     if (const char* env = getenv("NTC_SPEC_SPAN")) ctx->dix.spec_span = (uint32_t)strtoul(env, nullptr, 10);
@@ -563,7 +596,9 @@ void ntc_ctx_destroy(ntc_ctx* ctx) {
     free_column_work(ctx);
     release(&ctx->hold); release(&ctx->hold2);
     delete ctx->pool;
-    for (void* p : ctx->h_pack) if (p) cudaFreeHost(p);
+    for (auto& h : ctx->h_in) if (h.p) cudaFreeHost(h.p);
+    for (auto& h : ctx->h_out) if (h.p) cudaFreeHost(h.p);
+    for (cudaEvent_t ev : ctx->ev_out) if (ev) cudaEventDestroy(ev);
     for (auto& sp : ctx->spans) { cudaEventDestroy(sp.e0); cudaEventDestroy(sp.e1); }
     for (auto ev : ctx->event_pool) cudaEventDestroy(ev);
     cudaFree(ctx->d_rank); cudaFree(ctx->d_lcs); cudaFree(ctx->d_jump); cudaFree(ctx->d_pfx);
@@ -605,15 +640,13 @@ int32_t ntc_ctx_set_tile_len(ntc_ctx* ctx, uint32_t tile_len) {
 
 int32_t ntc_ctx_set_host_threads(ntc_ctx* ctx, int32_t n_threads) {
     if (!ctx) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
-    if (n_threads < 0) {                                              // auto: this GPU's share of the host's threads, when that is enough to beat the link
-        int n_dev = 1;
-        cudaGetDeviceCount(&n_dev);
-        const int share = (int)std::thread::hardware_concurrency() / std::max(1, n_dev);
-        n_threads = share >= 4 ? std::min(share, 16) : 0;
-    }
-    n_threads = std::min(n_threads, 64);
-    if (ctx->pool && ctx->pool->threads() != n_threads) { delete ctx->pool; ctx->pool = nullptr; }
-    ctx->host_threads = n_threads;
+    int n_dev = 1;
+    cudaGetDeviceCount(&n_dev);
+    const int share = (int)std::thread::hardware_concurrency() / std::max(1, n_dev);   // this GPU's share of the host's threads
+    ctx->auto_threads = share >= 2 ? std::min(share, 16) : 0;
+    ctx->host_threads = n_threads < 0 ? -1 : std::min(n_threads, 64);
+    const int want = ctx->host_threads > 0 ? ctx->host_threads : ctx->auto_threads;
+    if (ctx->pool && ctx->pool->threads() != want) { delete ctx->pool; ctx->pool = nullptr; }
     return NTC_OK;
 }
 

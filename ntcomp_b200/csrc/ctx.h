@@ -66,13 +66,19 @@ struct ntc_ctx {
     // (ranks out of phase: profiles/r2/ab_copy_directions.txt), so the default is 0.  NTC_COPY_DIRECTIONS=serial|duplex.
     int copy_serial = 0;
     ntc::DevBuf hold, hold2;        // copy_serial: records / offsets of a whole call parked in HBM
-    // Host-buffer encode: host_threads > 0 = that many host threads turn each chunk of ASCII reads into the 2-bit stream (host_pack.cpp) in
-    // page-locked staging, so 0.25 B per base cross PCIe and pack2bit_kernel is skipped; 0 (default) = the ASCII bytes are copied up and packed on
-    // the GPU.  Measured no faster than page-locked copies over Gen5 x16 at N = 1 and slower at N = 8 (profiles/r2/ab_host_pack.txt).
-    int host_threads = 0;
+    // Host threads of the host-buffer entry points (ntc_ctx_set_host_threads; host_pack.cpp).
+    //   PAGEABLE caller buffers (a Rust Vec, a numpy array) go through page-locked staging owned by the context, filled / emptied by the pool:
+    //   a pageable cudaMemcpy runs at 7.5 GB/s up and 14 GB/s down on the B200 boxes (encode 200 ms, decode 119 ms per 1.5 G bases against
+    //   32 + 31 ms from page-locked buffers; profiles/r2/pageable_probe.json).  Reads are packed to 2 bits per base on the way (the pool reads
+    //   them once either way), records / text / offsets are copied.  Page-locked caller buffers are copied by the DMA engines directly, as before.
+    //   host_threads: < 0 (default) = the above with auto_threads; 0 = never (the driver's pageable path); n > 0 = n threads, and the reads are
+    //   packed on the host for page-locked buffers too (measured no faster there: profiles/r2/ab_host_pack.txt).
+    int host_threads = -1;
+    int auto_threads = 0;
     ntc::HostPool* pool = nullptr;  // created on first use
-    void* h_pack[2] = {nullptr, nullptr};
-    size_t h_pack_cap[2] = {0, 0};
+    struct Pinned { void* p = nullptr; size_t cap = 0; };
+    Pinned h_in[2], h_out[2];       // per lane: staged input (packed reads + offsets, or records) and output (records / text + offsets)
+    cudaEvent_t ev_out[2] = {nullptr, nullptr};   // the lane's D2H into h_out is done
     void* colwork = nullptr;        // workspaces + pinned landing buffers of the GPU column codec, both directions (api_columns.inc)
 
     // optional per-kernel-class timing with CUDA events on the launching stream (bench.py roofline)

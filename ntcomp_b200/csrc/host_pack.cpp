@@ -79,6 +79,7 @@ HostPool::~HostPool() {
 }
 void HostPool::run(uint64_t n_items, const std::function<void(uint64_t)>& f) {
     if (n_items == 0) return;
+    if (n_items == 1 || n_ == 1) { for (uint64_t i = 0; i < n_items; i++) f(i); return; }   // nothing to share: nobody is woken
     Impl& p = *impl_;
     {
         std::lock_guard<std::mutex> lk(p.m);
