@@ -44,7 +44,7 @@ def one_case(rng, stats):
     os.environ["NTC_MAX_CHUNK_BASES"] = str(int(rng.choice([4096, 100000, 50331648])))
     os.environ["NTC_MAX_CHUNK_RECORDS"] = str(int(rng.choice([64, 5000, 4194304])))
     ctx = nt.Context(gpu, 0)
-    ctx.set_host_threads(int(rng.choice([0, 0, 3])))
+    ctx.set_host_threads(int(rng.choice([-1, -1, 0, 3])))                    # auto: pageable numpy buffers are staged by host threads
     src = [c for c in contigs if len(c) > 0 and not (c == ord("N")).any()]
     if not src:
         return
