@@ -139,3 +139,25 @@ def test_one_direction_contexts_and_pinned_buffers():
     _lib.check(L.ntc_encode_batch(full._h, p, off.ctypes.data_as(C.c_void_p), len(reads), out.ctypes.data_as(C.c_void_p), len(out), C.byref(n_rec), None))
     assert n_rec.value == len(rec) and (out[: len(rec)] == rec).all()
     L.ntc_pinned_free(p)
+    # every buffer page-locked (the DMA engines copy directly, many chunks) against every buffer pageable (staged by host threads)
+    import torch
+    os.environ["NTC_MAX_CHUNK_BASES"], os.environ["NTC_MAX_CHUNK_RECORDS"] = "4096", "64"
+    try:
+        small = nt.Context(idx, 0)
+    finally:
+        del os.environ["NTC_MAX_CHUNK_BASES"], os.environ["NTC_MAX_CHUNK_RECORDS"]
+    pb, po = torch.from_numpy(bases.copy()).pin_memory(), torch.from_numpy(off.astype(np.int64)).pin_memory()
+    pr, pro = torch.zeros(len(bases), dtype=torch.int64).pin_memory(), torch.zeros(len(off), dtype=torch.int64).pin_memory()
+    pt = torch.zeros(len(bases) + 24 * len(reads) + 64, dtype=torch.uint8).pin_memory()
+    n_bytes, n_seqs = C.c_uint64(0), C.c_uint64(0)
+    for threads in (-1, 0, 5):
+        small.set_host_threads(threads)
+        _lib.check(L.ntc_encode_batch(small._h, pb.data_ptr(), po.data_ptr(), len(reads), pr.data_ptr(), pr.numel(), C.byref(n_rec), pro.data_ptr()))
+        assert n_rec.value == len(rec) and (pr.numpy()[: len(rec)].view(np.uint64) == rec).all() and (pro.numpy().view(np.uint64) == roff).all()
+        _lib.check(L.ntc_decode_fasta(small._h, pr.data_ptr(), n_rec.value, 7, pt.data_ptr(), pt.numel(), C.byref(n_bytes), C.byref(n_seqs)))
+        assert bytes(pt.numpy()[: n_bytes.value]) == full.decode_fasta(rec, 7)[0] and n_seqs.value == len(reads)
+        rec_s, roff_s = small.encode_batch(bases, off)                  # pageable numpy buffers, same context
+        assert (rec_s == rec).all() and (roff_s == roff).all()
+        assert small.decode_fasta(rec_s, 7) == full.decode_fasta(rec, 7)
+        db, doff = small.decode_batch(rec_s)
+        assert (db == bases).all() and (doff == off).all()
