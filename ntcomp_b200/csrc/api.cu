@@ -1,6 +1,8 @@
 // api.cu -- C ABI of the hot path: context creation (index re-layout + upload), the stream-ordered
 // device pipelines, and the host-buffer entry points a Rust/cgo/ctypes caller binds.
 // There is no CPU fallback here: without a GPU every compute entry point returns NTC_ERR_CUDA.
+#include <sched.h>
+
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
@@ -642,7 +644,11 @@ int32_t ntc_ctx_set_host_threads(ntc_ctx* ctx, int32_t n_threads) {
     if (!ctx) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
     int n_dev = 1;
     cudaGetDeviceCount(&n_dev);
-    const int share = (int)std::thread::hardware_concurrency() / std::max(1, n_dev);   // this GPU's share of the host's threads
+    int cpus = (int)std::thread::hardware_concurrency();
+#if defined(__linux__)
+    { cpu_set_t set; if (sched_getaffinity(0, sizeof set, &set) == 0 && CPU_COUNT(&set) > 0) cpus = CPU_COUNT(&set); }   // the CPUs this process may run on
+#endif
+    const int share = cpus / std::max(1, n_dev);   // this GPU's share of them (processes that see one GPU each: set NTC_HOST_THREADS)
     ctx->auto_threads = share >= 2 ? std::min(share, 16) : 0;
     ctx->host_threads = n_threads < 0 ? -1 : std::min(n_threads, 64);
     const int want = ctx->host_threads > 0 ? ctx->host_threads : ctx->auto_threads;
