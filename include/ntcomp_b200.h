@@ -270,6 +270,29 @@ int32_t ntc_decode_device(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_re
                           uint64_t* d_counts, void* stream);
 int32_t ntc_ctx_status(ntc_ctx* ctx, void* stream);
 
+/* ntc_decode_device for callers that must not allocate.  No counterpart in the reference: it exists for hosts of this
+ * library, not for a function of ntcomp.  ntc_decode_device enlarges its workspaces with cudaFree + cudaMalloc whenever a
+ * batch is bigger than any before it.  That is unacceptable to a host which has given all of HBM to its own memory pool
+ * (the driver has nothing left to hand out, or the pool fragments), to a service that cannot afford the device-wide
+ * synchronisation and driver lock of an allocation inside a request, and to a sandboxed plugin that may launch kernels
+ * but not call the runtime's allocation functions.  This variant runs the same kernels and calls neither cudaMalloc nor
+ * cudaFree nor any routine that does: its workspaces are carved from one array that is part of the library image, so
+ * every GPU on which the library is loaded carries it (about 16 MiB) for the life of the process.
+ *   - Limit: n_records <= NTC_STATIC_MAX_RECORDS (one 65,536-read block of short reads is ~0.3 M records); more returns
+ *     NTC_ERR_CAPACITY with a message and enqueues nothing.  Cut a larger batch at sequence boundaries (just before a
+ *     record whose `first` flag is set) and advance first_seq_number by the sequences already decoded.
+ *   - The array is shared by every context and every stream of a GPU, and keeps what the last call left in it.  The call
+ *     clears the part that has to start at zero itself; the rest is overwritten before it is read.  Two calls whose GPU
+ *     work overlaps (different streams, or different contexts on one GPU) race on it: order them.
+ *   - The first call on each GPU looks the array's device address up (cudaGetSymbolAddress) and keeps it; make that first
+ *     call during set-up, before any stream capture is begun.
+ * Arguments, results, status reporting (ntc_ctx_status) and output bytes are those of ntc_decode_device. */
+#define NTC_STATIC_MAX_RECORDS 524288
+uint64_t ntc_decode_static_max_records(void); /* NTC_STATIC_MAX_RECORDS of the loaded library */
+int32_t ntc_decode_device_static(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_records, uint64_t first_seq_number,
+                                 int32_t fasta, uint8_t* d_out, uint64_t cap, uint64_t* d_seq_offsets, uint64_t cap_seqs,
+                                 uint64_t* d_counts, void* stream);
+
 /* number of kernels this library launched on ctx since creation (bench.py's gpu_launches) */
 uint64_t ntc_ctx_launch_count(const ntc_ctx* ctx);
 

@@ -61,6 +61,8 @@ SIGNATURES = {
     "ntc_decode_columns_fasta": (_i32, [_vp, _vp, _u64, _vp, _u64, _u64, _i32, _vp, _vp, _vp, _vp]),
     "ntc_encode_device": (_i32, [_vp, _vp, _vp, _u64, _u64, _vp, _u64, _vp, _vp, _vp]),
     "ntc_decode_device": (_i32, [_vp, _vp, _u64, _u64, _i32, _vp, _u64, _vp, _u64, _vp, _vp]),
+    "ntc_decode_device_static": (_i32, [_vp, _vp, _u64, _u64, _i32, _vp, _u64, _vp, _u64, _vp, _vp]),
+    "ntc_decode_static_max_records": (_u64, []),
     "ntc_ctx_status": (_i32, [_vp, _vp]),
     "ntc_ctx_launch_count": (_u64, [_vp]),
     "ntc_ctx_set_profiling": (_i32, [_vp, _i32]),

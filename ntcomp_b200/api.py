@@ -337,6 +337,16 @@ class Context:
         check(_lib.lib().ntc_decode_device(self._h, d_records, n_records, first_seq_number, int(fasta), d_out, cap, d_seq_offsets, cap_seqs,
                                            d_counts, stream))
 
+    def decode_device_static(self, d_records, n_records, first_seq_number, fasta, d_out, cap, d_seq_offsets, cap_seqs, d_counts, stream=0):
+        """decode_device on the library's built-in scratch array: no cudaMalloc / cudaFree inside the call, at most
+        static_max_records() records per call, calls on one GPU must not overlap (include/ntcomp_b200.h)."""
+        check(_lib.lib().ntc_decode_device_static(self._h, d_records, n_records, first_seq_number, int(fasta), d_out, cap, d_seq_offsets,
+                                                  cap_seqs, d_counts, stream))
+
+    @staticmethod
+    def static_max_records():
+        return int(_lib.lib().ntc_decode_static_max_records())
+
     def status(self, stream=0):
         check(_lib.lib().ntc_ctx_status(self._h, stream))
 

@@ -8,6 +8,8 @@
 #include <cstdio>
 #include <cstring>
 #include <exception>
+#include <mutex>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -793,6 +795,95 @@ extern "C" int32_t ntc_l2_random_bench(ntc_ctx* ctx, uint64_t buffer_bytes, uint
     release(&buf);
     NTC_CUDA_TRY(cudaGetLastError());
     *gsectors_per_s = (double)n_blocks * 256.0 * loads_per_thread / (best * 1e-3) / 1e9;
+    return NTC_OK;
+}
+
+// ---------------- decode without any allocation: ntc_decode_device_static ------------------------------------------------
+// ntc_decode_device keeps its scan workspaces in grow-only cudaMalloc'ed buffers, so a batch larger than any seen before
+// makes it call cudaFree + cudaMalloc.  Some hosts of this library cannot have that happen inside a call:
+//   * a host that handed the whole of HBM to its own pool (a database or an inference server with a caching allocator):
+//     a cudaMalloc behind its back fails or fragments the pool;
+//   * a latency-bound service: cudaMalloc / cudaFree synchronise the device and take a driver lock;
+//   * a sandboxed plugin whose policy allows launches but not the allocation calls of the runtime.
+// For them the same kernels run here on scratch that lives in the library image: one file-scope __device__ array, sized
+// for kStaticMaxRecords records.  Every GPU that loads the library carries the array (about 16 MiB) until the process ends.
+//
+// In host code `g_static_scratch` is only a handle for the symbol -- NOT a device address; handing it to a kernel would
+// fault (or scribble over host memory on a system where the GPU can reach it).  The address is looked up per device with
+// cudaGetSymbolAddress while that device is current, and cached.
+namespace {
+constexpr uint64_t kStaticMaxRecords = NTC_STATIC_MAX_RECORDS;
+constexpr size_t static_round(size_t b) { return (b + 255) / 256 * 256; }
+constexpr size_t kStaticArrayBytes = static_round((kStaticMaxRecords + 1) * 8);     // base_off, seq_idx, seq_first, seq_endkey
+constexpr size_t kStaticTileBytes = static_round(((kStaticMaxRecords + 1 + kScanTile - 1) / kScanTile) * sizeof(Pair64));
+constexpr size_t kStaticSmallBytes = 256;                                           // scan totals (2 x u64)
+constexpr size_t kStaticScratchBytes = 4 * kStaticArrayBytes + kStaticTileBytes + kStaticSmallBytes;
+constexpr int kStaticMaxDevices = 64;
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+std::mutex g_static_mu;
+unsigned char* g_static_addr[kStaticMaxDevices] = {nullptr};
+
+// device address of the array on `device`, which must be the current device; looked up once per device
+int32_t static_scratch_address(int device, unsigned char** out) {
+    if (device < 0 || device >= kStaticMaxDevices) { set_error("ntc_decode_device_static: device ordinal beyond 63"); return NTC_ERR_UNSUPPORTED; }
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_addr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) {
+            set_error(std::string("cudaGetSymbolAddress(static decode scratch): ") + cudaGetErrorString(e));
+            return NTC_ERR_CUDA;
+        }
+        g_static_addr[device] = (unsigned char*)p;
+    }
+    *out = g_static_addr[device];
+    return NTC_OK;
+}
+}  // namespace
+
+extern "C" uint64_t ntc_decode_static_max_records(void) { return kStaticMaxRecords; }
+
+extern "C" int32_t ntc_decode_device_static(ntc_ctx* ctx, const uint64_t* d_records, uint64_t n_records, uint64_t first_seq_number,
+                                            int32_t fasta, uint8_t* d_out, uint64_t cap, uint64_t* d_seq_offsets, uint64_t cap_seqs,
+                                            uint64_t* d_counts, void* stream) {
+    if (!ctx || (!d_records && n_records) || !d_counts) { set_error("null argument"); return NTC_ERR_INVALID_ARG; }
+    if (fasta && first_seq_number == 0) { set_error("first_seq_number is 1-based"); return NTC_ERR_INVALID_ARG; }
+    if (n_records > kStaticMaxRecords) {
+        set_error("ntc_decode_device_static: " + std::to_string(n_records) + " records exceed the static scratch's limit of " +
+                  std::to_string(kStaticMaxRecords) + " per call (split the batch at a `first` record, or use ntc_decode_device)");
+        return NTC_ERR_CAPACITY;
+    }
+    if (n_records && !(ctx->uses & NTC_USE_DECODE)) { set_error("this context was created without NTC_USE_DECODE (no jump table in HBM)"); return NTC_ERR_UNSUPPORTED; }
+    NTC_CUDA_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* base = nullptr;
+    if (int32_t rc = static_scratch_address(ctx->device, &base)) return rc;
+    if (n_records == 0) {
+        NTC_CUDA_TRY(cudaMemsetAsync(d_counts, 0, 16, st));
+        if (d_seq_offsets) NTC_CUDA_TRY(cudaMemsetAsync(d_seq_offsets, 0, 8, st));
+        return NTC_OK;
+    }
+    uint64_t* base_off = (uint64_t*)base;
+    uint64_t* seq_idx = (uint64_t*)(base + kStaticArrayBytes);
+    uint64_t* seq_first = (uint64_t*)(base + 2 * kStaticArrayBytes);
+    uint64_t* seq_endkey = (uint64_t*)(base + 3 * kStaticArrayBytes);
+    Pair64* tiles = (Pair64*)(base + 4 * kStaticArrayBytes);
+    uint64_t* totals = (uint64_t*)(base + 4 * kStaticArrayBytes + kStaticTileBytes);
+    // The array still holds the previous call's values.  Every word the kernels read is written earlier in the same call
+    // (scan outputs for 0..n, tile sums for this call's tiles, seq_first / seq_endkey for this call's sequences); the grand
+    // totals are the one place where a stale value could be mistaken for a result, so they are cleared.
+    NTC_CUDA_TRY(cudaMemsetAsync(totals, 0, kStaticSmallBytes, st));
+    const int n_scan = exclusive_scan_pairs(RecordLoad{d_records}, n_records, tiles, nullptr, totals, base_off, seq_idx, st,
+                                            SeqFirstPost{seq_first});
+    seq_layout_kernel<<<blocks_for(n_records + 1, 256), 256, 0, st>>>(base_off, seq_first, totals, n_records, seq_endkey, d_seq_offsets,
+                                                                      cap_seqs, 0, first_seq_number, fasta, cap, d_counts, ctx->d_status);
+    walk_kernel<<<blocks_for(n_records, kWalkThreads), kWalkThreads, 0, st>>>(ctx->dix, d_records, n_records, base_off, seq_idx, seq_endkey,
+                                                                              totals, first_seq_number, fasta, d_out, cap, d_counts,
+                                                                              ctx->d_status);
+    NTC_CUDA_TRY(cudaGetLastError());
+    ctx->launches += n_scan + 2;
     return NTC_OK;
 }
 

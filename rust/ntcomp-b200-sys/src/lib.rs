@@ -143,6 +143,11 @@ extern "C" {
                              d_out: *mut u8, cap: u64, d_seq_offsets: *mut u64, cap_seqs: u64, d_counts: *mut u64,
                              stream: *mut c_void) -> i32;
     pub fn ntc_ctx_status(ctx: *mut ntc_ctx, stream: *mut c_void) -> i32;
+    // allocation-free decode on the library's static scratch (no counterpart in the reference; see the header)
+    pub fn ntc_decode_static_max_records() -> u64;
+    pub fn ntc_decode_device_static(ctx: *mut ntc_ctx, d_records: *const u64, n_records: u64, first_seq_number: u64, fasta: i32,
+                                    d_out: *mut u8, cap: u64, d_seq_offsets: *mut u64, cap_seqs: u64, d_counts: *mut u64,
+                                    stream: *mut c_void) -> i32;
 
     // ---- measurement support ----
     pub fn ntc_ctx_launch_count(ctx: *const ntc_ctx) -> u64;
