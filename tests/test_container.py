@@ -374,6 +374,17 @@ def test_block_disassemble_and_assemble_round_trip_on_the_host():
     assert b"".join(nt.sub_block_assemble(blk, q, words) for q in range(4)) == want
     with pytest.raises(nt.NtcError):
         nt.sub_block_assemble(blk, 4, words)
+    # a missing word pointer for a non-empty column is an argument error, not a crash; a short buffer is a capacity error
+    import ctypes as C
+    from ntcomp_b200 import _lib
+    out = np.zeros(len(want) + 1024, dtype=np.uint8)
+    nb = C.c_uint64(7)
+    L = _lib.lib()
+    assert L.ntc_block_assemble(C.byref(blk), None, out.ctypes.data_as(C.c_void_p), len(out), C.byref(nb)) == 1 and nb.value == 0
+    assert L.ntc_block_assemble(C.byref(blk), words.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), len(want) - 1, C.byref(nb)) == 3
+    assert nb.value == 0
+    assert L.ntc_block_assemble(C.byref(blk), words.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), len(out), C.byref(nb)) == 0
+    assert bytes(out[: nb.value]) == want
 
 
 @pytest.mark.gpu
