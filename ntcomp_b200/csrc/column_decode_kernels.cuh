@@ -73,6 +73,8 @@ NTC_HD uint32_t cw_run(const CodeParams& p, const uint64_t* __restrict__ words, 
             }
             const uint64_t term = pos + zeros;
             if (!found || term >= total) { exit_state = 0; break; }   // zero padding after the last code
+            if (term + 1 + b > total) { exit_state = 0; break; }       // terminator found but the remainder bits are cut off: not a
+                                                                       // code (the host reader rejects the column too, container.cpp)
             const uint64_t rem = b ? cw_window(words, n_words, term + 1) >> (64 - b) : 0;
             sink(count, (zeros << b) | rem);
             count++;

@@ -509,3 +509,75 @@ def test_fused_columns_encode_and_decode_match_oracle_blocks():
     sb = b"".join(o.decode(b, fast=True)[0].tobytes() for _ in range(1))
     sa = o.decode(a, fast=True)[0].tobytes()
     assert n_seqs == 3 and text == b">seq.1\n" + sb + b"\n>seq.2\n" + sa + b"\n>seq.3\n" + sb + b"\n"
+
+
+def _blobs_with_crafted_len_column(b=3):
+    """One block whose match-length column (Rice, sub-block 1) is written by hand: (records, intact blob, [blobs whose LAST
+    Rice code has its terminating one bit but not all of its b remainder bits])."""
+    lens = [40, 13, 150, 91, 12, 77]
+    rec = [(1000 + i) | (L << 32) | (int(i == 0) << 56) for i, L in enumerate(lens)]
+    rec += [0b1101 | (((0 + 2) | (2 << 2)) << 56)]                                          # one literal: every column non-empty
+    rec = np.array(rec, dtype=np.uint64)
+    rc, blob = block_write(rec, 1)
+    assert rc == 0
+    blk, words, used = nt.block_disassemble(blob)
+    assert used == len(blob) and blk.col[1].n_values == len(lens)
+    code = lambda v: "0" * (v >> b) + "1" + format(v & ((1 << b) - 1), "0%db" % b)
+
+    def with_bits(bits):
+        assert len(bits) % 64 == 0
+        col1 = np.packbits(np.array([int(c) for c in bits], dtype=np.uint8)).view(np.uint64)   # stream bytes in order = the file's words
+        parts = [words[int(blk.col[q].word_offset): int(blk.col[q].word_offset + blk.col[q].n_words)] for q in range(4)]
+        parts[1] = col1
+        nb = nt.CodedBlock.from_buffer_copy(blk)
+        pos = 0
+        for q in range(4):
+            nb.col[q].word_offset, nb.col[q].n_words = pos, len(parts[q])
+            pos += len(parts[q])
+        nb.col[1].param = b
+        return nt.block_assemble(nb, np.concatenate(parts))
+
+    whole = "".join(code(v) for v in lens)
+    good = with_bits(whole + "0" * (-len(whole) % 64))
+    head = "".join(code(v) for v in lens[:-1])
+    bad = []
+    for missing in range(1, b + 1):                                                         # 1 .. b remainder bits cut off
+        tail_zeros = -(len(head) + 1 + (b - missing)) % 64
+        if tail_zeros > (lens[-1] >> b) + 64:
+            continue
+        bits = head + "0" * tail_zeros + "1" + "0" * (b - missing)
+        bad.append(with_bits(bits))
+    return rec, good, bad
+
+
+def test_truncated_final_rice_code_is_rejected_by_the_host_reader():
+    """a length column whose last code ends in the middle of its remainder bits is not a column (dsi-bitstream's
+    reader runs out of words, src/decode.rs:51-62).  The hand-written intact column decodes to the block's records."""
+    rec, good, bad = _blobs_with_crafted_len_column()
+    rc, got, used = block_read(good)
+    assert rc == 0 and used == len(good) and (got == rec).all()
+    assert len(bad) == 3
+    for blob in bad:
+        assert block_read(blob)[0] == 7
+
+
+@pytest.mark.gpu
+def test_truncated_final_rice_code_same_verdict_on_gpu_and_host():
+    """The GPU column decoder used to count a Rice code whose remainder bits lie beyond the stream (read as zero padding), so
+    ntc_block_read_gpu accepted what the host reader refuses.  Same verdict now, and the intact column gives the same records."""
+    rng = np.random.default_rng(3)
+    index = nt.Index.build([helpers.random_seq(rng, 5000)], 31)
+    ctx = nt.Context(index, 0)
+
+    def gpu_read(blob):
+        buf = np.frombuffer(blob, dtype=np.uint8)
+        out = np.zeros(8 * len(buf) + 1024, dtype=np.uint64)
+        n, used = C.c_uint64(0), C.c_uint64(0)
+        rc = _lib.lib().ntc_block_read_gpu(ctx._h, _ptr(buf), len(buf), _ptr(out), len(out), C.byref(n), C.byref(used), 0)
+        return rc, out[: n.value].copy(), used.value
+
+    rec, good, bad = _blobs_with_crafted_len_column()
+    rc, got, used = gpu_read(good)
+    assert rc == 0 and used == len(good) and (got == rec).all()
+    for blob in bad:
+        assert block_read(blob)[0] == 7 and gpu_read(blob)[0] == 7
