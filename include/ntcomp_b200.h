@@ -237,13 +237,20 @@ int32_t ntc_column_code(const uint64_t* values, uint64_t n, int32_t rice, uint64
  * (<= 0: all cores), and an in-order writer.  Paths may be "-" (stdin / stdout); fastX input may be
  * gzip-compressed.  encoded.dat layout: src/lib.rs:29-92,232-252.
  * encode stats[6]: reads, bases, records, bytes written, blocks written, blocks dropped (Q4);
- * decode stats[6]: sequences, FASTA bytes written, records, bytes read, blocks, 0.  stats may be NULL. */
+ * decode stats[6]: sequences, FASTA bytes written, records, bytes read, blocks, 0.  stats may be NULL.
+ * A damaged encoded.dat: ntc_decode_file writes every block that precedes the first damaged one, like the reference's
+ * `while let Ok(..)` loop (src/main.rs:203), and then -- unlike the reference, which stops silently -- returns the error. */
 int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_path, int32_t n_threads, uint64_t* stats);
 int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path, int32_t n_threads, uint64_t* stats);
 /* Page-locked host memory for the buffers handed to the host-buffer entry points: copies to and from it run at full
  * PCIe rate without a staging pass (the file pipeline fills its read batches in such buffers).  Needs a GPU. */
 int32_t ntc_pinned_alloc(uint64_t bytes, void** out);
 void ntc_pinned_free(void* p);
+/* Makes ctx's GPU the calling thread's current CUDA device.  Every entry point that takes a ctx does this itself; a helper
+ * thread that only calls ntc_pinned_alloc / ntc_pinned_free has no ctx argument, and a new thread's current device is GPU 0,
+ * so without this call its first allocation creates a CUDA context on GPU 0 (memory and start-up time there, failure where
+ * GPU 0 is exclusive or hidden).  No counterpart in the reference (which has no devices). */
+int32_t ntc_ctx_bind_thread(ntc_ctx* ctx);
 
 /* fastX file (FASTA / FASTQ, plain or gzip) -> the normalised sequences (needletail normalize(true) for what can reach the
  * encoder, src/main.rs:158-163), parsed like the encode pipeline does: one reader thread cutting at record boundaries,

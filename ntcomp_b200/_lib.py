@@ -37,6 +37,7 @@ SIGNATURES = {
     "ntc_ctx_create_for": (_i32, [_i32, _vp, _u32, _pp]),
     "ntc_pinned_alloc": (_i32, [_u64, _pp]),
     "ntc_pinned_free": (None, [_vp]),
+    "ntc_ctx_bind_thread": (_i32, [_vp]),
     "ntc_ctx_destroy": (None, [_vp]),
     "ntc_ctx_index_bytes": (None, [_vp, _vp]),
     "ntc_ctx_layout_read": (_i32, [_vp, _i32, _vp, _u64, _vp]),

@@ -413,8 +413,13 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
     std::exception_ptr build_err;
     if (host_layouts) {
         std::thread lcs_thread;
+        std::exception_ptr lcs_err;
         try {
-            if (uses & NTC_USE_ENCODE) lcs_thread = std::thread([&]() { build_lcs_words(*idx, &lcs); t_lcs = since(); });   // serial stack pass
+            if (uses & NTC_USE_ENCODE)                                                                                          // serial stack pass
+                lcs_thread = std::thread([&]() {
+                    try { build_lcs_words(*idx, &lcs); t_lcs = since(); }
+                    catch (...) { lcs_err = std::current_exception(); }   // an exception leaving a thread is std::terminate
+                });
             if (uses & NTC_USE_ENCODE) {
                 build_rank_blocks(*idx, &rank, std::max(1, threads - 1), rank_nodes);
                 if (use_pfx) build_prefix_table(rank, idx->n, &pfx, c_start, rank_nodes);
@@ -423,11 +428,12 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
             if (uses & NTC_USE_DECODE) { build_jump_table(*idx, &jump, std::max(1, threads - 1)); t_jump = since(); }
         } catch (...) { build_err = std::current_exception(); }
         if (lcs_thread.joinable()) lcs_thread.join();
+        if (lcs_err && !build_err) build_err = lcs_err;
     } else {
         for (int c = 0; c < 4; c++) c_start[c] = (uint32_t)idx->C[c];   // interval start after the single base c = rank_c(0) + C[c]
     }
     cuda_up.join();
-    if (build_err) { set_error("out of host memory while deriving the index layouts"); return NTC_ERR_INVALID_ARG; }
+    if (build_err) { set_error("out of host memory while deriving the index layouts"); return NTC_ERR_IO; }   // as container.cpp reports bad_alloc
     cudaError_t e = e_init;
     if (e != cudaSuccess || n_dev == 0) {
         set_error(std::string("no CUDA device available (this library has no CPU fallback): ") + cudaGetErrorString(e));
@@ -618,6 +624,12 @@ int32_t ntc_pinned_alloc(uint64_t bytes, void** out) {
     return NTC_OK;
 }
 void ntc_pinned_free(void* p) { if (p) cudaFreeHost(p); }
+
+int32_t ntc_ctx_bind_thread(ntc_ctx* ctx) {
+    if (!ctx) { set_error("null ctx"); return NTC_ERR_INVALID_ARG; }
+    NTC_CUDA_TRY(cudaSetDevice(ctx->device));
+    return NTC_OK;
+}
 
 void ntc_ctx_index_bytes(const ntc_ctx* ctx, uint64_t out[3]) { memcpy(out, ctx->index_bytes, 24); }
 

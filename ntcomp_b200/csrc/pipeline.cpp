@@ -585,6 +585,9 @@ int32_t ntc_encode_file(ntc_ctx* ctx, const char* fastx_path, const char* out_pa
     // stage 2: parsed pieces, in order -> batches of whole 65,536-read blocks.  This thread only decides where every piece
     // goes; the bytes are moved by copy tasks on the pool, straight into the page-locked buffer the GPU stage uploads from.
     std::thread t_batch([&] { stage_guard(&fatal, [&] {
+        // this thread allocates the page-locked batch buffers: without its own current device the first cudaHostAlloc would
+        // bring up a primary context on GPU 0, whatever GPU ctx lives on
+        ntc_ctx_bind_thread(ctx);
         uint64_t made = 0;
         auto fresh = [&]() -> BatchPtr {
             BatchPtr n;
@@ -867,15 +870,26 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
                 if (brc[j] != NTC_OK) bmsg[j] = ntc_last_error();
                 words[j].resize(brc[j] == NTC_OK ? nw : 0);
             });
-            uint64_t at = 0;
+            // A block that cannot be unpacked ends the stream: the group keeps the blocks before it, which are still decoded
+            // and written (the reference's `while let Ok(..)` loop writes every block before the first bad one, src/main.rs:203).
+            size_t n_good = nb;
             for (size_t j = 0; j < nb; j++) {
-                if (brc[j] != NTC_OK && cb.rc == NTC_OK) { cb.rc = brc[j] == NTC_ERR_CAPACITY ? NTC_ERR_IO : brc[j]; cb.msg = bmsg[j]; }
+                if (brc[j] == NTC_OK) continue;
+                cb.rc = brc[j] == NTC_ERR_CAPACITY ? NTC_ERR_IO : brc[j];
+                cb.msg = bmsg[j];
+                n_good = j;
+                eof = true;
+                break;
+            }
+            uint64_t at = 0;
+            for (size_t j = 0; j < n_good; j++) {
                 for (int q = 0; q < 4; q++) cb.blocks[j].col[q].word_offset += at;
                 at += words[j].size();
                 st[3] += raw[j].size();
             }
+            cb.blocks.resize(n_good);
             cb.words.reserve(at);
-            for (size_t j = 0; j < nb; j++) cb.words.insert(cb.words.end(), words[j].begin(), words[j].end());
+            for (size_t j = 0; j < n_good; j++) cb.words.insert(cb.words.end(), words[j].begin(), words[j].end());
             t_stage[0] += now_s() - t0;
             if (!unpacked.push(std::move(cb))) return;
         }
@@ -897,25 +911,44 @@ int32_t ntc_decode_file(ntc_ctx* ctx, const char* in_path, const char* out_path,
     // stage 2 (this thread): integer decoders + zip + decode_sequence + FASTA text on the GPU
     ColBatch cb;
     uint64_t pushed = 0;
-    while (unpacked.pop(&cb)) {
-        if (cb.rc != NTC_OK) { rc = cb.rc; msg = cb.msg; break; }
-        st[4] += cb.blocks.size();
-        // the text of call i lives in a pinned buffer that call i + 2 reuses: wait until the writer is done with it
-        if (pushed >= 2) { std::unique_lock<std::mutex> lk(wm); wcv.wait(lk, [&] { return writer_gone || written + 2 > pushed; }); }
+    // one call of the fused decoder over blocks [b, b + n_b) of the current group; false = stop (rc / msg say why, or the writer is gone)
+    auto decode_group = [&](const ntc_coded_block* b, uint64_t n_b) -> bool {
         const double t0 = now_s();
         const uint8_t* text = nullptr;
         uint64_t nb = 0, ns = 0, nr = 0;
-        rc = ntc_decode_columns_fasta(ctx, cb.blocks.data(), cb.blocks.size(), cb.words.data(), cb.words.size(), st[0] + 1,
+        rc = ntc_decode_columns_fasta(ctx, b, n_b, cb.words.data(), cb.words.size(), st[0] + 1,
                                       NTC_BLOCK_FULL_LAST_LITERAL_WORD, &text, &nb, &ns, &nr);   // Q5: the reference panics on 1 block in 31
         t_stage[1] += now_s() - t0;
-        if (rc != NTC_OK) { msg = ntc_last_error(); break; }
+        if (rc != NTC_OK) { msg = ntc_last_error(); return false; }
         st[0] += ns;
         st[1] += nb;
         st[2] += nr;
+        st[4] += n_b;
         if (nb) {
-            if (!texts.push(TextRef{text, nb})) break;
+            if (!texts.push(TextRef{text, nb})) return false;
             pushed++;
         }
+        return true;
+    };
+    while (unpacked.pop(&cb)) {
+        // the text of call i lives in a pinned buffer that call i + 2 reuses: wait until the writer is done with it
+        if (pushed >= 2) { std::unique_lock<std::mutex> lk(wm); wcv.wait(lk, [&] { return writer_gone || written + 2 > pushed; }); }
+        if (!cb.blocks.empty() && !decode_group(cb.blocks.data(), cb.blocks.size())) {
+            if (rc == NTC_OK || cb.blocks.size() == 1) break;
+            // A damaged block somewhere in the group.  Like the reference (src/main.rs:203), everything before the first bad
+            // block is still written: go through the group block by block.  (A deliberate difference remains: the reference
+            // then stops silently with exit status 0, this call returns the error.)  The failed call consumed one of the two
+            // text buffers out of turn, so each call here waits for the writer to be done with everything pushed so far.
+            const int32_t group_rc = rc;
+            const std::string group_msg = msg;
+            for (size_t j = 0; j < cb.blocks.size(); j++) {
+                { std::unique_lock<std::mutex> lk(wm); wcv.wait(lk, [&] { return writer_gone || written >= pushed; }); }
+                if (!decode_group(&cb.blocks[j], 1)) break;
+            }
+            if (rc == NTC_OK) { rc = group_rc; msg = group_msg; }
+            break;
+        }
+        if (cb.rc != NTC_OK) { rc = cb.rc; msg = cb.msg; break; }
     }
     unpacked.close();
     texts.finish();

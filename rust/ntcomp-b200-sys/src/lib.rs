@@ -128,6 +128,7 @@ extern "C" {
     pub fn ntc_decode_file(ctx: *mut ntc_ctx, in_path: *const c_char, out_path: *const c_char, n_threads: i32, stats: *mut u64) -> i32;
     pub fn ntc_pinned_alloc(bytes: u64, out: *mut *mut c_void) -> i32;
     pub fn ntc_pinned_free(p: *mut c_void);
+    pub fn ntc_ctx_bind_thread(ctx: *mut ntc_ctx) -> i32;
     pub fn ntc_fastx_load(path: *const c_char, n_threads: i32, bases: *mut *mut u8, offsets: *mut *mut u64, n_reads: *mut u64,
                           n_bases: *mut u64) -> i32;
     pub fn ntc_free(p: *mut c_void);

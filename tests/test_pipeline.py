@@ -5,6 +5,7 @@ oracle's record stream block by block, FASTA text is the writer loop's."""
 import gzip
 import os
 import subprocess
+import sys
 
 import numpy as np
 import pytest
@@ -204,3 +205,91 @@ def test_cli_round_trip_and_block_parity(tmp_path, genome_and_reads, monkeypatch
     with pytest.raises(nt.NtcError) as e:
         ctx.encode_file(bad, tmp_path / "bad.dat")
     assert e.value.code == 5
+
+
+_SECOND_GPU_SCRIPT = r"""
+import ctypes as C, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+import helpers, ntcomp_b200 as nt
+cu = C.CDLL("libcuda.so.1")
+def active(dev):
+    d, flags, act = C.c_int(), C.c_uint(), C.c_int()
+    assert cu.cuInit(0) == 0 and cu.cuDeviceGet(C.byref(d), dev) == 0
+    assert cu.cuDevicePrimaryCtxGetState(d, C.byref(flags), C.byref(act)) == 0
+    return act.value
+rng = np.random.default_rng(5)
+contigs = [helpers.random_seq(rng, 30000)]
+reads = helpers.sample_reads(rng, contigs, 3000, lengths=[150, 150, 400], error_rates=[0, 0.01], k=31)
+tmp = sys.argv[2]
+with open(tmp + "/r.fa", "wb") as f:
+    f.write(helpers.fasta_text(reads, 1))
+ctx = nt.Context(nt.Index.build(contigs, 31, True), 1)
+assert active(0) == 0 and active(1) == 1
+ctx.encode_file(tmp + "/r.fa", tmp + "/enc.dat", 4)
+assert active(0) == 0, "ntc_encode_file on GPU 1 created a CUDA context on GPU 0"
+ctx.decode_file(tmp + "/enc.dat", tmp + "/dec.fa", 4)
+assert active(0) == 0, "ntc_decode_file on GPU 1 created a CUDA context on GPU 0"
+assert open(tmp + "/dec.fa", "rb").read() == helpers.fasta_text(reads, 1)
+print("SECOND_GPU_OK")
+"""
+
+
+@pytest.mark.gpu
+def test_file_pipeline_on_second_gpu_leaves_gpu0_alone(tmp_path):
+    """A context on GPU 1 must not bring up a CUDA context on GPU 0: the pipeline's batch-assembler thread allocates
+    page-locked buffers and a new thread's current device is 0 (ntc_ctx_bind_thread).  Checked from a fresh process (this
+    one may already hold GPU 0 through torch) with the driver's own cuDevicePrimaryCtxGetState.  Needs two GPUs."""
+    import torch
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    r = subprocess.run([sys.executable, "-c", _SECOND_GPU_SCRIPT, ROOT, str(tmp_path)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "SECOND_GPU_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.gpu
+def test_decode_file_writes_the_blocks_before_a_damaged_one(tmp_path, genome_and_reads, monkeypatch):
+    """src/main.rs:203 (`while let Ok(..)`) writes every block decoded before the first bad one.  ntc_decode_file
+    must do the same whatever its internal grouping of blocks is (and then report the error, a deliberate difference).
+    Third block of three damaged (a) in its gzip bytes -- caught while unpacking -- and (b) in a header count that only the
+    column decoder on the GPU can see."""
+    import struct
+    contigs, reads = genome_and_reads
+    reads = (reads * 190)[: 2 * 65536 + 777]
+    fq = tmp_path / "reads.fa"
+    fq.write_bytes(helpers.fasta_text(reads, 1))
+    ctx = nt.Context(nt.Index.build(contigs, 31, True), 0)
+    enc = tmp_path / "enc.dat"
+    st = ctx.encode_file(fq, enc, 4)
+    assert st["blocks"] == 3 and st["dropped_blocks"] == 0
+    data = enc.read_bytes()
+    starts, pos = [], 32
+    while pos < len(data):
+        starts.append(pos)
+        for _ in range(4):
+            pos += 32 + struct.unpack_from("<I", data, pos)[0]
+    assert len(starts) == 3 and pos == len(data)
+    want = helpers.fasta_text(reads[: 2 * 65536], 1)
+    b3 = starts[2]
+    bs0 = struct.unpack_from("<I", data, b3)[0]
+    gz_damage = bytearray(data)
+    for i in range(40, 60):                                            # inside the first column's deflate stream
+        gz_damage[b3 + 32 + i] ^= 0xFF
+    count_damage = bytearray(data)                                     # one more match length announced than the stream holds
+    n_len = struct.unpack_from("<I", data, b3 + 32 + bs0 + 8)[0]
+    struct.pack_into("<I", count_damage, b3 + 32 + bs0 + 8, n_len + 1)
+    for name, blob in (("gzip", gz_damage), ("count", count_damage)):
+        for group in ("1", "2", None):
+            if group is None:
+                monkeypatch.delenv("NTC_PIPELINE_BATCH_BLOCKS", raising=False)
+            else:
+                monkeypatch.setenv("NTC_PIPELINE_BATCH_BLOCKS", group)
+            bad, out = tmp_path / "bad.dat", tmp_path / "out.fa"
+            bad.write_bytes(bytes(blob))
+            with pytest.raises(nt.NtcError):
+                ctx.decode_file(bad, out, 4)
+            assert out.read_bytes() == want, (name, group)
+    monkeypatch.delenv("NTC_PIPELINE_BATCH_BLOCKS", raising=False)
+    ctx.decode_file(enc, tmp_path / "ok.fa", 4)                        # the context is still usable after the failures
+    assert (tmp_path / "ok.fa").read_bytes() == helpers.fasta_text(reads, 1)
+    ctx.close()
