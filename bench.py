@@ -263,9 +263,10 @@ def free_host_cache(torch):
         pass
 
 
-def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap=None, want_l2=True, want_columns=False):
+def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap=None, want_l2=True, want_columns=False, light=False):
     """One config on this rank's shard [lo, lo + n_reads): device-resident timing (CUDA events on the launching
-    stream, barrier + synchronize on both sides, max over ranks) and the end-to-end leg through the host-buffer C ABI."""
+    stream, barrier + synchronize on both sides, max over ranks) and the end-to-end leg through the host-buffer C ABI.
+    light: a secondary config on the N = 1 line -- no host-builder comparison, no pageable-buffer leg."""
     torch = R.torch
     import ctypes as C
     import ntcomp_b200 as nt
@@ -290,7 +291,7 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
         out["index_build"] = {"impl": "ntc_index_build_gpu", "wall_ms": (time.time() - tb) * 1e3, "device_ms": bstats["device_ms"],
                               "upload_ms": bstats["upload_ms"], "n_sets": index.n_sets, "kmer_occurrences": bstats["occurrences"],
                               "radix_passes": bstats["radix_passes"], "launches": bstats["launches"]}
-        if world == 1 and args.cpu_budget > 0:
+        if world == 1 and args.cpu_budget > 0 and not light:
             tb = time.time()
             host = nt.Index.build([g], cfg["k"])
             host_s = time.time() - tb
@@ -445,7 +446,7 @@ def measure(R, cfg, lo, n_reads, steps, warm, args, want_e2e=True, e2e_reads_cap
                "encode_ms_per_step": 1e3 * split[0] / e2e_steps, "decode_ms_per_step": 1e3 * split[1] / e2e_steps,
                "pcie_h2d_gbs": pcie[0], "pcie_d2h_gbs": pcie[1],   # per GPU, all ranks copying at once (min over ranks)
                "pcie_floor_ms_per_step": (h2d / pcie[0] + d2h / pcie[1]) / 1e6 if pcie[0] else None}
-        if world == 1:
+        if world == 1 and not light:
             # the same two calls from PAGEABLE buffers (what a Rust Vec or a numpy array is): the context stages them through its own page-locked
             # buffers with host threads (ntc_ctx_set_host_threads, default auto); reported beside the contract's page-locked figure, not instead of it
             ctx.set_host_threads(-1)
@@ -539,6 +540,27 @@ def summarize_extra(m, steps, l2_gsect, note):
             "e2e": m["e2e"], "index_bytes": m["index_bytes"], "clocks": m["clocks"], "gpu_launches": m["gpu_launches"]}
 
 
+def cpu_baseline_of(m, n_reads, read_len, budget_s):
+    """literal oracle on one thread (the reference is single-threaded) over the first reads of the workload, for about budget_s
+    seconds; its record stream is compared with the GPU's for the same reads"""
+    from oracle import binding as ob
+    index = m["index"]
+    oracle = ob.OracleIndex.from_arrays(index.k, index.n_sets, index.rows(), index.lcs())
+    h_bases, h_off = m["h_sample"]
+    n_s = min(n_reads, 1 << 15)
+    sb = h_bases[: n_s * read_len].numpy()
+    so = h_off[: n_s + 1].numpy().astype(np.uint64)
+    r = time_oracle(oracle, sb, so, 1, budget_s, keep_records=True)
+    n_chk = int(m["d_roff"][r["reads"]].item())
+    gpu_rec = m["d_rec"][:n_chk].cpu().numpy().view(np.uint64)
+    if len(r["records"]) != n_chk or not (gpu_rec == r["records"]).all():
+        raise SystemExit("bench.py: the GPU record stream differs from the literal oracle's on the first %d reads" % r["reads"])
+    return {"value": r["bases"] / (r["t_enc"] + r["t_dec"]) / 1e6, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "first %d reads of this workload, literal oracle restatement (reference is single-threaded, src/main.rs:162-177)" % r["reads"],
+            "encode_mbases_s": r["bases"] / r["t_enc"] / 1e6, "decode_mbases_s": r["bases"] / r["t_dec"] / 1e6,
+            "record_stream_equal_to_gpu": True, "records_compared": n_chk}
+
+
 def release(R, m):
     for key in ("ctx", "index", "d_rec", "d_roff", "h_sample"):
         m.pop(key, None)
@@ -561,7 +583,7 @@ def main():
     ap.add_argument("--reads", type=int, default=None, help="override reads per GPU (testing)")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU baseline work (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer end-to-end leg (profiling runs)")
-    ap.add_argument("--no-extras", action="store_true", help="N > 1: skip the c4 / c5 objects")
+    ap.add_argument("--no-extras", action="store_true", help="skip the objects of the other BASELINE configs (c2 / c4 / c5)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args, int(os.environ.get("RANK", "0")))
@@ -591,22 +613,7 @@ def main():
     # double as a parity check of the GPU's record stream for the same reads ----
     cpu = None
     if world == 1 and rank == 0 and args.cpu_budget > 0 and m.get("h_sample") is not None:
-        from oracle import binding as ob
-        index = m["index"]
-        oracle = ob.OracleIndex.from_arrays(index.k, index.n_sets, index.rows(), index.lcs())
-        h_bases, h_off = m["h_sample"]
-        n_s = min(n_reads, 1 << 15)
-        sb = h_bases[: n_s * read_len].numpy()
-        so = h_off[: n_s + 1].numpy().astype(np.uint64)
-        r = time_oracle(oracle, sb, so, 1, args.cpu_budget, keep_records=True)
-        n_chk = int(m["d_roff"][r["reads"]].item())
-        gpu_rec = m["d_rec"][:n_chk].cpu().numpy().view(np.uint64)
-        if len(r["records"]) != n_chk or not (gpu_rec == r["records"]).all():
-            raise SystemExit("bench.py: the GPU record stream differs from the literal oracle's on the first %d reads" % r["reads"])
-        cpu = {"value": r["bases"] / (r["t_enc"] + r["t_dec"]) / 1e6, "unit": UNIT, "cores": 1, "kind": "port",
-               "sample": "first %d reads of this workload, literal oracle restatement (reference is single-threaded, src/main.rs:162-177)" % r["reads"],
-               "encode_mbases_s": r["bases"] / r["t_enc"] / 1e6, "decode_mbases_s": r["bases"] / r["t_dec"] / 1e6,
-               "record_stream_equal_to_gpu": True, "records_compared": n_chk}
+        cpu = cpu_baseline_of(m, n_reads, read_len, args.cpu_budget)
     release(R, m)
 
     # ---- N > 1: BASELINE configs 4 and 5 beside the C3-weak headline ----
@@ -638,6 +645,31 @@ def main():
             m5["total_bases"] = n5 * world * c5["read_len"]
             extras["c5"] = summarize_extra(m5, 3, l2["gsectors"], "C5: 5 Mbp genome, k=91, 2 M x 10 kbp reads at 5 % over 8 GPUs")
             release(R, m5)
+
+    # ---- N = 1: the other BASELINE configs beside the C3 headline -- C2 whole (it is a one-B200 config), and one 8-GPU shard each
+    # of C4 and C5 (what one GPU of the N = 8 line works on), so that every config has a driver-run number on this line ----
+    if world == 1 and cfg["name"] == "C3" and args.reads is None and not args.no_extras:
+        c2 = config_of("C2")
+        m2 = measure(R, c2, 0, c2["n_reads"], 3, 3, args, want_e2e=not args.no_e2e, want_l2=False, light=True)
+        m2["total_bases"] = c2["n_reads"] * c2["read_len"]
+        extras["c2"] = summarize_extra(m2, 3, l2["gsectors"], "C2: 5 Mbp genome, k=31, 1 M x 150 bp reads at 1 %, whole config on 1 GPU")
+        if args.cpu_budget > 0 and m2.get("h_sample") is not None:
+            extras["c2"]["cpu_baseline"] = cpu_baseline_of(m2, c2["n_reads"], c2["read_len"], min(args.cpu_budget, 5.0))
+        release(R, m2)
+        c4 = config_of("C4")
+        lo4, hi4 = shard_bounds(c4["n_reads"], 8)[0]
+        m4 = measure(R, c4, lo4, hi4 - lo4, 3, 3, args, want_e2e=not args.no_e2e, want_l2=False, light=True)
+        m4["total_bases"] = (hi4 - lo4) * c4["read_len"]
+        extras["c4"] = summarize_extra(m4, 3, l2["gsectors"], "C4 shard: 12 Mbp genome, k=91 (64-node rank blocks), shard 0 of the 8-GPU split of 100 M x "
+                                       "150 bp reads (%d reads) on 1 GPU" % (hi4 - lo4))
+        release(R, m4)
+        c5 = config_of("C5")
+        n5 = c5["n_reads"] // 8
+        m5 = measure(R, c5, 0, n5, 3, 3, args, want_e2e=not args.no_e2e, want_l2=False, light=True)
+        m5["total_bases"] = n5 * c5["read_len"]
+        extras["c5"] = summarize_extra(m5, 3, l2["gsectors"], "C5 shard: 5 Mbp genome, k=91, shard 0 of the 8-GPU split of 2 M x 10 kbp reads at 5 %% "
+                                       "(%d reads) on 1 GPU" % n5)
+        release(R, m5)
 
     if rank != 0:
         R.finish()
