@@ -128,17 +128,12 @@ int32_t ms_pipeline(ntc_ctx* ctx, Lane& lane, const uint64_t* packed, const uint
         // stage buffer for the block's packed reads: 128 reads of the batch's mean length (+ alignment slack), at most 8 KB
         const uint64_t mean_len = n_reads ? (n_bases + n_reads - 1) / n_reads : 0;
         uint32_t stage_words = (uint32_t)std::min<uint64_t>(kMsStageWordsMax, ((kMsThreads * mean_len + 31) / 32 + 8 + 15) & ~15ull);
-        static const long stage_env = [] { const char* e = getenv("NTC_MS_STAGE_WORDS"); return e ? atol(e) : -1L; }();   // experiments
+        static const long stage_env = [] { const char* e = getenv("NTC_MS_STAGE_WORDS"); return e ? atol(e) : -1L; }();   // tests/test_stress_determinism.py
         if (stage_env >= 0) stage_words = (uint32_t)std::min<long>(stage_env, (long)kMsStageWordsMax) & ~1u;
-        // NTC_MS_PAD_SMEM: extra dynamic shared memory per block (experiments: the kernel against the L1 / shared-memory split)
-        static const size_t pad = [] { const char* e = getenv("NTC_MS_PAD_SMEM"); return e ? (size_t)strtoull(e, nullptr, 10) : (size_t)0; }();
-        static const int carve = [] { const char* e = getenv("NTC_MS_CARVEOUT"); return e ? atoi(e) : -1; }();
         static const int force_blocks = [] { const char* e = getenv("NTC_MS_BLOCKS"); return e ? atoi(e) : 0; }();
-        const size_t smem = (size_t)stage_words * 8 + pad;
+        const size_t smem = (size_t)stage_words * 8;
         const bool twelve = force_blocks ? force_blocks == 12 : stage_words <= 640;
         auto launch = [&](auto kernel) {
-            if (pad) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (carve >= 0) cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
             kernel<<<blocks_for(max_items, kMsThreads), kMsThreads, smem, st>>>(ctx->dix, packed, d_offsets, (const uint64_t*)lane.desc.p,
                                                                                 tile_off + n_reads, T, scratch, counts, status, keep_records ? 1 : 0,
                                                                                 stage_words);
@@ -291,20 +286,6 @@ int32_t decode_walk(ntc_ctx* ctx, Lane& lane, const uint64_t* d_records, uint64_
         // (a two-pass variant -- walk to 2-bit slots per record, then one thread per sequence formatting header + bases
         // left to right -- measured slower on B200: 3.31 vs 2.56 ms on C3, 9.6 vs 6.0 ms on C5; r1 A/B, profiles/r1)
         Timed t(ctx, KC_WALK, st);
-        // experiment (NTC_WALK_WINDOW=<hit ratio in percent>, with NTC_L2_PERSIST_MB set): persisting access window over the jump table
-        static const int win = [] { const char* e = getenv("NTC_WALK_WINDOW"); return e ? atoi(e) : 0; }();
-        if (win > 0) {
-            cudaStreamAttrValue av;
-            memset(&av, 0, sizeof av);
-            int maxw = 0;
-            cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, ctx->device);
-            av.accessPolicyWindow.base_ptr = ctx->d_jump;
-            av.accessPolicyWindow.num_bytes = std::min<size_t>(ctx->index_bytes[2], (size_t)maxw);
-            av.accessPolicyWindow.hitRatio = win / 100.0f;
-            av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-            av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-            cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av);
-        }
         walk_kernel<<<blocks_for(n_rec, kWalkThreads), kWalkThreads, 0, st>>>(ctx->dix, d_records, n_rec, (const uint64_t*)lane.base_off.p,
                                                             (const uint64_t*)lane.seq_idx.p, (const uint64_t*)lane.seq_endkey.p,
                                                             (const uint64_t*)lane.dec_small.p, first_no, fasta, d_out, cap, d_counts,
@@ -390,7 +371,7 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
     // (layout_kernels.cuh): 1.5 B per node go up instead of 14.  NTC_HOST_LAYOUTS=1 (and builds with 16-bit LCS words) take the
     // first version's route: host threads build them WHILE the CUDA context comes up on another thread, then they are uploaded.
     // An encode-only / decode-only context (the CLI) holds only the arrays its path reads.
-    const bool host_layouts = NTC_LCS16 != 0 || (getenv("NTC_HOST_LAYOUTS") && atoi(getenv("NTC_HOST_LAYOUTS")) != 0);
+    const bool host_layouts = getenv("NTC_HOST_LAYOUTS") && atoi(getenv("NTC_HOST_LAYOUTS")) != 0;
     int n_dev = 0;
     cudaError_t e_init = cudaSuccess;
     double t_cuda = 0;
@@ -565,17 +546,6 @@ int32_t ntc_ctx_create_for(int32_t device, const ntc_index* idx, uint32_t uses, 
         // profiles/r1/ab_l2_persist.txt) a 64 / 79 MB set-aside slows ms_kernel from 15.3 to 20.1 / 26.4 ms, 32 MB changes
         // nothing -- the carve-out shrinks the L2 left for everything else.  (The evict_last / evict_first hints by
         // themselves measure neutral on v12: 12.01 ms without them, profiles/r1/ab_v12_variants.txt.)
-        // NTC_L2_PERSIST_MB sets a carve-out for experiments.
-        if (const char* env = getenv("NTC_L2_PERSIST_MB")) {
-            cudaDeviceProp prop;
-            if (cudaGetDeviceProperties(&prop, device) == cudaSuccess && prop.persistingL2CacheMaxSize > 0) {
-                size_t want = std::min<size_t>((size_t)strtoull(env, nullptr, 10) << 20, (size_t)prop.persistingL2CacheMaxSize);
-                cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
-                if (getenv("NTC_VERBOSE"))
-                    fprintf(stderr, "ntcomp_b200: L2 %d MB, persisting max %d MB, set-aside %zu MB\n", prop.l2CacheSize >> 20,
-                            prop.persistingL2CacheMaxSize >> 20, want >> 20);
-            }
-        }
     }
     ntc_ctx_set_host_threads(ctx, getenv("NTC_HOST_THREADS") ? atoi(getenv("NTC_HOST_THREADS")) : -1);   // default: staging for pageable caller buffers only
     if (const char* env = getenv("NTC_TILE_LEN")) ntc_ctx_set_tile_len(ctx, (uint32_t)strtoul(env, nullptr, 10));

@@ -107,24 +107,9 @@ __global__ void __launch_bounds__(256) seq_layout_kernel(const uint64_t* __restr
 // 8-byte words so the interior of a segment is written with full u64 stores; only the two edges
 // of a segment (which share words with neighbouring segments / headers) use 4/2/1-byte stores.
 // (First version, ncu r1: 1.59 G single-byte stores made walk_kernel L1TEX-bound.)
-// NTC_WALK_STREAM=1: the text stores carry the evict_first L2 policy the encode scratch uses (ncu r1 v15: plain stores,
-// lts hit rate 46 %, 4.9 GB of DRAM reads per launch for ~1 GB of compulsory ones -- the 1.6 GB output stream displaces
-// the 80 MB jump table).  Measured on B200 it is SLOWER -- 2.22 vs 1.99 ms on C3, 2.98 vs 2.78 ms on the 12 Mbp index
-// (profiles/r2/ab_walk_stream.txt): a text sector is completed by several threads at different times (the edges of
-// neighbouring records), and a partially written evict_first sector leaves L2 before the rest arrives.  Off by default.
-#ifndef NTC_WALK_STREAM
-#define NTC_WALK_STREAM 0
-#endif
+// (Rejected, profiles/r2/ab_walk_stream.txt: evict_first text stores -- 2.22 vs 1.99 ms on C3: a text sector is completed by
+// several threads at different times, and a partially written evict_first sector leaves L2 before the rest arrives.)
 NTC_HD void store_lanes(uint8_t* word_addr, uint64_t w, uint32_t lo, uint32_t hi, uint64_t pol) {  // lanes [lo, hi) of the aligned word
-#if NTC_WALK_STREAM
-    if (lo == 0 && hi == 8) { st8_stream((uint64_t*)word_addr, w, pol); return; }
-    uint32_t l = lo;
-    while (l < hi) {
-        if ((l & 3u) == 0 && l + 4 <= hi) { st4_stream(word_addr + l, (uint32_t)(w >> (8 * l)), pol); l += 4; }
-        else if ((l & 1u) == 0 && l + 2 <= hi) { st2_stream(word_addr + l, (uint16_t)(w >> (8 * l)), pol); l += 2; }
-        else { st1_stream(word_addr + l, (uint8_t)(w >> (8 * l)), pol); l += 1; }
-    }
-#else
     (void)pol;
     if (lo == 0 && hi == 8) { *(uint64_t*)word_addr = w; return; }
     uint32_t l = lo;
@@ -133,23 +118,15 @@ NTC_HD void store_lanes(uint8_t* word_addr, uint64_t w, uint32_t lo, uint32_t hi
         else if ((l & 1u) == 0 && l + 2 <= hi) { *(uint16_t*)(word_addr + l) = (uint16_t)(w >> (8 * l)); l += 2; }
         else { word_addr[l] = (uint8_t)(w >> (8 * l)); l += 1; }
     }
-#endif
 }
 NTC_HD void store_word(uint8_t* addr, uint64_t w, uint64_t pol) {
-#if NTC_WALK_STREAM
-    st8_stream((uint64_t*)addr, w, pol);
-#else
     (void)pol;
     *(uint64_t*)addr = w;
-#endif
 }
 
 // Complete words leave in descending address order; the upper half of a 16-byte unit waits in `hold` for the lower
 // half, and the two go out as one 16-byte store (ncu r1 v14: after the cost sort walk_kernel ran at the L1TEX sector
 // rate, 298 M store sectors for 51 M sectors of text -- every 8-byte store of a lane is a sector access of its own).
-#ifndef NTC_WALK_PAIR16
-#define NTC_WALK_PAIR16 1
-#endif
 struct LeftWriter {
     uint8_t* out;   // 16-byte aligned base of the output buffer
     uint64_t p;     // bytes [p, segment end) are done; pending bytes of the word holding p sit in acc
@@ -163,23 +140,13 @@ struct LeftWriter {
     // lanes [0, hi) of the aligned word at byte position pos (a multiple of 8)
     NTC_HD void put(uint64_t pos, uint64_t w, uint32_t hi) {
         if (hi != 8) { store_lanes(out + pos, w, 0, hi, pol); return; } // right edge of the segment: nothing is held yet
-#if !NTC_WALK_PAIR16
-        store_word(out + pos, w, pol);
-        return;
-#endif
         if (pos & 8) {
             if (have) store_word(out + pos + 8, hold, pol);            // (not reached: words arrive 8 bytes apart)
             hold = w;
             have = true;
         } else if (have) {
-#if NTC_WALK_STREAM
-            st16_stream(out + pos, w, hold, pol);
-#elif defined(__CUDA_ARCH__)
-            *(ulonglong2*)(out + pos) = make_ulonglong2(w, hold);
-#else
             *(uint64_t*)(out + pos) = w;
             *(uint64_t*)(out + pos + 8) = hold;
-#endif
             have = false;
         } else {
             store_word(out + pos, w, pol);
@@ -356,9 +323,6 @@ NTC_HD void walk_thread(const DevIndex& ix, const uint64_t* __restrict__ rec, ui
 #ifndef NTC_WALK_THREADS
 #define NTC_WALK_THREADS 256
 #endif
-#ifndef NTC_WALK_SORT
-#define NTC_WALK_SORT 1
-#endif
 constexpr int kWalkThreads = NTC_WALK_THREADS;
 constexpr uint32_t kWalkBuckets = 16;
 
@@ -377,7 +341,6 @@ __global__ void __launch_bounds__(kWalkThreads) walk_kernel(DevIndex ix, const u
     const uint32_t tid = threadIdx.x;
     // record i0 + tid on thread tid: coalesced loads of everything the walk needs
     const WalkItem mine = walk_prepare(rec, n_rec, base_off, seq_idx, seq_endkey, totals, fasta, out, cap_bytes, counts, i0 + tid);
-#if NTC_WALK_SORT
     __shared__ uint32_t s_hist[kWalkBuckets];
     __shared__ uint64_t s_w[kWalkThreads], s_end[kWalkThreads], s_sid[kWalkThreads];
     __shared__ uint32_t s_L[kWalkThreads], s_flags[kWalkThreads];
@@ -392,9 +355,6 @@ __global__ void __launch_bounds__(kWalkThreads) walk_kernel(DevIndex ix, const u
     __syncthreads();
     const WalkItem it{s_w[tid], s_end[tid], s_sid[tid], s_L[tid], s_flags[tid]};
     walk_emit(ix, it, first_no, out, status);
-#else
-    walk_emit(ix, mine, first_no, out, status);
-#endif
 }
 
 }  // namespace ntc

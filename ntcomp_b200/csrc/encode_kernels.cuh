@@ -288,14 +288,9 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
         // all loads of the iteration issue back to back, before any of their results is used
         const typename RL::Ent va = RL::ld_ent(ix.rank, bs, c, keep);
         const typename RL::Part vb = RL::ld_part_if(ix.rank, be, c, keep, other);
-#if NTC_LCS16
-        const uint32_t xs = ld2_keep_if(ix.lcsx + s, keep, spec);     // node s: LCS[s], distance to the previous smaller value
-        const uint32_t xe = ld2_keep_if(ix.lcsx + e, keep, spec);     // node e (<= n: the array has n + 1 entries): LCS[e], distance to the next smaller
-#else
         const uint32_t xs = ld4_keep_if(ix.lcsx + s, keep, spec);
         uint32_t xe = ld4_keep_if(ix.lcsx + (e - 1u), keep, spec && !single);
         xe = single ? xs : xe;
-#endif
         const uint32_t s2 = RL::rank(va, os);
         const uint32_t e2 = single ? s2 + RL::bit(va, os) : RL::rank_sel(va, vb, other, oe);
         if (fresh) {
@@ -322,11 +317,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
             if (!spec) { force = true; continue; }   // (a B200 sweep found on-demand loads here no faster for any window)
             force = false;
             const int ls = s > 0 ? (int)lcsx_lcs(xs) : -1;              // LCS[s]   (low half of word s)
-#if NTC_LCS16
-            const int le = e < n ? (int)lcsx_lcs(xe) : -1;              // LCS[e]
-#else
             const int le = e < n ? (int)((xe >> 16) & 0xFFu) : -1;      // LCS[e]   (high half of word e-1)
-#endif
             const int t = tmax(ls, le);
             if (t <= 0) { s = 0; e = n; d = 0; continue; }             // LCS >= 0 everywhere
             if (ls == t) {
@@ -335,11 +326,7 @@ NTC_HD void ms_thread(const DevIndex& ix, const uint64_t* packed, const uint64_t
                 if (dl == NTC_LCS_DIST_SAT) while (s > 0 && lcsx_lcs(NTC_LDG(ix.lcsx + s)) >= (uint32_t)t) s--;
             }
             if (le == t) {
-#if NTC_LCS16
-                uint32_t dr = xe >> 12;
-#else
                 uint32_t dr = xe >> 24;
-#endif
                 e += dr;
                 if (dr == NTC_LCS_DIST_SAT) while (e < n && lcsx_lcs(NTC_LDG(ix.lcsx + e)) >= (uint32_t)t) e++;
             }

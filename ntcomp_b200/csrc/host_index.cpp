@@ -164,16 +164,11 @@ void build_lcs_words(const ntc_index& idx, std::vector<ntc_lcsx_t>* out) {
         stack.push_back((uint32_t)i);
     }
     out->assign(n + 1, 0);
-#if NTC_LCS16
-    for (uint64_t i = 0; i < n; i++)
-        (*out)[i] = (ntc_lcsx_t)((uint32_t)idx.lcs[i] | (std::min<uint32_t>(dl[i], 15u) << 8) | (std::min<uint32_t>(dr[i], 15u) << 12));
-#else
     for (uint64_t i = 0; i <= n; i++) {
         uint32_t lo = i < n ? ((uint32_t)idx.lcs[i] | ((uint32_t)dl[i] << 8)) : 0u;
         uint32_t hi = i + 1 < n ? ((uint32_t)idx.lcs[i + 1] | ((uint32_t)dr[i + 1] << 8)) : 0u;
         (*out)[i] = lo | (hi << 16);
     }
-#endif
 }
 
 // window of match lengths in which extensions of chance matches keep failing: around log4(n_sets)

@@ -10,17 +10,8 @@
 //      load and the 64-bit masks cost 19 % on a 5 Mbp index (C3 11.5 -> 13.7 ms) and win once the 2 B / node array no longer stays in L2:
 //      -10 % at 12 Mbp (C4 20.4 -> 18.4 ms, rank array 48 -> 24 MB), -28 % at 24 Mbp (32.3 -> 23.4 ms).  profiles/r2/ab_rank64.txt.
 #define NTC_RANK64_MIN_NODES 20000000ull   // indexes with at least this many nodes take the 64-node layout
-// LCS side array.  0: one u32 per node = LCS[i] | min(255, i - PSV(i)) << 8 | LCS[i+1] << 16 | min(255, NSV(i+1) - (i+1)) << 24 -- a
-// singleton interval finds both of its sides in ONE word.  1: one u16 per node = LCS[i] | min(15, i - PSV(i)) << 8 |
-// min(15, NSV(i) - i) << 12 -- half the bytes (rank + LCS of a 12 Mbp index: 96 instead of 144 MB, inside the L2), two loads per
-// contraction instead of one.  A/B: profiles/r2/ab_lcs16.txt.
-#ifndef NTC_LCS16
-#define NTC_LCS16 0
-#endif
-#if NTC_LCS16
-typedef unsigned short ntc_lcsx_t;
-#define NTC_LCS_DIST_SAT 15u
-#else
+// LCS side array: one u32 per node = LCS[i] | min(255, i - PSV(i)) << 8 | LCS[i+1] << 16 | min(255, NSV(i+1) - (i+1)) << 24 -- a
+// singleton interval finds both of its sides in ONE word.  (Rejected, profiles/r2/ab_lcs16.txt: a u16 per node with 4-bit
+// distances -- half the bytes, but two loads per contraction; slower on C3 and on the 12 Mbp index.)
 typedef unsigned int ntc_lcsx_t;
 #define NTC_LCS_DIST_SAT 255u
-#endif

@@ -376,7 +376,6 @@ extern "C" int32_t emul_layouts_check(const ntc_index* idx) {
         if (got_pfx != want_pfx) return 20 + (int32_t)nodes;
         for (int c = 0; c < 4; c++) if (c_start[c] != (uint32_t)idx->C[c]) return 30;
     }
-#if !NTC_LCS16
     {
         std::vector<ntc_lcsx_t> want;
         build_lcs_words(*idx, &want);
@@ -384,7 +383,6 @@ extern "C" int32_t emul_layouts_check(const ntc_index* idx) {
         for (uint64_t i = 0; i <= n; i++) lay::lcs_word_thread(idx->lcs.data(), n, got.data(), i);
         if (want.size() != got.size() || memcmp(want.data(), got.data(), got.size() * 4) != 0) return 40;
     }
-#endif
     {
         std::vector<uint64_t> want, a(n, ~0ull), b(n, ~0ull);
         build_jump_table(*idx, &want, 2);
